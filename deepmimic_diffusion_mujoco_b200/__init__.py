@@ -1,0 +1,14 @@
+"""B200-native drop-in for the DiffMimic sampling hot path (sample -> condition -> score).
+
+Public names mirror the reference modules they replace:
+  diffuser.models.temporal.TemporalUnet            -> TemporalUnet
+  diffuser.models.diffusion.GaussianDiffusion      -> GaussianDiffusion (sampling half), Sample, InjectedNoise
+  diffuser.models.sampling_config.apply_conditioning* -> sampling_config
+  data_loaders.motion_dataset.MotionDataset        -> MotionDataset
+  metrics.fid_score.MotionFID                      -> MotionFID
+"""
+from ._lib import DmError, build, lib  # noqa: F401
+from .diffusion import GaussianDiffusion, InjectedNoise, Sample, default_sample_fn  # noqa: F401
+from .sampling_config import (apply_conditioning, apply_conditioning_motion_editing,  # noqa: F401
+                              trace_conditioning)
+from .temporal import TemporalUnet  # noqa: F401

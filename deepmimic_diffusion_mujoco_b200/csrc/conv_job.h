@@ -1,0 +1,75 @@
+// Descriptor of one Conv1d-family layer launch (K1 + K2 of SURVEY.md §2b), shared by host plan builder and
+// the device kernel.  One launch computes, for every sample group, a conv (k=5 pad 2 | k=3 stride 2 |
+// k=1 | ConvTranspose k=4 stride 2) as an implicit GEMM on tcgen05, followed in the same kernel by the
+// epilogue of the reference block: bias, GroupNorm(8), Mish, + time bias, + residual.
+//
+// Reference semantics restated here:
+//   Conv1dBlock            diffuser/models/helpers.py:50-69
+//   ResidualTemporalBlock  diffuser/models/temporal.py:18-46
+//   Downsample1d/Upsample1d diffuser/models/helpers.py:32-47
+#pragma once
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace dm {
+
+constexpr int kGroupSamples = 16;   // samples per activation group: layout [plane][G][L][16][C] fp16
+constexpr int kMaxTaps = 5;
+constexpr int kConvThreads = 192;   // warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer
+
+struct ConvTap {
+  int wtap;    // index into the packed weight's tap dimension
+  int shift;   // l offset of this tap's view inside the A box (in l positions)
+  int phase;   // accumulator set (ConvTranspose: 0 = even outputs, 1 = odd outputs)
+  int first;   // 1 if this is the first tap accumulated into its phase
+};
+
+enum { EPI_BIAS = 0, EPI_GN_MISH = 1 };
+
+struct ConvJob {
+  CUtensorMap a_map[2];   // 5-D (C, 16, L, G, plane) fp16, one per input source (2 = channel concat)
+  CUtensorMap w_map;      // 4-D (CinTot, CoutPad, ntaps, plane) fp16
+  int nsrc;
+  int src_chunks[2];      // channel chunks per source
+  int Cc;                 // channels per chunk (64 -> SWIZZLE_128B rows, 32 -> SWIZZLE_64B rows)
+  int row_bytes;          // Cc * 2
+  int swz;                // UMMA layout code (2 = 128B, 4 = 64B)
+  int S;                  // samples per CTA: 8 or 16
+  int l_stride;           // 1, or 2 for the strided down-sampling conv
+  int halo_lo;            // A box starts at l = l_stride * j0 - halo_lo
+  int box_l;              // l positions in the A box
+  int Lt;                 // M positions (j) per l-tile; Lt * S is a multiple of 128
+  int n_ltiles;
+  int Mt;                 // 128-row MMA tiles per l-tile
+  int Lj;                 // number of valid M positions (Lout, or Lin for ConvTranspose)
+  int Lout;               // output length
+  int ntaps;
+  ConvTap taps[kMaxTaps];
+  int nphase;
+  int Nc;                 // output channels per CTA == MMA N
+  int n_a_stages, n_w_stages;
+  int a_stage_bytes, w_stage_bytes, a_plane_bytes, w_plane_bytes;
+  int a_tx_bytes, w_tx_bytes;
+  int tmem_cols;
+  // epilogue
+  int epi;
+  int Cout;               // real output channels
+  int cg;                 // channels per GroupNorm group
+  int B;                  // real batch (masks the fp32 output)
+  const float* bias;      // [CoutPad]
+  const float* gamma;     // [CoutPad]
+  const float* beta;      // [CoutPad]
+  const float* tbias;     // time bias rows, added after Mish (temporal.py:44); null if none
+  int tbias_stride;       // 0: one row shared by all samples (uniform t); else per-sample row stride
+  const __half* res;      // residual planes in activation layout, added last (temporal.py:46); null if none
+  int res_C;
+  long long res_plane_stride;
+  __half* out;            // output planes in activation layout; null if none
+  int out_C;
+  long long out_plane_stride;
+  float* out_f32;         // public layout [B][Lout][out_f32_C]; null if none
+  int out_f32_C;
+};
+
+}  // namespace dm

@@ -1,0 +1,765 @@
+// Plan builder + C ABI for the U-Net / sampling-loop part of the hot path.  Host C++ only; the arithmetic is
+// in conv_kernel.cu and step_kernels.cu.
+#include "plan.h"
+
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/dm_b200.h"
+
+namespace dm {
+
+cudaError_t launch_conv_job(const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes, cudaStream_t stream);
+cudaError_t read_device_error(unsigned int* code);
+
+static thread_local char g_err[512] = "";
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+const char* last_error() { return g_err; }
+
+#define DM_CUDA(expr)                                                                              \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess) return fail(DM_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(_e)); \
+  } while (0)
+
+int check_device() {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(DM_ERR_DEVICE, "no CUDA device: this library has no CPU fallback");
+  }
+  int dev = 0, major = 0;
+  DM_CUDA(cudaGetDevice(&dev));
+  DM_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) return fail(DM_ERR_DEVICE, "device compute capability %d.x is not sm_100 (B200)", major);
+  return DM_OK;
+}
+
+// ---- TMA descriptor encoding through the driver entry point (no link-time libcuda dependency) ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+static int encode_map(CUtensorMap* m, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swz) {
+  EncodeTiledFn fn = get_encode();
+  if (!fn) return fail(DM_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t gd[5], gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
+  CUtensorMapSwizzle sw = swz == 2 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, rank, base, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(DM_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return DM_OK;
+}
+
+// ---- allocation helpers ----
+static int dev_alloc(dm_plan* P, void** p, size_t bytes, bool zero = true) {
+  DM_CUDA(cudaMalloc(p, bytes));
+  P->allocs.push_back(*p);
+  if (zero) DM_CUDA(cudaMemset(*p, 0, bytes));
+  return DM_OK;
+}
+static int upload(dm_plan* P, const std::vector<float>& h, float** d) {
+  int rc = dev_alloc(P, reinterpret_cast<void**>(d), h.size() * sizeof(float), false);
+  if (rc) return rc;
+  DM_CUDA(cudaMemcpy(*d, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+  return DM_OK;
+}
+static int new_act(dm_plan* P, int C, int L, int* idx) {
+  Act a;
+  a.C = C;
+  a.L = L;
+  a.plane = (long long)P->G * L * kGroupSamples * C;
+  int rc = dev_alloc(P, reinterpret_cast<void**>(&a.p), (size_t)a.plane * 2 * sizeof(__half));
+  if (rc) return rc;
+  P->acts.push_back(a);
+  *idx = (int)P->acts.size() - 1;
+  return DM_OK;
+}
+
+typedef std::map<std::string, HostTensor> WeightMap;
+static int find_w(const WeightMap& W, const std::string& name, std::vector<int64_t> shape, const float** out) {
+  auto it = W.find(name);
+  if (it == W.end()) return fail(DM_ERR_WEIGHT, "state_dict tensor '%s' missing", name.c_str());
+  if (it->second.shape != shape) return fail(DM_ERR_WEIGHT, "state_dict tensor '%s' has the wrong shape", name.c_str());
+  *out = it->second.data;
+  return DM_OK;
+}
+
+enum ConvKind { CONV_K5 = 0, CONV_DOWN = 1, CONV_K1 = 2, CONV_T4 = 3 };
+
+struct ConvSpec {
+  std::string name;      // debug name
+  std::string wkey;      // state_dict prefix of the conv: "<wkey>.weight", "<wkey>.bias"
+  std::string gnkey;     // GroupNorm prefix or ""
+  ConvKind kind;
+  int src[2] = {-1, -1}; // act indices
+  int src_real_c[2] = {0, 0};  // real (unpadded) channels each source contributes to the weight's Cin
+  int nsrc = 1;
+  int Cout = 0;
+  int tb_off = -1;
+  int res = -1;          // residual act index
+  bool want_act_out = true;
+  bool f32_out = false;  // write plan->model_out style fp32 [B,L,Cout]
+};
+
+static int round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+// Adds one conv launch to the plan; returns the output act index in *out_idx (or -1).
+static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out_idx) {
+  Layer ly;
+  ConvJob& j = ly.job;
+  memset(&j, 0, sizeof(j));
+  ly.name = sp.name;
+  ly.tb_off = sp.tb_off;
+
+  const Act& a0 = P->acts[sp.src[0]];
+  const int Lin = a0.L;
+  int ktaps = sp.kind == CONV_K5 ? 5 : sp.kind == CONV_DOWN ? 3 : sp.kind == CONV_K1 ? 1 : 4;
+  const int Lout = sp.kind == CONV_DOWN ? Lin / 2 : sp.kind == CONV_T4 ? Lin * 2 : Lin;
+  const int Lj = sp.kind == CONV_T4 ? Lin : Lout;
+
+  // channel chunking
+  int cin_tot = 0, cin_real = 0;
+  bool all64 = true;
+  for (int s = 0; s < sp.nsrc; ++s) {
+    const Act& a = P->acts[sp.src[s]];
+    if (a.L != Lin) return fail(DM_ERR_ARG, "%s: concat sources differ in length", sp.name.c_str());
+    if (a.C % 64) all64 = false;
+    cin_tot += a.C;
+    cin_real += sp.src_real_c[s];
+  }
+  j.Cc = all64 ? 64 : 32;
+  j.row_bytes = j.Cc * 2;
+  j.swz = all64 ? 2 : 4;
+  j.nsrc = sp.nsrc;
+  for (int s = 0; s < sp.nsrc; ++s) j.src_chunks[s] = P->acts[sp.src[s]].C / j.Cc;
+
+  // tile shape
+  j.l_stride = sp.kind == CONV_DOWN ? 2 : 1;
+  j.S = (sp.kind == CONV_DOWN || Lj * 8 >= 128) ? 8 : 16;
+  const int pos_per_mt = 128 / j.S;
+  int maxshift;
+  if (sp.kind == CONV_K5) { j.halo_lo = 2; maxshift = 4; }
+  else if (sp.kind == CONV_DOWN) { j.halo_lo = 1; maxshift = 2; }
+  else if (sp.kind == CONV_K1) { j.halo_lo = 0; maxshift = 0; }
+  else { j.halo_lo = 1; maxshift = 2; }
+  const int mt_total = (Lj + pos_per_mt - 1) / pos_per_mt;
+  auto box_for = [&](int mt) { return round_up(j.l_stride * (mt * pos_per_mt - 1) + maxshift + 1, 2); };
+  auto stage_for = [&](int mt) { return 2 * box_for(mt) * j.S * j.row_bytes; };
+  int Mt = mt_total;
+  const int a_budget = 80 * 1024;
+  while (Mt > 1 && (stage_for(Mt) > a_budget || box_for(Mt) > 256)) --Mt;
+  j.Mt = Mt;
+  j.Lt = Mt * pos_per_mt;
+  j.n_ltiles = (mt_total + Mt - 1) / Mt;
+  j.box_l = box_for(Mt);
+  j.Lj = Lj;
+  j.Lout = Lout;
+  j.a_plane_bytes = j.box_l * j.S * j.row_bytes;
+  j.a_tx_bytes = 2 * j.a_plane_bytes;
+  j.a_stage_bytes = round_up(j.a_tx_bytes, 1024);
+
+  // taps
+  j.nphase = 1;
+  if (sp.kind == CONV_T4) {
+    // ConvTranspose1d(k=4,s=2,p=1): out[2j] = W1 x[j] + W3 x[j-1]; out[2j+1] = W2 x[j] + W0 x[j+1]
+    j.nphase = 2;
+    j.ntaps = 4;
+    j.taps[0] = {1, 1, 0, 1};
+    j.taps[1] = {3, 0, 0, 0};
+    j.taps[2] = {2, 1, 1, 1};
+    j.taps[3] = {0, 2, 1, 0};
+  } else {
+    j.ntaps = ktaps;
+    for (int t = 0; t < ktaps; ++t) j.taps[t] = {t, t, 0, t == 0 ? 1 : 0};
+  }
+
+  // N split and TMEM budget
+  const bool gn = !sp.gnkey.empty();
+  const int cout_pad = round_up(sp.Cout, 32);
+  const int cg = gn ? sp.Cout / 8 : 32;
+  if (gn && (sp.Cout % 32 != 0)) return fail(DM_ERR_ARG, "%s: GroupNorm layers need Cout %% 32 == 0", sp.name.c_str());
+  int Nc = cout_pad < 128 ? cout_pad : 128;
+  while (cout_pad % Nc) Nc -= 32;
+  const int mt_all = j.n_ltiles * j.Mt;
+  while (j.nphase * mt_all * Nc > 512 && Nc > 32 && (Nc / 2) % 32 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
+  if (j.nphase * mt_all * Nc > 512)
+    return fail(DM_ERR_ARG, "%s: horizon too long for the TMEM-resident GroupNorm design (H <= 256)", sp.name.c_str());
+  if (gn && Nc % cg) return fail(DM_ERR_ARG, "%s: N slice does not hold whole GroupNorm groups", sp.name.c_str());
+  j.Nc = Nc;
+  ly.slices = cout_pad / Nc;
+  int cols = 32;
+  while (cols < j.nphase * mt_all * Nc) cols *= 2;
+  j.tmem_cols = cols;
+  j.w_plane_bytes = Nc * j.row_bytes;
+  j.w_tx_bytes = 2 * j.w_plane_bytes;
+  j.w_stage_bytes = round_up(j.w_tx_bytes, 1024);
+
+  // pipeline depth under a 200 KB shared-memory budget
+  const int total_chunks = (j.src_chunks[0] + (sp.nsrc > 1 ? j.src_chunks[1] : 0)) * j.n_ltiles;
+  j.n_a_stages = total_chunks > 1 ? 2 : 1;
+  const int budget = 200 * 1024;
+  if (j.n_a_stages * j.a_stage_bytes + j.w_stage_bytes > budget) j.n_a_stages = 1;
+  int nw = (budget - j.n_a_stages * j.a_stage_bytes) / j.w_stage_bytes;
+  const int w_loads = total_chunks * j.ntaps;
+  if (nw > w_loads) nw = w_loads;
+  if (nw > 8) nw = 8;
+  if (nw < 1) return fail(DM_ERR_ARG, "%s: tile does not fit in shared memory", sp.name.c_str());
+  j.n_w_stages = nw;
+  ly.smem = (size_t)j.n_a_stages * j.a_stage_bytes + (size_t)nw * j.w_stage_bytes + 1024;
+
+  // ---- pack weights: planes [2][ktaps][cout_pad][cin_tot] fp16, zero padded ----
+  const float* wsrc = nullptr;
+  int rc;
+  if (sp.kind == CONV_T4) rc = find_w(W, sp.wkey + ".weight", {cin_real, sp.Cout, ktaps}, &wsrc);
+  else rc = find_w(W, sp.wkey + ".weight", {sp.Cout, cin_real, ktaps}, &wsrc);
+  if (rc) return rc;
+  const float* bsrc = nullptr;
+  if ((rc = find_w(W, sp.wkey + ".bias", {sp.Cout}, &bsrc))) return rc;
+  const size_t wplane = (size_t)ktaps * cout_pad * cin_tot;
+  std::vector<__half> wp(2 * wplane, __float2half_rn(0.f));
+  {
+    int col0 = 0, real0 = 0;
+    for (int s = 0; s < sp.nsrc; ++s) {
+      for (int ci = 0; ci < sp.src_real_c[s]; ++ci) {
+        for (int co = 0; co < sp.Cout; ++co) {
+          for (int k = 0; k < ktaps; ++k) {
+            const int cr = real0 + ci;
+            const float v = sp.kind == CONV_T4 ? wsrc[((size_t)cr * sp.Cout + co) * ktaps + k]
+                                               : wsrc[((size_t)co * cin_real + cr) * ktaps + k];
+            const __half hi = __float2half_rn(v);
+            const __half lo = __float2half_rn(v - __half2float(hi));
+            const size_t o = ((size_t)k * cout_pad + co) * cin_tot + col0 + ci;
+            wp[o] = hi;
+            wp[wplane + o] = lo;
+          }
+        }
+      }
+      col0 += P->acts[sp.src[s]].C;
+      real0 += sp.src_real_c[s];
+    }
+  }
+  __half* wdev = nullptr;
+  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&wdev), wp.size() * sizeof(__half), false))) return rc;
+  DM_CUDA(cudaMemcpy(wdev, wp.data(), wp.size() * sizeof(__half), cudaMemcpyHostToDevice));
+  {
+    const uint64_t dims[4] = {(uint64_t)cin_tot, (uint64_t)cout_pad, (uint64_t)ktaps, 2};
+    const uint64_t str[3] = {(uint64_t)cin_tot * 2, (uint64_t)cin_tot * cout_pad * 2, (uint64_t)wplane * 2};
+    const uint32_t box[4] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 2};
+    if ((rc = encode_map(&j.w_map, wdev, 4, dims, str, box, j.swz))) return rc;
+  }
+  for (int s = 0; s < sp.nsrc; ++s) {
+    const Act& a = P->acts[sp.src[s]];
+    const uint64_t dims[5] = {(uint64_t)a.C, kGroupSamples, (uint64_t)a.L, (uint64_t)P->G, 2};
+    const uint64_t str[4] = {(uint64_t)a.C * 2, (uint64_t)a.C * 2 * kGroupSamples,
+                             (uint64_t)a.C * 2 * kGroupSamples * a.L, (uint64_t)a.plane * 2};
+    const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)j.S, (uint32_t)j.box_l, 1, 2};
+    if ((rc = encode_map(&j.a_map[s], a.p, 5, dims, str, box, j.swz))) return rc;
+  }
+
+  // ---- epilogue parameters ----
+  std::vector<float> hb(cout_pad, 0.f), hg(cout_pad, 1.f), hbe(cout_pad, 0.f);
+  for (int c = 0; c < sp.Cout; ++c) hb[c] = bsrc[c];
+  if (gn) {
+    const float *gs = nullptr, *bs = nullptr;
+    if ((rc = find_w(W, sp.gnkey + ".weight", {sp.Cout}, &gs))) return rc;
+    if ((rc = find_w(W, sp.gnkey + ".bias", {sp.Cout}, &bs))) return rc;
+    for (int c = 0; c < sp.Cout; ++c) { hg[c] = gs[c]; hbe[c] = bs[c]; }
+  }
+  float *db, *dg, *dbe;
+  if ((rc = upload(P, hb, &db)) || (rc = upload(P, hg, &dg)) || (rc = upload(P, hbe, &dbe))) return rc;
+  j.epi = gn ? EPI_GN_MISH : EPI_BIAS;
+  j.Cout = sp.Cout;
+  j.cg = cg;
+  j.B = P->B;
+  j.bias = db;
+  j.gamma = dg;
+  j.beta = dbe;
+  j.tbias = nullptr;
+  j.tbias_stride = 0;
+  if (sp.res >= 0) {
+    const Act& r = P->acts[sp.res];
+    if (r.L != Lout || r.C < cout_pad) return fail(DM_ERR_ARG, "%s: residual shape mismatch", sp.name.c_str());
+    j.res = r.p;
+    j.res_C = r.C;
+    j.res_plane_stride = r.plane;
+  }
+  *out_idx = -1;
+  if (sp.want_act_out) {
+    int oi;
+    if ((rc = new_act(P, cout_pad, Lout, &oi))) return rc;
+    const Act& o = P->acts[oi];
+    j.out = o.p;
+    j.out_C = o.C;
+    j.out_plane_stride = o.plane;
+    ly.out_act = oi;
+    *out_idx = oi;
+  }
+  if (sp.f32_out) {
+    j.out_f32 = P->model_out;
+    j.out_f32_C = sp.Cout;
+  }
+  P->layers.push_back(ly);
+  return DM_OK;
+}
+
+}  // namespace dm
+
+// =====================================================================================================
+// U-Net launch list (TemporalUnet.__init__/forward, diffuser/models/temporal.py:51-165)
+// =====================================================================================================
+namespace dm {
+
+struct BlockOut { int act; };
+
+// ResidualTemporalBlock (temporal.py:18-46): conv5+GN+Mish (+time bias) -> conv5+GN+Mish (+ residual)
+static int add_resblock(dm_plan* P, const WeightMap& W, const std::string& key, const int* src, const int* src_real,
+                        int nsrc, int cin_real, int Cout, int* tb_cursor, int* out_act) {
+  int rc, mid = -1, res = -1, out = -1;
+  ConvSpec c0;
+  c0.name = key + ".blocks.0";
+  c0.wkey = key + ".blocks.0.block.0";
+  c0.gnkey = key + ".blocks.0.block.2";
+  c0.kind = CONV_K5;
+  c0.nsrc = nsrc;
+  for (int s = 0; s < nsrc; ++s) { c0.src[s] = src[s]; c0.src_real_c[s] = src_real[s]; }
+  c0.Cout = Cout;
+  c0.tb_off = *tb_cursor;
+  if ((rc = add_conv(P, W, c0, &mid))) return rc;
+
+  if (cin_real != Cout) {
+    ConvSpec cr;
+    cr.name = key + ".residual_conv";
+    cr.wkey = key + ".residual_conv";
+    cr.kind = CONV_K1;
+    cr.nsrc = nsrc;
+    for (int s = 0; s < nsrc; ++s) { cr.src[s] = src[s]; cr.src_real_c[s] = src_real[s]; }
+    cr.Cout = Cout;
+    if ((rc = add_conv(P, W, cr, &res))) return rc;
+  } else {
+    res = src[0];  // nn.Identity
+  }
+
+  ConvSpec c1;
+  c1.name = key + ".blocks.1";
+  c1.wkey = key + ".blocks.1.block.0";
+  c1.gnkey = key + ".blocks.1.block.2";
+  c1.kind = CONV_K5;
+  c1.src[0] = mid;
+  c1.src_real_c[0] = Cout;
+  c1.Cout = Cout;
+  c1.res = res;
+  if ((rc = add_conv(P, W, c1, &out))) return rc;
+  *tb_cursor += Cout;
+  *out_act = out;
+  return DM_OK;
+}
+
+static int build_unet(dm_plan* P, const WeightMap& W) {
+  const int nlev = (int)P->mults.size();
+  std::vector<int> dims;
+  dims.push_back(P->T);
+  for (int m : P->mults) dims.push_back(P->dim * m);
+  int rc;
+
+  // time-bias row layout: blocks in module order downs, mid, ups
+  int tb_total = 0;
+  for (int i = 0; i < nlev; ++i) tb_total += 2 * dims[i + 1];
+  tb_total += 2 * dims[nlev];
+  for (int i = nlev - 1; i >= 1; --i) tb_total += 2 * dims[i];
+  P->TB = tb_total;
+
+  // input operand planes: transition_dim padded to a multiple of 64 channels
+  const int xs_C = round_up(P->T, 64);
+  if ((rc = new_act(P, xs_C, P->H, &P->xs_act))) return rc;
+  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->model_out), (size_t)P->B * P->H * P->T * sizeof(float)))) return rc;
+
+  int tb = 0;
+  int x = P->xs_act, x_real = P->T;
+  std::vector<int> skips, skip_c;
+  std::vector<float> wcat, bcat;
+  auto add_tb = [&](const std::string& key, int Cout) -> int {
+    const float *w = nullptr, *b = nullptr;
+    int r;
+    if ((r = find_w(W, key + ".time_mlp.1.weight", {Cout, P->dim}, &w))) return r;
+    if ((r = find_w(W, key + ".time_mlp.1.bias", {Cout}, &b))) return r;
+    wcat.insert(wcat.end(), w, w + (size_t)Cout * P->dim);
+    bcat.insert(bcat.end(), b, b + Cout);
+    return DM_OK;
+  };
+
+  for (int i = 0; i < nlev; ++i) {
+    const int cout = dims[i + 1];
+    const std::string k = "downs." + std::to_string(i);
+    int o;
+    if ((rc = add_tb(k + ".0", cout))) return rc;
+    if ((rc = add_resblock(P, W, k + ".0", &x, &x_real, 1, x_real, cout, &tb, &o))) return rc;
+    x = o; x_real = cout;
+    if ((rc = add_tb(k + ".1", cout))) return rc;
+    if ((rc = add_resblock(P, W, k + ".1", &x, &x_real, 1, x_real, cout, &tb, &o))) return rc;
+    x = o;
+    skips.push_back(x);
+    skip_c.push_back(cout);
+    if (i < nlev - 1) {
+      ConvSpec d;
+      d.name = k + ".3.conv";
+      d.wkey = k + ".3.conv";
+      d.kind = CONV_DOWN;
+      d.src[0] = x;
+      d.src_real_c[0] = cout;
+      d.Cout = cout;
+      if ((rc = add_conv(P, W, d, &o))) return rc;
+      x = o;
+    }
+  }
+  {
+    const int c = dims[nlev];
+    int o;
+    if ((rc = add_tb("mid_block1", c))) return rc;
+    if ((rc = add_resblock(P, W, "mid_block1", &x, &x_real, 1, c, c, &tb, &o))) return rc;
+    x = o;
+    if ((rc = add_tb("mid_block2", c))) return rc;
+    if ((rc = add_resblock(P, W, "mid_block2", &x, &x_real, 1, c, c, &tb, &o))) return rc;
+    x = o;
+  }
+  // ups: for (dim_in, dim_out) in reversed(in_out[1:]) (temporal.py:96-109)
+  for (int u = 0; u < nlev - 1; ++u) {
+    const int lev = nlev - 1 - u;          // in_out index
+    const int dim_in = dims[lev], dim_out = dims[lev + 1];
+    const std::string k = "ups." + std::to_string(u);
+    const int skip = skips.back();
+    skips.pop_back();
+    skip_c.pop_back();
+    int srcs[2] = {x, skip};
+    int reals[2] = {dim_out, dim_out};
+    int o;
+    if ((rc = add_tb(k + ".0", dim_in))) return rc;
+    if ((rc = add_resblock(P, W, k + ".0", srcs, reals, 2, 2 * dim_out, dim_in, &tb, &o))) return rc;
+    x = o; x_real = dim_in;
+    if ((rc = add_tb(k + ".1", dim_in))) return rc;
+    if ((rc = add_resblock(P, W, k + ".1", &x, &x_real, 1, dim_in, dim_in, &tb, &o))) return rc;
+    x = o;
+    ConvSpec t;
+    t.name = k + ".3.conv";
+    t.wkey = k + ".3.conv";
+    t.kind = CONV_T4;
+    t.src[0] = x;
+    t.src_real_c[0] = dim_in;
+    t.Cout = dim_in;
+    if ((rc = add_conv(P, W, t, &o))) return rc;
+    x = o;
+  }
+  {
+    ConvSpec f0;
+    f0.name = "final_conv.0";
+    f0.wkey = "final_conv.0.block.0";
+    f0.gnkey = "final_conv.0.block.2";
+    f0.kind = CONV_K5;
+    f0.src[0] = x;
+    f0.src_real_c[0] = P->dim;
+    f0.Cout = P->dim;
+    int o;
+    if ((rc = add_conv(P, W, f0, &o))) return rc;
+    ConvSpec f1;
+    f1.name = "final_conv.1";
+    f1.wkey = "final_conv.1";
+    f1.kind = CONV_K1;
+    f1.src[0] = o;
+    f1.src_real_c[0] = P->dim;
+    f1.Cout = P->T;
+    f1.want_act_out = false;
+    f1.f32_out = true;
+    int o2;
+    if ((rc = add_conv(P, W, f1, &o2))) return rc;
+  }
+  if (tb != P->TB) return fail(DM_ERR_ARG, "internal: time-bias layout mismatch (%d vs %d)", tb, P->TB);
+
+  // time MLP parameters
+  const float *w1, *b1, *w2, *b2;
+  if ((rc = find_w(W, "time_mlp.1.weight", {4 * P->dim, P->dim}, &w1))) return rc;
+  if ((rc = find_w(W, "time_mlp.1.bias", {4 * P->dim}, &b1))) return rc;
+  if ((rc = find_w(W, "time_mlp.3.weight", {P->dim, 4 * P->dim}, &w2))) return rc;
+  if ((rc = find_w(W, "time_mlp.3.bias", {P->dim}, &b2))) return rc;
+  float *dw1, *db1, *dw2, *db2, *dwc, *dbc;
+  const int D = P->dim;
+  if ((rc = upload(P, std::vector<float>(w1, w1 + 4 * D * D), &dw1))) return rc;
+  if ((rc = upload(P, std::vector<float>(b1, b1 + 4 * D), &db1))) return rc;
+  if ((rc = upload(P, std::vector<float>(w2, w2 + 4 * D * D), &dw2))) return rc;
+  if ((rc = upload(P, std::vector<float>(b2, b2 + D), &db2))) return rc;
+  if ((rc = upload(P, wcat, &dwc))) return rc;
+  if ((rc = upload(P, bcat, &dbc))) return rc;
+  P->tmlp = TimeMlpParams{D, P->TB, dw1, db1, dw2, db2, dwc, dbc};
+  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->seed_dev), sizeof(unsigned long long)))) return rc;
+  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tb_rows), (size_t)P->G * kGroupSamples * P->TB * sizeof(float))))
+    return rc;
+  return DM_OK;
+}
+
+// Launch every layer.  tb: time-bias rows; tb_stride 0 = one row for all samples (uniform t).
+static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, cudaStream_t s) {
+  for (Layer& ly : P->layers) {
+    ConvJob j = ly.job;
+    if (ly.tb_off >= 0) {
+      j.tbias = tb + ly.tb_off;
+      j.tbias_stride = tb_stride;
+    }
+    if (j.out_f32) j.out_f32 = out_f32;
+    DM_CUDA(launch_conv_job(j, P->G, ly.slices, ly.smem, s));
+    P->last_launches++;
+  }
+  return DM_OK;
+}
+
+}  // namespace dm
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+using namespace dm;
+
+extern "C" const char* dm_last_error(void) { return last_error(); }
+
+extern "C" int dm_device_error_code(unsigned int* code) {
+  if (!code) return fail(DM_ERR_ARG, "null argument");
+  DM_CUDA(read_device_error(code));
+  return DM_OK;
+}
+
+extern "C" int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, int H, int T, int dim,
+                              const int* dim_mults, int n_mults, dm_plan_t** plan) {
+  if (!weights || !plan || !dim_mults) return fail(DM_ERR_ARG, "null argument");
+  if (B < 1 || T < 1 || dim < 32 || dim % 32) return fail(DM_ERR_ARG, "need B >= 1, T >= 1, dim a multiple of 32");
+  if (n_mults < 2 || n_mults > 6) return fail(DM_ERR_ARG, "need 2..6 resolution levels");
+  const int div = 1 << (n_mults - 1);
+  if (H < div || H % div)
+    return fail(DM_ERR_ARG, "horizon %d must be a positive multiple of %d (temporal.py:156 concat would fail)", H, div);
+  int rc = check_device();
+  if (rc) return rc;
+  WeightMap W;
+  for (int i = 0; i < n_weights; ++i) {
+    if (!weights[i].name || !weights[i].data || weights[i].ndim < 1 || weights[i].ndim > 4)
+      return fail(DM_ERR_WEIGHT, "weight entry %d is malformed", i);
+    HostTensor t;
+    t.data = weights[i].data;
+    t.shape.assign(weights[i].shape, weights[i].shape + weights[i].ndim);
+    W[weights[i].name] = t;
+  }
+  for (auto& kv : W)
+    if (kv.first.find("to_qkv") != std::string::npos)
+      return fail(DM_ERR_ARG, "attention=True (LinearAttention, helpers.py:110-131) is not supported");
+  dm_plan* P = new dm_plan();
+  P->B = B; P->H = H; P->T = T; P->dim = dim;
+  P->G = (B + kGroupSamples - 1) / kGroupSamples;
+  P->mults.assign(dim_mults, dim_mults + n_mults);
+  cudaGetDevice(&P->device);
+  rc = build_unet(P, W);
+  if (rc) { dm_plan_free(P); return rc; }
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { dm_plan_free(P); return fail(DM_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); }
+  *plan = P;
+  return DM_OK;
+}
+
+extern "C" void dm_plan_free(dm_plan_t* P) {
+  if (!P) return;
+  if (P->graph_exec) cudaGraphExecDestroy(P->graph_exec);
+  for (void* p : P->allocs) cudaFree(p);
+  delete P;
+}
+
+extern "C" int dm_plan_set_schedule(dm_plan_t* P, const dm_schedule_t* s) {
+  if (!P || !s || s->n_timesteps < 1) return fail(DM_ERR_ARG, "bad schedule");
+  const int n = s->n_timesteps;
+  P->sr.assign(s->sqrt_recip_alphas_cumprod, s->sqrt_recip_alphas_cumprod + n);
+  P->srm1.assign(s->sqrt_recipm1_alphas_cumprod, s->sqrt_recipm1_alphas_cumprod + n);
+  P->c1.assign(s->posterior_mean_coef1, s->posterior_mean_coef1 + n);
+  P->c2.assign(s->posterior_mean_coef2, s->posterior_mean_coef2 + n);
+  P->logvar.assign(s->posterior_log_variance_clipped, s->posterior_log_variance_clipped + n);
+  P->n_timesteps = n;
+  P->graph_valid = false;
+  std::vector<float> tv(n);
+  for (int i = 0; i < n; ++i) tv[i] = (float)i;
+  int rc;
+  if ((rc = upload(P, tv, &P->t_table))) return rc;
+  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tb_table), (size_t)n * P->TB * sizeof(float)))) return rc;
+  DM_CUDA(launch_time_bias(P->tmlp, P->t_table, n, P->tb_table, 0));
+  DM_CUDA(cudaDeviceSynchronize());
+  return DM_OK;
+}
+
+extern "C" int dm_unet_forward(dm_plan_t* P, const float* x_dev, const float* t_dev, float* out_dev, dm_stream_t st) {
+  if (!P || !x_dev || !t_dev || !out_dev) return fail(DM_ERR_ARG, "null argument");
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  P->last_launches = 0;
+  const Act& xs = P->acts[P->xs_act];
+  DM_CUDA(launch_pack_input(x_dev, xs.p, xs.plane, xs.C, P->B, P->H, P->T, s));
+  DM_CUDA(launch_time_bias(P->tmlp, t_dev, P->B, P->tb_rows, s));
+  P->last_launches += 2;
+  return run_unet(P, P->tb_rows, P->TB, out_dev, s);
+}
+
+static int fill_step(dm_plan* P, StepParams* sp, float* x, const float* model_out, const float* noise,
+                     unsigned long long seed, int t, int pe, int clip, const dm_cond_t* cond) {
+  memset(sp, 0, sizeof(*sp));
+  const Act& xs = P->acts[P->xs_act];
+  sp->x = x;
+  sp->model_out = model_out;
+  sp->noise = noise;
+  sp->seed = seed;
+  sp->predict_epsilon = pe;
+  sp->clip_denoised = clip;
+  if (t >= 0) {
+    sp->mode = 0;
+    sp->add_noise = t > 0;   // noise[t == 0] = 0 (diffusion.py:25-26)
+    sp->sr = P->sr[t]; sp->srm1 = P->srm1[t]; sp->c1 = P->c1[t]; sp->c2 = P->c2[t];
+    sp->sigma = expf(0.5f * P->logvar[t]);
+  } else {
+    sp->mode = 1;
+  }
+  if (cond && cond->mask_dev) {
+    if (!cond->value_dev) return fail(DM_ERR_ARG, "conditioning mask without values");
+    sp->mask = cond->mask_dev;
+    sp->value = cond->value_dev;
+    sp->mask_bstride = cond->mask_batched ? (long long)P->H * P->T : 0;
+    sp->value_bstride = cond->value_batched ? (long long)P->H * P->T : 0;
+  }
+  sp->xs = xs.p;
+  sp->xs_plane_stride = xs.plane;
+  sp->xs_C = xs.C;
+  sp->B = P->B; sp->H = P->H; sp->T = P->T;
+  sp->n_elems = (long long)P->B * P->H * P->T;
+  if (sp->n_elems % 4) return fail(DM_ERR_ARG, "B*H*T must be a multiple of 4");
+  return DM_OK;
+}
+
+extern "C" int dm_ddpm_step(dm_plan_t* P, float* x_dev, const float* model_out_dev, const float* noise_dev,
+                            uint64_t seed, int t, int predict_epsilon, int clip_denoised, const dm_cond_t* cond,
+                            dm_stream_t st) {
+  if (!P || !x_dev || !model_out_dev) return fail(DM_ERR_ARG, "null argument");
+  if (P->n_timesteps == 0) return fail(DM_ERR_STATE, "dm_plan_set_schedule has not been called");
+  if (t < 0 || t >= P->n_timesteps) return fail(DM_ERR_ARG, "timestep %d out of range", t);
+  StepParams sp;
+  int rc = fill_step(P, &sp, x_dev, model_out_dev, noise_dev, seed, t, predict_epsilon, clip_denoised, cond);
+  if (rc) return rc;
+  sp.rng_stream = (unsigned)t + 1;
+  sp.rng_offset = P->rng_calls++ << 40;
+  DM_CUDA(launch_ddpm_step(sp, static_cast<cudaStream_t>(st)));
+  P->last_launches = 1;
+  return DM_OK;
+}
+
+static int enqueue_loop(dm_plan* P, float* x, int have_start, const float* noise_stack, unsigned long long seed,
+                        int timesteps, int pe, int clip, const dm_cond_t* cond, float* chain, cudaStream_t s) {
+  const long long n = (long long)P->B * P->H * P->T;
+  StepParams sp;
+  int rc = fill_step(P, &sp, x, nullptr, noise_stack, seed, -1, pe, clip, cond);
+  if (rc) return rc;
+  sp.have_start = have_start;
+  sp.rng_stream = 0;
+  sp.seed_ptr = P->seed_dev;
+  sp.chain = chain; sp.chain_len = timesteps + 1; sp.chain_slot = 0;
+  DM_CUDA(launch_ddpm_step(sp, s));
+  P->last_launches++;
+  int k = 1;
+  for (int i = timesteps - 1; i >= 0; --i, ++k) {
+    if ((rc = run_unet(P, P->tb_table + (size_t)i * P->TB, 0, P->model_out, s))) return rc;
+    if ((rc = fill_step(P, &sp, x, P->model_out, noise_stack ? noise_stack + (size_t)k * n : nullptr, seed, i, pe, clip,
+                        cond)))
+      return rc;
+    sp.rng_stream = (unsigned)k;
+    sp.seed_ptr = P->seed_dev;
+    sp.chain = chain; sp.chain_len = timesteps + 1; sp.chain_slot = k;
+    DM_CUDA(launch_ddpm_step(sp, s));
+    P->last_launches++;
+  }
+  return DM_OK;
+}
+
+extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const float* noise_stack_dev, uint64_t seed,
+                              int timesteps, int predict_epsilon, int clip_denoised, const dm_cond_t* cond,
+                              float* chain_dev, int use_graph, dm_stream_t st) {
+  if (!P || !x_dev) return fail(DM_ERR_ARG, "null argument");
+  if (P->n_timesteps == 0) return fail(DM_ERR_STATE, "dm_plan_set_schedule has not been called");
+  if (timesteps < 0 || timesteps > P->n_timesteps) return fail(DM_ERR_ARG, "timesteps %d out of range", timesteps);
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  P->last_launches = 0;
+  {
+    unsigned long long sd = seed;
+    DM_CUDA(cudaMemcpyAsync(P->seed_dev, &sd, sizeof(sd), cudaMemcpyHostToDevice, s));
+  }
+  if (!use_graph) return enqueue_loop(P, x_dev, have_start, noise_stack_dev, seed, timesteps, predict_epsilon,
+                                      clip_denoised, cond, chain_dev, s);
+  GraphKey key{x_dev, noise_stack_dev, chain_dev, cond ? (const void*)cond->mask_dev : nullptr,
+               cond ? (const void*)cond->value_dev : nullptr, have_start, timesteps, predict_epsilon,
+               clip_denoised, cond ? cond->mask_batched : 0, cond ? cond->value_batched : 0};
+  if (!(P->graph_valid && P->graph_key == key)) {
+    if (P->graph_exec) { cudaGraphExecDestroy(P->graph_exec); P->graph_exec = nullptr; }
+    P->graph_valid = false;
+    cudaStream_t cs;
+    DM_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+    if (e != cudaSuccess) { cudaStreamDestroy(cs); return fail(DM_ERR_CUDA, "begin capture: %s", cudaGetErrorString(e)); }
+    int rc = enqueue_loop(P, x_dev, have_start, noise_stack_dev, seed, timesteps, predict_epsilon, clip_denoised, cond,
+                          chain_dev, cs);
+    cudaGraph_t graph = nullptr;
+    e = cudaStreamEndCapture(cs, &graph);
+    cudaStreamDestroy(cs);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess) return fail(DM_ERR_CUDA, "end capture: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&P->graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return fail(DM_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
+    P->graph_key = key;
+    P->graph_valid = true;
+    P->graph_launches = P->last_launches;
+  }
+  P->last_launches = P->graph_launches;
+  DM_CUDA(cudaGraphLaunch(P->graph_exec, s));
+  return DM_OK;
+}
+
+extern "C" int dm_plan_num_layers(const dm_plan_t* P) { return P ? (int)P->layers.size() : 0; }
+
+extern "C" int dm_plan_layer_info(const dm_plan_t* P, int i, char* name, int name_cap, int* C, int* L) {
+  if (!P || i < 0 || i >= (int)P->layers.size()) return fail(DM_ERR_ARG, "layer index out of range");
+  const Layer& ly = P->layers[i];
+  if (name && name_cap > 0) snprintf(name, name_cap, "%s", ly.name.c_str());
+  if (C) *C = ly.out_act >= 0 ? ly.job.Cout : 0;
+  if (L) *L = ly.job.Lout;
+  return DM_OK;
+}
+
+extern "C" int dm_plan_read_layer(dm_plan_t* P, int i, float* out_dev, dm_stream_t st) {
+  if (!P || i < 0 || i >= (int)P->layers.size() || !out_dev) return fail(DM_ERR_ARG, "layer index out of range");
+  const Layer& ly = P->layers[i];
+  if (ly.out_act < 0) return fail(DM_ERR_ARG, "layer %d has no activation output", i);
+  const Act& a = P->acts[ly.out_act];
+  // unpack only the real channels: out is [B, Cout, L]
+  if (a.C != ly.job.Cout) return fail(DM_ERR_ARG, "layer %d output is channel padded", i);
+  DM_CUDA(launch_unpack_act(a.p, a.plane, a.C, a.L, P->B, out_dev, static_cast<cudaStream_t>(st)));
+  return DM_OK;
+}
+
+extern "C" int dm_plan_last_launch_count(const dm_plan_t* P) { return P ? P->last_launches : 0; }

@@ -1,0 +1,75 @@
+// Host-side plan: packed weights, activation workspace, TMA descriptors and the per-layer launch list of one
+// TemporalUnet (diffuser/models/temporal.py:49-165) at a fixed (B, H, T, dim, dim_mults).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "conv_job.h"
+#include "step_kernels.h"
+
+namespace dm {
+
+struct Act {
+  __half* p = nullptr;   // [2][G][L][16][C]
+  int C = 0, L = 0;
+  long long plane = 0;   // elements per plane
+};
+
+struct Layer {
+  ConvJob job;
+  int slices = 1;
+  size_t smem = 0;
+  int tb_off = -1;       // offset into a time-bias row, or -1
+  int out_act = -1;      // index into acts (for dm_plan_read_layer), -1 if fp32-only
+  std::string name;
+};
+
+struct HostTensor {
+  const float* data;
+  std::vector<int64_t> shape;
+};
+
+struct GraphKey {
+  const float* x;
+  const float* noise;
+  const float* chain;
+  const void* mask;
+  const void* value;
+  int have_start, timesteps, pe, clip, mb, vb;
+  bool operator==(const GraphKey& o) const {
+    return x == o.x && noise == o.noise && chain == o.chain && mask == o.mask && value == o.value &&
+           have_start == o.have_start && timesteps == o.timesteps && pe == o.pe && clip == o.clip && mb == o.mb &&
+           vb == o.vb;
+  }
+};
+
+}  // namespace dm
+
+struct dm_plan {
+  int B = 0, H = 0, T = 0, dim = 0, G = 0, device = 0;
+  std::vector<int> mults;
+  std::vector<void*> allocs;
+  std::vector<dm::Act> acts;
+  std::vector<dm::Layer> layers;
+  int xs_act = -1;
+  float* model_out = nullptr;      // fp32 [B,H,T] scratch for the sampling loop
+  dm::TimeMlpParams tmlp{};
+  int TB = 0;
+  float* tb_table = nullptr;       // [n_timesteps, TB]
+  float* tb_rows = nullptr;        // [G*16, TB] per-sample rows for dm_unet_forward
+  float* t_table = nullptr;        // [n_timesteps] 0..n-1
+  int n_timesteps = 0;
+  std::vector<float> sr, srm1, c1, c2, logvar;
+  int last_launches = 0;
+  unsigned long long rng_calls = 0;
+  unsigned long long* seed_dev = nullptr;
+  // one cached CUDA graph of the whole sampling loop
+  bool graph_valid = false;
+  dm::GraphKey graph_key{};
+  cudaGraphExec_t graph_exec = nullptr;
+  int graph_launches = 0;
+};

@@ -1,0 +1,51 @@
+// Host-visible parameter blocks and launchers for the elementwise kernels (K3, K4, layout helpers, K5, K6).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dm {
+
+struct TimeMlpParams {
+  int D;             // time embedding width (== unet dim)
+  int TB;            // total time-bias width: sum of Cout over all residual blocks
+  const float* w1;   // [4D, D]   time_mlp.1
+  const float* b1;   // [4D]
+  const float* w2;   // [D, 4D]   time_mlp.3
+  const float* b2;   // [D]
+  const float* wcat; // [TB, D]   every block's time_mlp.1, concatenated in block order
+  const float* bcat; // [TB]
+};
+
+struct StepParams {
+  int mode;            // 0 = denoise step, 1 = init (x = starting motion or noise; then inpaint)
+  float* x;            // [B,H,T] fp32, updated in place
+  const float* model_out;
+  const float* noise;  // injected noise [B,H,T] or null -> Philox(seed, offset)
+  unsigned long long seed, rng_offset;
+  const unsigned long long* seed_ptr;   // if set, overrides seed (lets one CUDA graph serve many seeds)
+  unsigned int rng_stream;
+  int add_noise;       // t > 0
+  int have_start;      // init mode: keep x (starting_motion) instead of drawing noise
+  int predict_epsilon, clip_denoised;
+  float sr, srm1, c1, c2, sigma;
+  const unsigned char* mask;   // [H*T] (bstride 0) or [B,H*T]; null = no conditioning
+  const float* value;
+  long long mask_bstride, value_bstride;
+  __half* xs;          // operand planes of the first conv: [2][G][H][16][xs_C]
+  long long xs_plane_stride;
+  int xs_C;
+  float* chain;        // [B, chain_len, H, T] or null
+  int chain_len, chain_slot;
+  int B, H, T;
+  long long n_elems;   // B*H*T (multiple of 4 because H % 8 == 0)
+};
+
+cudaError_t launch_time_bias(const TimeMlpParams& p, const float* t_dev, int nt, float* out, cudaStream_t s);
+cudaError_t launch_ddpm_step(const StepParams& p, cudaStream_t s);
+cudaError_t launch_pack_input(const float* x, __half* xs, long long plane_stride, int xs_C, int B, int H, int T,
+                              cudaStream_t s);
+cudaError_t launch_unpack_act(const __half* a, long long plane_stride, int C, int L, int B, float* out,
+                              cudaStream_t s);
+
+}  // namespace dm

@@ -1,0 +1,177 @@
+"""Drop-in for the reference's diffuser/models/temporal.py:49-165 (TemporalUnet).
+
+Same constructor signature, same parameter construction order (so a seeded default init gives the reference's
+weights) and the same state_dict keys/shapes (so reference checkpoints load); forward() runs the hand-written
+sm_100a kernels through libdm_b200.so.  The nn modules below only HOLD parameters -- none of them is ever
+called.  attention=True and a non-CUDA device are hard errors (no fallback).
+"""
+import ctypes
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+class _PosEmbSlot(nn.Module):
+    """Parameter-free stand-in for SinusoidalPosEmb (helpers.py:17-29) so time_mlp keeps indices 1 and 3."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.dim = dim
+
+
+class _ConvBlockParams(nn.Module):
+    """Parameters of Conv1dBlock (helpers.py:50-69): block.0 = Conv1d(k, pad k//2), block.2 = GroupNorm(8)."""
+
+    def __init__(self, cin, cout, k, n_groups=8):
+        super().__init__()
+        self.block = nn.Sequential(nn.Conv1d(cin, cout, k, padding=k // 2), nn.Identity(),
+                                   nn.GroupNorm(n_groups, cout), nn.Identity(), nn.Mish())
+
+
+class _ResBlockParams(nn.Module):
+    """Parameters of ResidualTemporalBlock (temporal.py:18-35)."""
+
+    def __init__(self, cin, cout, embed_dim, kernel_size=5):
+        super().__init__()
+        self.blocks = nn.ModuleList([_ConvBlockParams(cin, cout, kernel_size),
+                                     _ConvBlockParams(cout, cout, kernel_size)])
+        self.time_mlp = nn.Sequential(nn.Mish(), nn.Linear(embed_dim, cout), nn.Identity())
+        self.residual_conv = nn.Conv1d(cin, cout, 1) if cin != cout else nn.Identity()
+
+
+class _Resample(nn.Module):
+    def __init__(self, conv):
+        super().__init__()
+        self.conv = conv
+
+
+class UnetPlan:
+    """Owns one dm_plan_t (packed weights + workspace + launch list) for a fixed (B, H)."""
+
+    def __init__(self, state_dict, B, H, T, dim, dim_mults):
+        L = _lib.lib()
+        self._keep = []
+        entries = []
+        for k, v in state_dict.items():
+            t = v.detach().to("cpu", torch.float32).contiguous()
+            self._keep.append(t)
+            e = _lib.DmTensor()
+            e.name = k.encode()
+            e.data = t.data_ptr()
+            e.ndim = t.dim()
+            for i, s in enumerate(t.shape):
+                e.shape[i] = s
+            entries.append(e)
+        arr = (_lib.DmTensor * len(entries))(*entries)
+        mults = (ctypes.c_int * len(dim_mults))(*dim_mults)
+        h = ctypes.c_void_p()
+        _lib.check(L.dm_plan_create(arr, len(entries), B, H, T, dim, mults, len(dim_mults), ctypes.byref(h)))
+        self.handle = h
+        self.B, self.H, self.T = B, H, T
+        self._keep = []  # the plan copied everything it needs
+        self.schedule_id = None
+
+    def set_schedule(self, bufs, sched_id):
+        if self.schedule_id == sched_id:
+            return
+        keep = {k: bufs[k].detach().to("cpu", torch.float32).contiguous() for k in (
+            "sqrt_recip_alphas_cumprod", "sqrt_recipm1_alphas_cumprod", "posterior_mean_coef1",
+            "posterior_mean_coef2", "posterior_log_variance_clipped")}
+        s = _lib.DmSchedule()
+        s.n_timesteps = len(keep["posterior_mean_coef1"])
+        for k, v in keep.items():
+            setattr(s, k, v.data_ptr())
+        _lib.check(_lib.lib().dm_plan_set_schedule(self.handle, ctypes.byref(s)))
+        self.schedule_id = sched_id
+
+    def layer_names(self):
+        L = _lib.lib()
+        out = []
+        for i in range(L.dm_plan_num_layers(self.handle)):
+            buf = ctypes.create_string_buffer(128)
+            C, Ln = ctypes.c_int(), ctypes.c_int()
+            _lib.check(L.dm_plan_layer_info(self.handle, i, buf, 128, ctypes.byref(C), ctypes.byref(Ln)))
+            out.append((buf.value.decode(), C.value, Ln.value))
+        return out
+
+    def read_layer(self, i, C, Ln):
+        out = torch.empty(self.B, C, Ln, device="cuda", dtype=torch.float32)
+        _lib.check(_lib.lib().dm_plan_read_layer(self.handle, i, out.data_ptr(), _lib.stream_ptr()))
+        return out
+
+    def last_launch_count(self):
+        return _lib.lib().dm_plan_last_launch_count(self.handle)
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _lib.lib().dm_plan_free(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+class TemporalUnet(nn.Module):
+    def __init__(self, horizon, transition_dim, cond_dim, dim=32, dim_mults=(1, 2, 4, 8), attention=False):
+        super().__init__()
+        if attention:
+            raise NotImplementedError("attention=True (LinearAttention, helpers.py:110-131) is outside the hot path "
+                                      "(SURVEY.md 8(f) item 3); no fallback is provided")
+        dims = [transition_dim, *map(lambda m: dim * m, dim_mults)]
+        in_out = list(zip(dims[:-1], dims[1:]))
+        self.horizon, self.transition_dim, self.dim, self.dim_mults = horizon, transition_dim, dim, tuple(dim_mults)
+
+        self.time_mlp = nn.Sequential(_PosEmbSlot(dim), nn.Linear(dim, dim * 4), nn.Mish(), nn.Linear(dim * 4, dim))
+        self.downs = nn.ModuleList([])
+        self.ups = nn.ModuleList([])
+        n = len(in_out)
+        for ind, (cin, cout) in enumerate(in_out):
+            last = ind >= n - 1
+            self.downs.append(nn.ModuleList([
+                _ResBlockParams(cin, cout, dim), _ResBlockParams(cout, cout, dim), nn.Identity(),
+                _Resample(nn.Conv1d(cout, cout, 3, 2, 1)) if not last else nn.Identity()]))
+        mid = dims[-1]
+        self.mid_block1 = _ResBlockParams(mid, mid, dim)
+        self.mid_attn = nn.Identity()
+        self.mid_block2 = _ResBlockParams(mid, mid, dim)
+        for ind, (cin, cout) in enumerate(reversed(in_out[1:])):
+            self.ups.append(nn.ModuleList([
+                _ResBlockParams(cout * 2, cin, dim), _ResBlockParams(cin, cin, dim), nn.Identity(),
+                _Resample(nn.ConvTranspose1d(cin, cin, 4, 2, 1))]))
+        self.final_conv = nn.Sequential(_ConvBlockParams(dim, dim, 5), nn.Conv1d(dim, transition_dim, 1))
+        self._plans = {}
+
+    # ---- plan cache: rebuilt when the batch/horizon or the weights change ----
+    def _weights_version(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    def plan_for(self, B, H):
+        key = (B, H)
+        ver = self._weights_version()
+        hit = self._plans.get(key)
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        plan = UnetPlan(self.state_dict(), B, H, self.transition_dim, self.dim, self.dim_mults)
+        if len(self._plans) >= 4:
+            self._plans.pop(next(iter(self._plans)))
+        self._plans[key] = (ver, plan)
+        return plan
+
+    def forward(self, x, cond, time, verbose=False):
+        """x: [batch, horizon, transition] fp32 CUDA; time: [batch]; cond is ignored, as in the reference."""
+        if not x.is_cuda:
+            raise _lib.DmError("TemporalUnet.forward needs a CUDA tensor on a B200 (no CPU fallback)")
+        if x.dtype != torch.float32 or x.dim() != 3 or x.shape[2] != self.transition_dim:
+            raise _lib.DmError(f"expected fp32 [B, H, {self.transition_dim}], got {x.dtype} {tuple(x.shape)}")
+        x = x.contiguous()
+        B, H, _ = x.shape
+        plan = self.plan_for(B, H)
+        t = time.to(device=x.device, dtype=torch.float32).contiguous()
+        if t.numel() != B:
+            raise _lib.DmError("time must have one entry per sample")
+        out = torch.empty_like(x)
+        _lib.check(_lib.lib().dm_unet_forward(plan.handle, x.data_ptr(), t.data_ptr(), out.data_ptr(),
+                                              _lib.stream_ptr()))
+        return out

@@ -1,0 +1,99 @@
+"""Generates tests/golden/*.npz by IMPORTING THE UNMODIFIED REFERENCE from /root/reference/diffusion.
+Run in the build container only (the reference does not exist on the GPU box):
+    PYTHONDONTWRITEBYTECODE=1 python tests/golden/make_golden.py
+The fixtures pin oracle/diffusion_oracle.py (tests/test_oracle_golden.py), which in turn checks the CUDA path.
+"""
+import contextlib
+import io
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.dont_write_bytecode = True
+sys.path.insert(0, "/root/reference/diffusion")
+sys.path.insert(0, ROOT)
+
+with contextlib.redirect_stdout(io.StringIO()):
+    from diffuser.models.diffusion import GaussianDiffusion  # noqa: E402
+    from diffuser.models.temporal import TemporalUnet  # noqa: E402
+from oracle.diffusion_oracle import seeded_state_dict  # noqa: E402
+
+
+class InjectedNoise:
+    """sample_fn plug point (diffusion.py:193,214): default_sample_fn with the randn_like draw replaced by a
+    pre-generated tensor, so CUDA and reference consume identical noise."""
+
+    def __init__(self, stack):
+        self.stack, self.k = stack, 1
+
+    def __call__(self, model, x, cond, t):
+        mean, _, logv = model.p_mean_variance(x=x, cond=cond, t=t)
+        noise = self.stack[self.k].clone()
+        self.k += 1
+        noise[t == 0] = 0
+        return mean + torch.exp(0.5 * logv) * noise, torch.zeros(len(x))
+
+
+def box_holding(x):  # sampling_config.py:23-32
+    x[:, :, 13:16] = 0.0
+    x[:, :, 16] = 1.57
+    x[:, :, 17:20] = 0.0
+    x[:, :, 20] = 1.57
+    return x
+
+
+def run(name, B, H, n_steps, pe, clip, cond=None, start=False, max_t=None, seed=0):
+    with contextlib.redirect_stdout(io.StringIO()):
+        net = TemporalUnet(H, 35, 35)
+    sd = seeded_state_dict(H=H, seed=seed)
+    net.load_state_dict(sd)
+    diff = GaussianDiffusion(net, H, 35, n_timesteps=n_steps, predict_epsilon=pe, clip_denoised=clip).eval()
+    g = torch.Generator().manual_seed(1234 + seed)
+    steps = n_steps if max_t is None else max_t
+    stack = torch.randn(steps + 1, B, H, 35, generator=g)
+    kw = {}
+    if cond is not None:
+        kw["conditioning_fn"] = cond
+    if start:
+        kw["starting_motion"] = stack[0].clone() * 0.3 + 0.1
+    if max_t is not None:
+        kw["max_timesteps"] = max_t
+    torch.manual_seed(99)
+    if not start:
+        # the reference draws torch.randn(shape) itself (diffusion.py:205): make that draw equal stack[0]
+        torch.manual_seed(4321)
+        stack[0] = torch.randn(B, H, 35)
+        torch.manual_seed(4321)
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=InjectedNoise(stack), **kw)
+    chain = out.chains.numpy()
+    # one plain forward for the U-Net alone, non-uniform t
+    xf = torch.randn(B, H, 35, generator=g)
+    tf = torch.randint(0, n_steps, (B,), generator=g)
+    with torch.no_grad():
+        yf = net(xf, {}, tf)
+    ck = float(sum(v.double().sum() for v in sd.values()))
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), chain=chain, noise=stack.numpy(), fwd_x=xf.numpy(),
+                        fwd_t=tf.numpy(), fwd_y=yf.numpy(), weight_checksum=ck,
+                        start=(kw["starting_motion"].numpy() if start else np.zeros(0, np.float32)),
+                        meta=np.array([B, H, n_steps, int(pe), int(clip), int(cond is not None), int(start),
+                                       -1 if max_t is None else max_t, seed]))
+    print(name, chain.shape, "checksum", ck)
+
+
+if __name__ == "__main__":
+    run("unet_chain_plain", B=2, H=64, n_steps=8, pe=False, clip=False)
+    run("unet_chain_box_eps_clip", B=3, H=16, n_steps=12, pe=True, clip=True, cond=box_holding, seed=1)
+    run("unet_chain_start_maxt", B=2, H=24, n_steps=10, pe=False, clip=False, cond=box_holding, start=True, max_t=4,
+        seed=2)
+    # schedule buffers straight from the reference module
+    with contextlib.redirect_stdout(io.StringIO()):
+        net = TemporalUnet(8, 35, 35)
+    for n in (100, 1000):
+        d = GaussianDiffusion(net, 8, 35, n_timesteps=n)
+        np.savez_compressed(os.path.join(HERE, f"schedule_{n}.npz"),
+                            **{k: v.numpy() for k, v in d.state_dict().items() if not k.startswith("model.")})
+    print("done")
