@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(kConvThreads, 2) conv_gemm_kernel(const __grid
   __shared__ uint32_t tmem_slot;
   __shared__ float s_par[4][256];      // bias, gamma, beta, time-bias for this CTA's Nc channels
   __shared__ float s_stat[16][8][2];   // per (sample, group): sum, sum of squares
+  __shared__ float s_part[4][16][8][2]; // per-warp partials, combined in a fixed order (deterministic)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(kConvThreads, 2) conv_gemm_kernel(const __grid
       s_par[2][i] = gn ? job.beta[n0 + i] : 0.f;
       s_par[3][i] = (job.tbias && job.tbias_stride == 0) ? job.tbias[n0 + i] : 0.f;
     }
-    for (int i = tid; i < 16 * 8 * 2; i += 128) (&s_stat[0][0][0])[i] = 0.f;
+    for (int i = tid; i < 4 * 16 * 8 * 2; i += 128) (&s_part[0][0][0][0])[i] = 0.f;
     named_bar_sync(1, 128);
 
     mbar_wait(&acc_full, 0, 0x500);
@@ -188,11 +189,17 @@ __global__ void __launch_bounds__(kConvThreads, 2) conv_gemm_kernel(const __grid
             q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
           }
           if (lane < S) {
+            // runs of 4 channels that fall in the same group are added in increasing r: fixed order
             const int gi = (cc * 32 + r * 4) / job.cg;
-            atomicAdd(&s_stat[lane][gi][0], s[r]);
-            atomicAdd(&s_stat[lane][gi][1], q[r]);
+            s_part[warp][lane][gi][0] += s[r];
+            s_part[warp][lane][gi][1] += q[r];
           }
         }
+      }
+      named_bar_sync(1, 128);
+      for (int i = tid; i < 16 * 8 * 2; i += 128) {
+        const float* pp = &s_part[0][0][0][0];
+        (&s_stat[0][0][0])[i] = ((pp[i] + pp[256 + i]) + pp[512 + i]) + pp[768 + i];
       }
       named_bar_sync(1, 128);
     }

@@ -46,8 +46,6 @@ def trace_conditioning(fn, shape, device):
     if not torch.is_tensor(out) or tuple(out.shape) != tuple(shape):
         raise DmError("conditioning_fn must return a tensor of the input shape")
     mask = ~torch.isnan(out)
-    if not bool(mask.any()):
-        return None, None
     value = torch.where(mask, out, torch.zeros_like(out))
     g = torch.Generator(device="cpu").manual_seed(5)
     probe2 = torch.randn(shape, generator=g).to(device)
@@ -57,6 +55,8 @@ def trace_conditioning(fn, shape, device):
     if not ok:
         raise DmError("conditioning_fn is not an x-independent overwrite x = where(mask, value, x); it cannot be "
                       "fused into the sampling kernels (no fallback)")
+    if not bool(mask.any()):
+        return None, None
     if bool((mask == mask[:1]).all()):
         mask = mask[0]
     if bool((value == value[:1]).all()) and mask.dim() == 2:

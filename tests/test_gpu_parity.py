@@ -1,0 +1,245 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI, against the CPU
+oracle and the committed reference-generated fixtures.  Tolerances: <= 1e-3 relative per denoising step
+(north_star); conditioned channels bit-exact; FK <= 1e-5 m."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import diffusion_oracle as O  # noqa: E402
+from oracle import scoring_oracle as SO  # noqa: E402
+
+REL_STEP = 1e-3
+
+
+def rel(a, b):
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-12)).item()
+
+
+@pytest.fixture(scope="module")
+def dm():
+    import deepmimic_diffusion_mujoco_b200 as m
+    assert torch.cuda.is_available(), "GPU tests need a B200"
+    assert os.path.exists(m._lib.LIB_PATH), "libdm_b200.so missing: the CUDA path must be the one that runs"
+    return m
+
+
+def box_cond(H):
+    mask = torch.zeros(H, 35, dtype=torch.bool)
+    value = torch.zeros(H, 35)
+    mask[:, 13:21] = True
+    value[:, 16] = 1.57
+    value[:, 20] = 1.57
+    return mask, value
+
+
+def box_holding(x):
+    x[:, :, 13:16] = 0.0
+    x[:, :, 16] = 1.57
+    x[:, :, 17:20] = 0.0
+    x[:, :, 20] = 1.57
+    return x
+
+
+@pytest.mark.parametrize("B,H", [(3, 64), (17, 16), (1, 8), (2, 128), (16, 40)])
+def test_unet_layers_match_oracle(dm, B, H):
+    sd = O.seeded_state_dict(H=H, seed=B)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    g = torch.Generator().manual_seed(B * 100 + H)
+    x = torch.randn(B, H, 35, generator=g)
+    t = torch.randint(0, 100, (B,), generator=g)
+    rec = {}
+    y_ref = O.unet_forward(sd, x, t, record=rec)
+    y = net(x.cuda(), {}, t.cuda()).cpu()
+    plan = net.plan_for(B, H)
+    for i, (name, C, L) in enumerate(plan.layer_names()):
+        if C == 0:
+            continue
+        got = plan.read_layer(i, C, L).cpu()
+        assert rel(got, rec[name]) < 1e-4, (name, rel(got, rec[name]))
+    assert rel(y, y_ref) < 1e-4
+
+
+@pytest.mark.parametrize("name", ["unet_chain_plain", "unet_chain_box_eps_clip", "unet_chain_start_maxt"])
+def test_forward_matches_reference_fixture(dm, golden_dir, name):
+    z = np.load(os.path.join(golden_dir, name + ".npz"))
+    B, H, n_steps, pe, clip, cond, start, max_t, seed = [int(v) for v in z["meta"]]
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=seed))
+    y = net(torch.from_numpy(z["fwd_x"]).cuda(), {}, torch.from_numpy(z["fwd_t"]).cuda()).cpu()
+    assert rel(y, torch.from_numpy(z["fwd_y"])) < 1e-4
+
+
+@pytest.mark.parametrize("name", ["unet_chain_plain", "unet_chain_box_eps_clip", "unet_chain_start_maxt"])
+def test_chain_matches_reference_fixture(dm, golden_dir, name):
+    """Full p_sample_loop with injected noise against the chain recorded from the UNMODIFIED reference."""
+    z = np.load(os.path.join(golden_dir, name + ".npz"))
+    B, H, n_steps, pe, clip, cond, start, max_t, seed = [int(v) for v in z["meta"]]
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=seed))
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n_steps, predict_epsilon=bool(pe), clip_denoised=bool(clip)).cuda()
+    kw = {}
+    if cond:
+        kw["conditioning_fn"] = box_holding
+    if start:
+        kw["starting_motion"] = torch.from_numpy(z["start"])
+    if max_t >= 0:
+        kw["max_timesteps"] = max_t
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True,
+                             sample_fn=dm.InjectedNoise(torch.from_numpy(z["noise"])), **kw)
+    ref = torch.from_numpy(z["chain"])
+    chain = out.chains.cpu()
+    assert chain.shape == ref.shape
+    for k in range(ref.shape[1]):
+        assert rel(chain[:, k], ref[:, k]) < REL_STEP, (k, rel(chain[:, k], ref[:, k]))
+    assert torch.equal(out.trajectories.cpu(), chain[:, -1])
+    if cond:
+        m = box_cond(H)[0].expand(B, H, 35)
+        for k in range(ref.shape[1]):
+            assert torch.equal(chain[:, k][m], ref[:, k][m]), "conditioned channels must be bit-exact"
+
+
+def test_hundred_step_chain_vs_oracle(dm):
+    """100 steps, H=64, box-holding conditioning: free-running chain stays within 1e-3 of the fp32 oracle."""
+    B, H, n = 2, 64, 100
+    sd = O.seeded_state_dict(H=H, seed=5)
+    g = torch.Generator().manual_seed(77)
+    noise = torch.randn(n + 1, B, H, 35, generator=g)
+    mask, value = box_cond(H)
+    ref = O.p_sample_loop(sd, O.make_schedule(n), noise, mask=mask, value=value)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=dm.InjectedNoise(noise),
+                             conditioning_fn=box_holding)
+    chain = out.chains.cpu()
+    worst = max(rel(chain[:, k], ref[:, k]) for k in range(n + 1))
+    assert worst < REL_STEP, worst
+    m = mask.expand(B, H, 35)
+    assert torch.equal(chain[:, -1][m], ref[:, -1][m])
+
+
+def test_ddpm_step_kernel_matches_oracle(dm):
+    """K4 alone through dm_ddpm_step, both parameterisations, with clamp and a per-sample mask."""
+    import ctypes
+    from deepmimic_diffusion_mujoco_b200 import _lib
+    B, H, n = 5, 16, 50
+    sd = O.seeded_state_dict(H=H, seed=3)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n).cuda()
+    plan = net.plan_for(B, H)
+    plan.set_schedule(diff._schedule_bufs(), diff._schedule_id())
+    sched = O.make_schedule(n)
+    g = torch.Generator().manual_seed(9)
+    for pe, clip, t in [(0, 0, 30), (1, 1, 7), (1, 0, 0), (0, 1, 49)]:
+        x = torch.randn(B, H, 35, generator=g)
+        out = torch.randn(B, H, 35, generator=g)
+        z = torch.randn(B, H, 35, generator=g)
+        mask = torch.rand(B, H, 35, generator=g) < 0.2
+        value = torch.randn(B, H, 35, generator=g)
+        ref = O.apply_cond(O.ddpm_step(sched, x, out, z, t, bool(pe), bool(clip)), mask, value)
+        xd, od, zd = x.cuda(), out.cuda(), z.cuda()
+        md, vd = mask.to(torch.uint8).cuda().contiguous(), value.cuda()
+        c = _lib.DmCond(md.data_ptr(), vd.data_ptr(), 1, 1)
+        _lib.check(_lib.lib().dm_ddpm_step(plan.handle, xd.data_ptr(), od.data_ptr(), zd.data_ptr(), 0, t, pe, clip,
+                                           ctypes.byref(c), _lib.stream_ptr()))
+        got = xd.cpu()
+        assert rel(got, ref) < 1e-6
+        assert torch.equal(got[mask], value[mask])
+
+
+def test_philox_sampling_statistics_and_determinism(dm):
+    """Built-in sampler (in-kernel Philox noise, CUDA-graph replay): deterministic per seed, finite, conditioned
+    entries exact, different seeds differ."""
+    B, H = 32, 64
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=20, predict_epsilon=False).cuda()
+    a = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=11).trajectories.clone()
+    b = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=11).trajectories.clone()
+    c = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=12).trajectories.clone()
+    assert torch.isfinite(a).all()
+    assert torch.equal(a, b)
+    assert not torch.equal(a, c)
+    assert torch.equal(a[:, :, 16], torch.full((B, H), 1.57, device="cuda"))
+    assert torch.equal(a[:, :, 13:16], torch.zeros(B, H, 3, device="cuda"))
+    assert diff.last_launch_count > 20 * 40
+
+
+def test_initial_noise_is_standard_normal(dm):
+    B, H = 256, 64
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=10, predict_epsilon=False).cuda()
+    x = diff.p_sample_loop((B, H, 35), {}, verbose=False, max_timesteps=0, seed=3).trajectories
+    assert abs(x.mean().item()) < 0.01 and abs(x.std().item() - 1.0) < 0.01
+    k = ((x ** 4).mean() / (x ** 2).mean() ** 2).item()
+    assert abs(k - 3.0) < 0.1
+
+
+def test_fk_positions_and_reward(dm):
+    from deepmimic_diffusion_mujoco_b200 import scoring
+    g = np.random.default_rng(0)
+    N, H, dt = 6, 24, 1 / 60
+    ref = np.zeros((H, 35))
+    ref[:, 2] = 0.9
+    ref[:, 3] = 1.0
+    ref[:, 7:] = 0.3 * g.standard_normal((H, 28))
+    ref[:, 3:7] += 0.1 * g.standard_normal((H, 4))
+    qpos = ref[None] + 0.15 * g.standard_normal((N, H, 35))
+    qpos[0] = ref  # a perfect tracker: reward 1
+    out = scoring.fk_reward(torch.tensor(qpos, dtype=torch.float32).cuda(),
+                            torch.tensor(ref, dtype=torch.float32), dt, return_body_pos=True)
+    q32 = np.asarray(torch.tensor(qpos, dtype=torch.float32).numpy(), dtype=np.float64)
+    r32 = np.asarray(torch.tensor(ref, dtype=torch.float32).numpy(), dtype=np.float64)
+    bp = SO.body_positions(q32)
+    assert np.abs(out["body_pos"].cpu().numpy() - bp).max() < 1e-5
+    r, terms = SO.tracking_reward(q32, r32, dt)
+    got = out["reward"].cpu().numpy()
+    assert np.abs(got - r).max() < 2e-4
+    assert abs(got[0].mean() - 1.0) < 1e-5
+    s = out["sums"].cpu().numpy()
+    assert abs(s[0] - r.sum()) < 1e-2 and s[6] == N * H
+    assert np.allclose(s[2:6], terms.reshape(-1, 4).sum(0), atol=2e-2)
+
+
+def test_fid_moments_match_oracle(dm):
+    from deepmimic_diffusion_mujoco_b200 import scoring
+    g = torch.Generator().manual_seed(4)
+    N, H = 700, 8
+    data = torch.randn(N, H, 35, generator=g) * 0.3 + torch.randn(1, H, 35, generator=g)
+    fid = scoring.MotionFID()
+    mu, sigma = fid.calculate_activation_statistics(data.cuda())
+    mu_o, sig_o = SO.activation_statistics(data.numpy())
+    assert np.abs(mu - mu_o).max() < 1e-5
+    assert np.abs(sigma - sig_o).max() < 1e-4 * max(1.0, np.abs(sig_o).max())
+    other = data[: N // 2] * 1.1 + 0.05
+    mu2, sigma2 = fid.calculate_activation_statistics(other.cuda())
+    f = fid.calculate_fid(mu, sigma, mu2, sigma2)
+    f_o = SO.fid_from_statistics(*SO.activation_statistics(data.numpy()), *SO.activation_statistics(other.numpy()))
+    assert abs(f - f_o) < 2e-2 * max(1.0, abs(f_o))
+    # two halves of the same distribution: FID close to zero (test_motion_fid.py:106-124)
+    h1, h2 = data[::2], data[1::2]
+    f0 = fid.calculate_fid(*fid.calculate_activation_statistics(h1.cuda()), *fid.calculate_activation_statistics(h2.cuda()))
+    f0_o = SO.fid_from_statistics(*SO.activation_statistics(h1.numpy()), *SO.activation_statistics(h2.numpy()))
+    assert abs(f0 - f0_o) < 2e-2 * max(1.0, abs(f0_o))
+
+
+def test_errors_are_loud(dm):
+    net = dm.TemporalUnet(64, 35, 35)
+    with pytest.raises(dm.DmError):
+        net(torch.zeros(1, 64, 35), {}, torch.zeros(1))          # CPU tensor: no fallback
+    with pytest.raises(dm.DmError):
+        net(torch.zeros(1, 60, 35).cuda(), {}, torch.zeros(1).cuda())   # H % 8 != 0
+    with pytest.raises(NotImplementedError):
+        dm.TemporalUnet(64, 35, 35, attention=True)
+    diff = dm.GaussianDiffusion(net, 64, 35, n_timesteps=10).cuda()
+    with pytest.raises(dm.DmError):
+        diff.p_sample_loop((1, 64, 35), {}, verbose=False, conditioning_fn=lambda x: x * 0.5)
+    with pytest.raises(dm.DmError):
+        diff.p_sample_loop((1, 64, 35), {}, verbose=False, sample_fn=lambda *a: None)
