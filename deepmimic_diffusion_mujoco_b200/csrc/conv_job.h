@@ -16,7 +16,10 @@ namespace dm {
 
 constexpr int kGroupSamples = 16;   // samples per activation group: layout [plane][G][L][16][C] fp16
 constexpr int kMaxTaps = 5;
-constexpr int kConvThreads = 192;   // warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer
+constexpr int kEpiWarps = 16;       // epilogue warps 0-15: TMEM lane quarter = warp % 4, work slice = warp / 4
+constexpr int kProducerWarp = 16;   // one elected lane issues TMA
+constexpr int kMmaWarp = 17;        // one elected lane issues tcgen05.mma; the warp owns the TMEM allocation
+constexpr int kConvThreads = (kEpiWarps + 2) * 32;
 
 struct ConvTap {
   int wtap;    // index into the packed weight's tap dimension

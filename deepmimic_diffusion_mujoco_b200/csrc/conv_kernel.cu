@@ -1,17 +1,23 @@
 // K1 + K2: Conv1d-family implicit GEMM on tcgen05 (fp16 hi/lo split operands, fp32 accumulate in TMEM), TMA
 // fed, with the reference block's epilogue fused: bias -> GroupNorm(8) -> Mish -> + time bias -> + residual.
+// Two kernels share the device code below:
+//   conv_gemm_kernel    one launch per layer (dm_unet_forward: arbitrary per-sample timesteps, layer debugging)
+//   sample_loop_kernel  PERSISTENT: a 2-CTA cluster owns one 16-sample group and runs every layer of every
+//                       denoising step plus the fused DDPM update (K4) with only cluster-local barriers --
+//                       samples never interact, so the whole p_sample_loop is one launch.
 //
 // Data layout: activations are fp16 planes [plane][G][L][16][C] (plane 0 = hi, 1 = lo,
-// value = hi + lo).  A CTA owns S (8 or 16) samples of one group for ALL L positions, so its GEMM rows are
-// ordered (l, b): row = l * S + b.  A conv tap that reads position l + d is then the SAME shared-memory tile
-// viewed d * S rows further down -- a whole number of 8-row swizzle atoms -- so the five taps of a k=5 conv
-// are five UMMA descriptors over one TMA-loaded box (halo rows zero-filled by TMA out-of-bounds handling).
+// value = hi + lo).  A work unit owns S (8 or 16) samples of one group for ALL L positions, so its GEMM rows
+// are ordered (l, b): row = l * S + b.  A conv tap that reads position l + d is then the SAME shared-memory
+// tile viewed d * S rows further down -- a whole number of 8-row swizzle atoms -- so the five taps of a k=5
+// conv are five UMMA descriptors over one TMA-loaded box (halo rows zero-filled by TMA out-of-bounds handling).
 // The whole per-sample conv output lives in TMEM until GroupNorm statistics are known; no cross-CTA reduce.
 //
 // Reference: Conv1dBlock helpers.py:50-69; ResidualTemporalBlock temporal.py:37-46; Downsample1d/Upsample1d
-// helpers.py:32-47 (under /root/reference/diffusion/diffuser/models/).
+// helpers.py:32-47; p_sample_loop diffusion.py:186-228 (under /root/reference/diffusion/diffuser/models/).
 #include "conv_job.h"
 #include "ptx.cuh"
+#include "step_device.cuh"
 
 namespace dm {
 
@@ -27,286 +33,426 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-__global__ void __launch_bounds__(kConvThreads, 2) conv_gemm_kernel(const __grid_constant__ ConvJob job) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+constexpr int kEpiThreads = kEpiWarps * 32;
+
+struct ConvShared {
+  uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full;
+  uint32_t tmem_slot;
+  alignas(16) float par[4][256];                    // bias, gamma, beta, time bias of this unit's Nc channels
+  float stat[16][8][2];                 // per (sample, group): sum, sum of squares
+  float part[kEpiWarps][16][8][2];      // per-warp partials, combined in a fixed order (deterministic)
+};
+
+// Parity bookkeeping of the mbarrier rings.  Bit s of a mask = parity of the number of times stage s has been
+// used; producer and MMA issuer walk the same stage sequence, so their private copies stay in step even
+// though ring depths change from layer to layer inside the persistent kernel.
+struct RoleState {
+  uint32_t a_bits = 0, w_bits = 0, acc_count = 0;
+};
+
+__device__ __forceinline__ void init_shared(ConvShared& sh) {
+  for (int i = 0; i < 2; ++i) { mbar_init(&sh.a_full[i], 1); mbar_init(&sh.a_empty[i], 1); }
+  for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], 1); }
+  mbar_init(&sh.acc_full, 1);
+  fence_barrier_init();
+}
+
+// ================================ TMA producer (one thread) ================================
+__device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
+                                              int g, int b0, int n0, uint8_t* a_smem, uint8_t* w_smem, ConvShared& sh,
+                                              RoleState& rs) {
+  int as = 0, ws = 0;
+  for (int lt = 0; lt < job.n_ltiles; ++lt) {
+    const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
+    int cin_off = 0;
+    for (int src = 0; src < job.nsrc; ++src) {
+      for (int ch = 0; ch < job.src_chunks[src]; ++ch) {
+        mbar_wait(&sh.a_empty[as], ((rs.a_bits >> as) & 1) ^ 1, 0x100 + as);
+        mbar_arrive_expect_tx(&sh.a_full[as], job.a_tx_bytes);
+        tma_load_5d(a_smem + (size_t)as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
+        rs.a_bits ^= 1u << as;
+        for (int t = 0; t < job.ntaps; ++t) {
+          mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
+          mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
+          tma_load_4d(w_smem + (size_t)ws * job.w_stage_bytes, w_map, &sh.w_full[ws], cin_off + ch * job.Cc, n0,
+                      job.taps[t].wtap, 0);
+          rs.w_bits ^= 1u << ws;
+          if (++ws == job.n_w_stages) ws = 0;
+        }
+        if (++as == job.n_a_stages) as = 0;
+      }
+      cin_off += job.src_chunks[src] * job.Cc;
+    }
+  }
+}
+
+// ================================ MMA issuer (one thread) ==================================
+__device__ __forceinline__ void mma_unit(const ConvJob& job, uint8_t* a_smem, uint8_t* w_smem, ConvShared& sh,
+                                         uint32_t tmem_base, RoleState& rs) {
+  const int S = job.S, Nc = job.Nc;
+  const int MT = job.n_ltiles * job.Mt;
+  const uint32_t idesc = umma_idesc_f16(128, Nc);
+  const uint32_t sbo_a = job.l_stride * 8 * job.row_bytes;
+  const uint32_t sbo_w = 8 * job.row_bytes;
+  const int ksteps = job.Cc / 16;
+  const int pos_per_mt = 128 / S;
+  int as = 0, ws = 0;
+  for (int lt = 0; lt < job.n_ltiles; ++lt) {
+    int cidx = 0;
+    for (int src = 0; src < job.nsrc; ++src) {
+      for (int ch = 0; ch < job.src_chunks[src]; ++ch, ++cidx) {
+        mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
+        rs.a_bits ^= 1u << as;
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(a_smem + (size_t)as * job.a_stage_bytes);
+        for (int t = 0; t < job.ntaps; ++t) {
+          mbar_wait(&sh.w_full[ws], (rs.w_bits >> ws) & 1, 0x400 + ws);
+          rs.w_bits ^= 1u << ws;
+          tc_fence_after();
+          const uint32_t w_base = smem_u32(w_smem + (size_t)ws * job.w_stage_bytes);
+          const ConvTap tap = job.taps[t];
+          for (int mt = 0; mt < job.Mt; ++mt) {
+            const uint32_t d = tmem_base + (uint32_t)((tap.phase * MT + lt * job.Mt + mt) * Nc);
+            const uint32_t a_row = (uint32_t)((job.l_stride * mt * pos_per_mt + tap.shift) * S);
+            const uint32_t a_addr = a_base + a_row * job.row_bytes;
+            for (int k = 0; k < ksteps; ++k) {
+              const uint32_t acc = !(cidx == 0 && tap.first && k == 0);
+              const uint64_t a_hi = umma_smem_desc(a_addr + k * 32, sbo_a, job.swz);
+              const uint64_t a_lo = umma_smem_desc(a_addr + job.a_plane_bytes + k * 32, sbo_a, job.swz);
+              const uint64_t w_hi = umma_smem_desc(w_base + k * 32, sbo_w, job.swz);
+              const uint64_t w_lo = umma_smem_desc(w_base + job.w_plane_bytes + k * 32, sbo_w, job.swz);
+              umma_f16(d, a_lo, w_hi, idesc, acc);
+              umma_f16(d, a_hi, w_lo, idesc, 1);
+              umma_f16(d, a_hi, w_hi, idesc, 1);
+            }
+          }
+          umma_commit(&sh.w_empty[ws]);
+          if (++ws == job.n_w_stages) ws = 0;
+        }
+        umma_commit(&sh.a_empty[as]);
+        if (++as == job.n_a_stages) as = 0;
+      }
+    }
+  }
+  umma_commit(&sh.acc_full);
+}
+
+// ================================ epilogue (warps 0..15) ===================================
+// Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
+// u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
+__device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0, int n0, const float* tbias,
+                                              int tbias_stride, ConvShared& sh, uint32_t tmem_base, RoleState& rs) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tid = threadIdx.x;                 // 0..511
+  const int S = job.S, Nc = job.Nc;
+  const int MT = job.n_ltiles * job.Mt;
+  const int row = (warp & 3) * 32 + lane;      // row inside a 128-row tile == TMEM lane
+  const int slice = warp >> 2;
+  const int b = row & (S - 1);
+  const bool gn = job.epi == EPI_GN_MISH;
+  const bool tb_uniform = tbias != nullptr && tbias_stride == 0;
+
+  for (int i = tid; i < Nc; i += kEpiThreads) {
+    sh.par[0][i] = __ldg(job.bias + n0 + i);
+    sh.par[1][i] = gn ? __ldg(job.gamma + n0 + i) : 1.f;
+    sh.par[2][i] = gn ? __ldg(job.beta + n0 + i) : 0.f;
+    sh.par[3][i] = tb_uniform ? __ldg(tbias + n0 + i) : 0.f;
+  }
+  if (gn) {
+    float* pp = &sh.part[0][0][0][0];
+    for (int i = tid; i < kEpiWarps * 256; i += kEpiThreads) pp[i] = 0.f;
+  }
+  named_bar_sync(1, kEpiThreads);
+
+  mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x500);
+  rs.acc_count++;
+  tc_fence_after();
+  const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+  const int nchunks = Nc >> 5;
+  float v[32];
+
+  if (gn) {
+    // ---- pass 1: GroupNorm statistics over (channels of group) x (all L positions), per sample ----
+    const int units = MT * nchunks;
+    for (int u = slice; u < units; u += 4) {
+      const int T = u / nchunks, cc = u - T * nchunks;
+      const int j = (T * 128 + row) / S;
+      tmem_ld32(trow + (uint32_t)(T * Nc + cc * 32), v);
+      tmem_ld_wait();
+      float s[8], q[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cc * 32 + r * 4]);
+        const float x0 = v[r * 4] + bi.x, x1 = v[r * 4 + 1] + bi.y, x2 = v[r * 4 + 2] + bi.z, x3 = v[r * 4 + 3] + bi.w;
+        const bool ok = j < job.Lj;
+        s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
+        q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
+      }
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
+        q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
+        if (S == 8) {
+          s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
+          q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
+        }
+        if (lane < S) {
+          const int gi = (cc * 32 + r * 4) / job.cg;   // fixed (u, r) order per warp: deterministic
+          sh.part[warp][lane][gi][0] += s[r];
+          sh.part[warp][lane][gi][1] += q[r];
+        }
+      }
+    }
+    named_bar_sync(1, kEpiThreads);
+    if (tid < 256) {
+      const float* pp = &sh.part[0][0][0][0];
+      float a = 0.f;
+#pragma unroll
+      for (int w = 0; w < kEpiWarps; ++w) a += pp[w * 256 + tid];
+      (&sh.stat[0][0][0])[tid] = a;
+    }
+    named_bar_sync(1, kEpiThreads);
+  }
+
+  // ---- pass 2: normalise, Mish, + time bias, + residual, split to fp16 hi/lo, store ----
+  const float inv_n = 1.f / (float)(job.cg * job.Lj);
+  const int bg = g * kGroupSamples + b0 + b;
+  const int units2 = job.nphase * MT * nchunks;
+  for (int u = slice; u < units2; u += 4) {
+    const int ph = u / (MT * nchunks);
+    const int u1 = u - ph * MT * nchunks;
+    const int T = u1 / nchunks, cc = u1 - T * nchunks;
+    const int j = (T * 128 + row) / S;
+    tmem_ld32(trow + (uint32_t)((ph * MT + T) * Nc + cc * 32), v);
+    tmem_ld_wait();
+    if (j >= job.Lj) continue;
+    const int lrow = job.nphase == 2 ? 2 * j + ph : j;
+    const size_t rowoff = ((size_t)g * job.Lout + lrow) * kGroupSamples + b0 + b;
+    const int cb = cc * 32;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
+      float x[4] = {v[r * 4] + bi.x, v[r * 4 + 1] + bi.y, v[r * 4 + 2] + bi.z, v[r * 4 + 3] + bi.w};
+      if (gn) {
+        const int gi = (cb + r * 4) / job.cg;
+        const float mean = sh.stat[b][gi][0] * inv_n;
+        const float var = fmaxf(sh.stat[b][gi][1] * inv_n - mean * mean, 0.f);
+        const float rstd = rsqrtf(var + 1e-5f);
+        const float4 ga = *reinterpret_cast<const float4*>(&sh.par[1][cb + r * 4]);
+        const float4 be = *reinterpret_cast<const float4*>(&sh.par[2][cb + r * 4]);
+        const float4 tb = *reinterpret_cast<const float4*>(&sh.par[3][cb + r * 4]);
+        x[0] = mish_f(fmaf((x[0] - mean) * rstd, ga.x, be.x)) + tb.x;
+        x[1] = mish_f(fmaf((x[1] - mean) * rstd, ga.y, be.y)) + tb.y;
+        x[2] = mish_f(fmaf((x[2] - mean) * rstd, ga.z, be.z)) + tb.z;
+        x[3] = mish_f(fmaf((x[3] - mean) * rstd, ga.w, be.w)) + tb.w;
+      }
+      v[r * 4] = x[0]; v[r * 4 + 1] = x[1]; v[r * 4 + 2] = x[2]; v[r * 4 + 3] = x[3];
+    }
+    if (gn && tbias != nullptr && tbias_stride != 0) {
+      const float4* tb = reinterpret_cast<const float4*>(tbias + (size_t)bg * tbias_stride + n0 + cb);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float4 t4 = __ldg(tb + e);
+        v[e * 4] += t4.x; v[e * 4 + 1] += t4.y; v[e * 4 + 2] += t4.z; v[e * 4 + 3] += t4.w;
+      }
+    }
+    if (job.res) {
+      // L2-coherent loads: inside the persistent kernel this data was written by another SM moments ago
+      const uint4* rh = reinterpret_cast<const uint4*>(job.res + rowoff * job.res_C + n0 + cb);
+      const uint4* rl = reinterpret_cast<const uint4*>(job.res + job.res_plane_stride + rowoff * job.res_C + n0 + cb);
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        const uint4 hv = __ldcg(rh + q4), lv = __ldcg(rl + q4);
+        const __half2* hh = reinterpret_cast<const __half2*>(&hv);
+        const __half2* ll = reinterpret_cast<const __half2*>(&lv);
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
+          v[q4 * 8 + w * 2] += fh.x + fl.x;
+          v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
+        }
+      }
+    }
+    if (job.out) {
+      uint4* oh = reinterpret_cast<uint4*>(job.out + rowoff * job.out_C + n0 + cb);
+      uint4* ol = reinterpret_cast<uint4*>(job.out + job.out_plane_stride + rowoff * job.out_C + n0 + cb);
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        uint4 hv, lv;
+        __half2* hh = reinterpret_cast<__half2*>(&hv);
+        __half2* ll = reinterpret_cast<__half2*>(&lv);
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          __half h0, l0, h1, l1;
+          split_half(v[q4 * 8 + w * 2], h0, l0);
+          split_half(v[q4 * 8 + w * 2 + 1], h1, l1);
+          hh[w] = __halves2half2(h0, h1);
+          ll[w] = __halves2half2(l0, l1);
+        }
+        oh[q4] = hv;
+        ol[q4] = lv;
+      }
+    }
+    if (job.out_f32 && bg < job.B) {
+      float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        const int c = n0 + cb + e;
+        if (c < job.Cout) of[c] = v[e];
+      }
+    }
+  }
+}
+
+// One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
+__device__ __forceinline__ void run_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map, int g,
+                                         int b0, int n0, const float* tbias, int tbias_stride, uint8_t* smem,
+                                         ConvShared& sh, uint32_t tmem_base, RoleState& rs) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* a_smem = smem;
   uint8_t* w_smem = smem + (size_t)job.n_a_stages * job.a_stage_bytes;
-
-  __shared__ uint64_t a_full[4], a_empty[4], w_full[8], w_empty[8], acc_full;
-  __shared__ uint32_t tmem_slot;
-  __shared__ float s_par[4][256];      // bias, gamma, beta, time-bias for this CTA's Nc channels
-  __shared__ float s_stat[16][8][2];   // per (sample, group): sum, sum of squares
-  __shared__ float s_part[4][16][8][2]; // per-warp partials, combined in a fixed order (deterministic)
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  const int S = job.S;
-  const int subs = kGroupSamples / S;
-  const int g = blockIdx.x / subs;
-  const int b0 = (blockIdx.x % subs) * S;
-  const int n0 = blockIdx.y * job.Nc;
-  const int Nc = job.Nc;
-  const int MT = job.n_ltiles * job.Mt;
-
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < job.n_a_stages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < job.n_w_stages; ++i) { mbar_init(&w_full[i], 1); mbar_init(&w_empty[i], 1); }
-    mbar_init(&acc_full, 1);
-    fence_barrier_init();
+  if (warp == kProducerWarp) {
+    if (lane == 0) producer_unit(job, a_maps, w_map, g, b0, n0, a_smem, w_smem, sh, rs);
+    __syncwarp();
+  } else if (warp == kMmaWarp) {
+    if (lane == 0) mma_unit(job, a_smem, w_smem, sh, tmem_base, rs);
+    __syncwarp();
+  } else {
+    epilogue_unit(job, g, b0, n0, tbias, tbias_stride, sh, tmem_base, rs);
   }
-  if (warp == 4 && lane == 0) {
+}
+
+__device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
+  return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-layer launch: grid = (groups * 16/S, N slices)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kConvThreads, 1) conv_gemm_kernel(const __grid_constant__ ConvJob job) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
+  __shared__ ConvShared sh;
+  const int warp = threadIdx.x >> 5;
+  const int subs = kGroupSamples / job.S;
+  if (threadIdx.x == 0) init_shared(sh);
+  if (warp == kProducerWarp && (threadIdx.x & 31) == 0) {
     tma_prefetch_desc(&job.a_map[0]);
     if (job.nsrc > 1) tma_prefetch_desc(&job.a_map[1]);
     tma_prefetch_desc(&job.w_map);
   }
-  if (warp == 5) tmem_alloc(&tmem_slot, job.tmem_cols);
+  if (warp == kMmaWarp) tmem_alloc(&sh.tmem_slot, job.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
-
-  if (warp == 4) {
-    // ================================ TMA producer ================================
-    if (lane == 0) {
-      int as = 0, aph = 0, ws = 0, wph = 0;
-      for (int lt = 0; lt < job.n_ltiles; ++lt) {
-        const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
-        int cin_off = 0;
-        for (int src = 0; src < job.nsrc; ++src) {
-          for (int ch = 0; ch < job.src_chunks[src]; ++ch) {
-            mbar_wait(&a_empty[as], aph ^ 1, 0x100 + as);
-            mbar_arrive_expect_tx(&a_full[as], job.a_tx_bytes);
-            tma_load_5d(a_smem + (size_t)as * job.a_stage_bytes, &job.a_map[src], &a_full[as], ch * job.Cc, b0,
-                        lstart, g, 0);
-            for (int t = 0; t < job.ntaps; ++t) {
-              mbar_wait(&w_empty[ws], wph ^ 1, 0x200 + ws);
-              mbar_arrive_expect_tx(&w_full[ws], job.w_tx_bytes);
-              tma_load_4d(w_smem + (size_t)ws * job.w_stage_bytes, &job.w_map, &w_full[ws],
-                          cin_off + ch * job.Cc, n0, job.taps[t].wtap, 0);
-              if (++ws == job.n_w_stages) { ws = 0; wph ^= 1; }
-            }
-            if (++as == job.n_a_stages) { as = 0; aph ^= 1; }
-          }
-          cin_off += job.src_chunks[src] * job.Cc;
-        }
-      }
-    }
-  } else if (warp == 5) {
-    // ================================ MMA issuer ==================================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_f16(128, Nc);
-      const uint32_t sbo_a = job.l_stride * 8 * job.row_bytes;
-      const uint32_t sbo_w = 8 * job.row_bytes;
-      const int ksteps = job.Cc / 16;
-      const int rows_per_mt = 128 / S;  // M positions per 128-row tile
-      int as = 0, aph = 0, ws = 0, wph = 0;
-      for (int lt = 0; lt < job.n_ltiles; ++lt) {
-        int cidx = 0;
-        for (int src = 0; src < job.nsrc; ++src) {
-          for (int ch = 0; ch < job.src_chunks[src]; ++ch, ++cidx) {
-            mbar_wait(&a_full[as], aph, 0x300 + as);
-            tc_fence_after();
-            const uint32_t a_base = smem_u32(a_smem + (size_t)as * job.a_stage_bytes);
-            for (int t = 0; t < job.ntaps; ++t) {
-              mbar_wait(&w_full[ws], wph, 0x400 + ws);
-              tc_fence_after();
-              const uint32_t w_base = smem_u32(w_smem + (size_t)ws * job.w_stage_bytes);
-              const ConvTap tap = job.taps[t];
-              for (int mt = 0; mt < job.Mt; ++mt) {
-                const uint32_t d = tmem_base + (uint32_t)((tap.phase * MT + lt * job.Mt + mt) * Nc);
-                const uint32_t a_row = (uint32_t)((job.l_stride * mt * rows_per_mt + tap.shift) * S);
-                const uint32_t a_addr = a_base + a_row * job.row_bytes;
-                for (int k = 0; k < ksteps; ++k) {
-                  const uint32_t acc = !(cidx == 0 && tap.first && k == 0);
-                  const uint64_t a_hi = umma_smem_desc(a_addr + k * 32, sbo_a, job.swz);
-                  const uint64_t a_lo = umma_smem_desc(a_addr + job.a_plane_bytes + k * 32, sbo_a, job.swz);
-                  const uint64_t w_hi = umma_smem_desc(w_base + k * 32, sbo_w, job.swz);
-                  const uint64_t w_lo = umma_smem_desc(w_base + job.w_plane_bytes + k * 32, sbo_w, job.swz);
-                  umma_f16(d, a_lo, w_hi, idesc, acc);
-                  umma_f16(d, a_hi, w_lo, idesc, 1);
-                  umma_f16(d, a_hi, w_hi, idesc, 1);
-                }
-              }
-              umma_commit(&w_empty[ws]);
-              if (++ws == job.n_w_stages) { ws = 0; wph ^= 1; }
-            }
-            umma_commit(&a_empty[as]);
-            if (++as == job.n_a_stages) { as = 0; aph ^= 1; }
-          }
-        }
-      }
-      umma_commit(&acc_full);
-    }
-  } else {
-    // ================================ epilogue (warps 0-3) =========================
-    const int tid = threadIdx.x;       // 0..127 == TMEM lane
-    const int b = tid & (S - 1);
-    const bool gn = job.epi == EPI_GN_MISH;
-    for (int i = tid; i < Nc; i += 128) {
-      s_par[0][i] = job.bias[n0 + i];
-      s_par[1][i] = gn ? job.gamma[n0 + i] : 1.f;
-      s_par[2][i] = gn ? job.beta[n0 + i] : 0.f;
-      s_par[3][i] = (job.tbias && job.tbias_stride == 0) ? job.tbias[n0 + i] : 0.f;
-    }
-    for (int i = tid; i < 4 * 16 * 8 * 2; i += 128) (&s_part[0][0][0][0])[i] = 0.f;
-    named_bar_sync(1, 128);
-
-    mbar_wait(&acc_full, 0, 0x500);
-    tc_fence_after();
-    const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
-    const int nchunks = Nc >> 5;
-    float v[32];
-
-    if (gn) {
-      // ---- pass 1: GroupNorm statistics over (channels of group) x (all L positions), per sample ----
-      for (int cc = 0; cc < nchunks; ++cc) {
-        float s[8], q[8];
-#pragma unroll
-        for (int r = 0; r < 8; ++r) { s[r] = 0.f; q[r] = 0.f; }
-        for (int T = 0; T < MT; ++T) {
-          const int j = (T * 128 + tid) / S;
-          tmem_ld32(trow + (uint32_t)(T * Nc + cc * 32), v);
-          tmem_ld_wait();
-          if (j < job.Lj) {
-#pragma unroll
-            for (int r = 0; r < 8; ++r) {
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float x = v[r * 4 + e] + s_par[0][cc * 32 + r * 4 + e];
-                s[r] += x;
-                q[r] = fmaf(x, x, q[r]);
-              }
-            }
-          }
-        }
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
-          q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
-          if (S == 8) {
-            s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
-            q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
-          }
-          if (lane < S) {
-            // runs of 4 channels that fall in the same group are added in increasing r: fixed order
-            const int gi = (cc * 32 + r * 4) / job.cg;
-            s_part[warp][lane][gi][0] += s[r];
-            s_part[warp][lane][gi][1] += q[r];
-          }
-        }
-      }
-      named_bar_sync(1, 128);
-      for (int i = tid; i < 16 * 8 * 2; i += 128) {
-        const float* pp = &s_part[0][0][0][0];
-        (&s_stat[0][0][0])[i] = ((pp[i] + pp[256 + i]) + pp[512 + i]) + pp[768 + i];
-      }
-      named_bar_sync(1, 128);
-    }
-
-    // ---- pass 2: normalise, Mish, + time bias, + residual, split to fp16 hi/lo, store ----
-    const float inv_n = 1.f / (float)(job.cg * job.Lj);
-    const int bg = g * kGroupSamples + b0 + b;
-    for (int T = 0; T < MT; ++T) {
-      const int j = (T * 128 + tid) / S;
-      const bool valid = j < job.Lj;
-      for (int ph = 0; ph < job.nphase; ++ph) {
-        const int lrow = job.nphase == 2 ? 2 * j + ph : j;
-        const size_t rowoff = ((size_t)g * job.Lout + lrow) * kGroupSamples + b0 + b;
-        for (int cc = 0; cc < nchunks; ++cc) {
-          tmem_ld32(trow + (uint32_t)((ph * MT + T) * Nc + cc * 32), v);
-          tmem_ld_wait();
-          if (!valid) continue;
-          const int cb = cc * 32;
-#pragma unroll
-          for (int r = 0; r < 8; ++r) {
-            float mean = 0.f, rstd = 1.f;
-            if (gn) {
-              const int gi = (cb + r * 4) / job.cg;
-              mean = s_stat[b][gi][0] * inv_n;
-              const float var = fmaxf(s_stat[b][gi][1] * inv_n - mean * mean, 0.f);
-              rstd = rsqrtf(var + 1e-5f);
-            }
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int c = cb + r * 4 + e;
-              float x = v[r * 4 + e] + s_par[0][c];
-              if (gn) {
-                x = (x - mean) * rstd * s_par[1][c] + s_par[2][c];
-                x = mish_f(x);
-                x += s_par[3][c];
-              }
-              v[r * 4 + e] = x;
-            }
-          }
-          if (gn && job.tbias && job.tbias_stride != 0) {
-            const float* tb = job.tbias + (size_t)bg * job.tbias_stride + n0 + cb;
-#pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] += __ldg(tb + e);
-          }
-          if (job.res) {
-            const uint4* rh = reinterpret_cast<const uint4*>(job.res + rowoff * job.res_C + n0 + cb);
-            const uint4* rl = reinterpret_cast<const uint4*>(job.res + job.res_plane_stride + rowoff * job.res_C + n0 + cb);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const uint4 hv = __ldg(rh + u), lv = __ldg(rl + u);
-              const __half2* hh = reinterpret_cast<const __half2*>(&hv);
-              const __half2* ll = reinterpret_cast<const __half2*>(&lv);
-#pragma unroll
-              for (int w = 0; w < 4; ++w) {
-                const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
-                v[u * 8 + w * 2] += fh.x + fl.x;
-                v[u * 8 + w * 2 + 1] += fh.y + fl.y;
-              }
-            }
-          }
-          if (job.out) {
-            uint4* oh = reinterpret_cast<uint4*>(job.out + rowoff * job.out_C + n0 + cb);
-            uint4* ol = reinterpret_cast<uint4*>(job.out + job.out_plane_stride + rowoff * job.out_C + n0 + cb);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              uint4 hv, lv;
-              __half2* hh = reinterpret_cast<__half2*>(&hv);
-              __half2* ll = reinterpret_cast<__half2*>(&lv);
-#pragma unroll
-              for (int w = 0; w < 4; ++w) {
-                __half h0, l0, h1, l1;
-                split_half(v[u * 8 + w * 2], h0, l0);
-                split_half(v[u * 8 + w * 2 + 1], h1, l1);
-                hh[w] = __halves2half2(h0, h1);
-                ll[w] = __halves2half2(l0, l1);
-              }
-              oh[u] = hv;
-              ol[u] = lv;
-            }
-          }
-          if (job.out_f32 && bg < job.B) {
-            float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const int c = n0 + cb + e;
-              if (c < job.Cout) of[c] = v[e];
-            }
-          }
-        }
-      }
-    }
-  }
-
+  const uint32_t tmem_base = sh.tmem_slot;
+  RoleState rs;
+  run_unit(job, &job.a_map[0], &job.w_map, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
+           job.tbias, job.tbias_stride, smem, sh, tmem_base, rs);
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem_base, job.tmem_cols);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, job.tmem_cols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// persistent sampling loop: cluster c of 2 CTAs owns samples [16c, 16c+16)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void job_sync(bool wrote_global) {
+  if (wrote_global) fence_proxy_async_all();   // generic-proxy stores -> visible to later TMA (async proxy) loads
+  tc_fence_before();
+  __syncwarp();
+  cluster_sync_all();
+  tc_fence_after();
+  fence_proxy_async_all();
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
+sample_loop_kernel(const __grid_constant__ LoopParams lp) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem(smem_raw);
+  __shared__ ConvShared sh;
+  __shared__ ConvJob sjob;
+  __shared__ StepParams sstep;
+  const int warp = threadIdx.x >> 5;
+  const int rank = (int)cluster_ctarank();
+  const int g = (int)cluster_id_x();
+  if (threadIdx.x == 0) init_shared(sh);
+  if (warp == kMmaWarp) tmem_alloc(&sh.tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sh.tmem_slot;
+  RoleState rs;
+
+  const long long ht4 = ((long long)lp.H * lp.T) >> 2;           // float4 per sample
+  const int s_lo = g * kGroupSamples + rank * 8;
+  const int s_hi = min(lp.B, s_lo + 8);
+
+  for (int k = 0; k <= lp.n_steps; ++k) {
+    if (k > 0) {
+      const int t_index = lp.steps[k].t_index;
+      for (int ji = 0; ji < lp.n_jobs; ++ji) {
+        {  // stage the layer descriptor in shared memory
+          const uint32_t* src = reinterpret_cast<const uint32_t*>(lp.jobs + ji);
+          uint32_t* dst = reinterpret_cast<uint32_t*>(&sjob);
+          for (int i = threadIdx.x; i < (int)(sizeof(ConvJob) / 4); i += kConvThreads) dst[i] = __ldg(src + i);
+        }
+        __syncthreads();
+        const ConvJob& job = sjob;
+        const int slices = lp.slices[ji];
+        const int off = lp.tb_off[ji];
+        const float* tb = off >= 0 ? lp.tb_table + (size_t)t_index * lp.TB + off : nullptr;
+        const CUtensorMap* a_maps = &lp.jobs[ji].a_map[0];
+        const CUtensorMap* w_map = &lp.jobs[ji].w_map;
+        const int first = job.S == 8 ? 0 : rank, stride = job.S == 8 ? 1 : 2;
+        const int b0 = job.S == 8 ? rank * 8 : 0;
+        for (int sl = first; sl < slices; sl += stride) {
+          run_unit(job, a_maps, w_map, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs);
+          if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit
+            tc_fence_before();
+            __syncthreads();
+            tc_fence_after();
+          }
+        }
+        job_sync(warp < kEpiWarps);
+      }
+    }
+    // ---- K4: init (k == 0) or fused posterior + noise + inpaint + operand re-pack for this CTA's samples ----
+    {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(lp.steps + k);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(&sstep);
+      for (int i = threadIdx.x; i < (int)(sizeof(StepParams) / 4); i += kConvThreads) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    if (warp < kEpiWarps && s_hi > s_lo)
+      ddpm_step_range<true>(sstep, s_lo * ht4, s_hi * ht4, threadIdx.x, kEpiThreads);
+    job_sync(warp < kEpiWarps);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 }
 
 cudaError_t launch_conv_job(const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   dim3 grid(n_groups * (kGroupSamples / job.S), n_slices);
   conv_gemm_kernel<<<grid, kConvThreads, smem_bytes, stream>>>(job);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(sample_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  sample_loop_kernel<<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
   return cudaGetLastError();
 }
 

@@ -203,6 +203,8 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (gn && (sp.Cout % 32 != 0)) return fail(DM_ERR_ARG, "%s: GroupNorm layers need Cout %% 32 == 0", sp.name.c_str());
   int Nc = cout_pad < 128 ? cout_pad : 128;
   while (cout_pad % Nc) Nc -= 32;
+  // 16-sample units are split over the two CTAs of a cluster by N slice: prefer an even slice count
+  if (j.S == 16 && (cout_pad / Nc) % 2 == 1 && Nc % 64 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
   const int mt_all = j.n_ltiles * j.Mt;
   while (j.nphase * mt_all * Nc > 512 && Nc > 32 && (Nc / 2) % 32 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
   if (j.nphase * mt_all * Nc > 512)
@@ -512,6 +514,24 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
   if ((rc = upload(P, bcat, &dbc))) return rc;
   P->tmlp = TimeMlpParams{D, P->TB, dw1, db1, dw2, db2, dwc, dbc};
   if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->seed_dev), sizeof(unsigned long long)))) return rc;
+  {
+    const int n = (int)P->layers.size();
+    std::vector<ConvJob> jobs(n);
+    std::vector<int> slices(n), tboff(n);
+    P->loop_smem = 0;
+    for (int i = 0; i < n; ++i) {
+      jobs[i] = P->layers[i].job;
+      slices[i] = P->layers[i].slices;
+      tboff[i] = P->layers[i].tb_off;
+      if (P->layers[i].smem > P->loop_smem) P->loop_smem = P->layers[i].smem;
+    }
+    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->jobs_dev), n * sizeof(ConvJob), false))) return rc;
+    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->slices_dev), n * sizeof(int), false))) return rc;
+    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tboff_dev), n * sizeof(int), false))) return rc;
+    DM_CUDA(cudaMemcpy(P->jobs_dev, jobs.data(), n * sizeof(ConvJob), cudaMemcpyHostToDevice));
+    DM_CUDA(cudaMemcpy(P->slices_dev, slices.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+    DM_CUDA(cudaMemcpy(P->tboff_dev, tboff.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+  }
   if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tb_rows), (size_t)P->G * kGroupSamples * P->TB * sizeof(float))))
     return rc;
   return DM_OK;
@@ -574,6 +594,7 @@ extern "C" int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, 
   P->G = (B + kGroupSamples - 1) / kGroupSamples;
   P->mults.assign(dim_mults, dim_mults + n_mults);
   cudaGetDevice(&P->device);
+  if (cudaEventCreateWithFlags(&P->steps_event, cudaEventDisableTiming) != cudaSuccess) { delete P; return fail(DM_ERR_CUDA, "event create failed"); }
   rc = build_unet(P, W);
   if (rc) { dm_plan_free(P); return rc; }
   cudaError_t e = cudaDeviceSynchronize();
@@ -584,7 +605,8 @@ extern "C" int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, 
 
 extern "C" void dm_plan_free(dm_plan_t* P) {
   if (!P) return;
-  if (P->graph_exec) cudaGraphExecDestroy(P->graph_exec);
+  if (P->steps_host) cudaFreeHost(P->steps_host);
+  if (P->steps_event) cudaEventDestroy(P->steps_event);
   for (void* p : P->allocs) cudaFree(p);
   delete P;
 }
@@ -598,12 +620,14 @@ extern "C" int dm_plan_set_schedule(dm_plan_t* P, const dm_schedule_t* s) {
   P->c2.assign(s->posterior_mean_coef2, s->posterior_mean_coef2 + n);
   P->logvar.assign(s->posterior_log_variance_clipped, s->posterior_log_variance_clipped + n);
   P->n_timesteps = n;
-  P->graph_valid = false;
   std::vector<float> tv(n);
   for (int i = 0; i < n; ++i) tv[i] = (float)i;
   int rc;
   if ((rc = upload(P, tv, &P->t_table))) return rc;
   if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tb_table), (size_t)n * P->TB * sizeof(float)))) return rc;
+  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->steps_dev), (size_t)(n + 1) * sizeof(StepParams)))) return rc;
+  if (P->steps_host) cudaFreeHost(P->steps_host);
+  DM_CUDA(cudaMallocHost(reinterpret_cast<void**>(&P->steps_host), (size_t)(n + 1) * sizeof(StepParams)));
   DM_CUDA(launch_time_bias(P->tmlp, P->t_table, n, P->tb_table, 0));
   DM_CUDA(cudaDeviceSynchronize());
   return DM_OK;
@@ -632,6 +656,7 @@ static int fill_step(dm_plan* P, StepParams* sp, float* x, const float* model_ou
   sp->clip_denoised = clip;
   if (t >= 0) {
     sp->mode = 0;
+    sp->t_index = t;
     sp->add_noise = t > 0;   // noise[t == 0] = 0 (diffusion.py:25-26)
     sp->sr = P->sr[t]; sp->srm1 = P->srm1[t]; sp->c1 = P->c1[t]; sp->c2 = P->c2[t];
     sp->sigma = expf(0.5f * P->logvar[t]);
@@ -699,44 +724,47 @@ static int enqueue_loop(dm_plan* P, float* x, int have_start, const float* noise
 
 extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const float* noise_stack_dev, uint64_t seed,
                               int timesteps, int predict_epsilon, int clip_denoised, const dm_cond_t* cond,
-                              float* chain_dev, int use_graph, dm_stream_t st) {
+                              float* chain_dev, int fused, dm_stream_t st) {
   if (!P || !x_dev) return fail(DM_ERR_ARG, "null argument");
   if (P->n_timesteps == 0) return fail(DM_ERR_STATE, "dm_plan_set_schedule has not been called");
   if (timesteps < 0 || timesteps > P->n_timesteps) return fail(DM_ERR_ARG, "timesteps %d out of range", timesteps);
   cudaStream_t s = static_cast<cudaStream_t>(st);
   P->last_launches = 0;
+  if (P->steps_pending) { DM_CUDA(cudaEventSynchronize(P->steps_event)); P->steps_pending = false; }
   {
     unsigned long long sd = seed;
     DM_CUDA(cudaMemcpyAsync(P->seed_dev, &sd, sizeof(sd), cudaMemcpyHostToDevice, s));
   }
-  if (!use_graph) return enqueue_loop(P, x_dev, have_start, noise_stack_dev, seed, timesteps, predict_epsilon,
-                                      clip_denoised, cond, chain_dev, s);
-  GraphKey key{x_dev, noise_stack_dev, chain_dev, cond ? (const void*)cond->mask_dev : nullptr,
-               cond ? (const void*)cond->value_dev : nullptr, have_start, timesteps, predict_epsilon,
-               clip_denoised, cond ? cond->mask_batched : 0, cond ? cond->value_batched : 0};
-  if (!(P->graph_valid && P->graph_key == key)) {
-    if (P->graph_exec) { cudaGraphExecDestroy(P->graph_exec); P->graph_exec = nullptr; }
-    P->graph_valid = false;
-    cudaStream_t cs;
-    DM_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
-    cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
-    if (e != cudaSuccess) { cudaStreamDestroy(cs); return fail(DM_ERR_CUDA, "begin capture: %s", cudaGetErrorString(e)); }
-    int rc = enqueue_loop(P, x_dev, have_start, noise_stack_dev, seed, timesteps, predict_epsilon, clip_denoised, cond,
-                          chain_dev, cs);
-    cudaGraph_t graph = nullptr;
-    e = cudaStreamEndCapture(cs, &graph);
-    cudaStreamDestroy(cs);
-    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
-    if (e != cudaSuccess) return fail(DM_ERR_CUDA, "end capture: %s", cudaGetErrorString(e));
-    e = cudaGraphInstantiate(&P->graph_exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (e != cudaSuccess) return fail(DM_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
-    P->graph_key = key;
-    P->graph_valid = true;
-    P->graph_launches = P->last_launches;
+  if (!fused) return enqueue_loop(P, x_dev, have_start, noise_stack_dev, seed, timesteps, predict_epsilon, clip_denoised,
+                                  cond, chain_dev, s);
+  // ---- persistent cluster kernel: the whole loop is ONE launch ----
+  const long long n = (long long)P->B * P->H * P->T;
+  StepParams* sp = P->steps_host;
+  int rc = fill_step(P, &sp[0], x_dev, nullptr, noise_stack_dev, seed, -1, predict_epsilon, clip_denoised, cond);
+  if (rc) return rc;
+  sp[0].have_start = have_start;
+  sp[0].rng_stream = 0;
+  sp[0].seed_ptr = P->seed_dev;
+  sp[0].chain = chain_dev; sp[0].chain_len = timesteps + 1; sp[0].chain_slot = 0;
+  int k = 1;
+  for (int i = timesteps - 1; i >= 0; --i, ++k) {
+    if ((rc = fill_step(P, &sp[k], x_dev, P->model_out, noise_stack_dev ? noise_stack_dev + (size_t)k * n : nullptr, seed,
+                        i, predict_epsilon, clip_denoised, cond)))
+      return rc;
+    sp[k].rng_stream = (unsigned)k;
+    sp[k].seed_ptr = P->seed_dev;
+    sp[k].chain = chain_dev; sp[k].chain_len = timesteps + 1; sp[k].chain_slot = k;
   }
-  P->last_launches = P->graph_launches;
-  DM_CUDA(cudaGraphLaunch(P->graph_exec, s));
+  DM_CUDA(cudaMemcpyAsync(P->steps_dev, sp, (size_t)(timesteps + 1) * sizeof(StepParams), cudaMemcpyHostToDevice, s));
+  LoopParams lp;
+  lp.jobs = P->jobs_dev; lp.slices = P->slices_dev; lp.tb_off = P->tboff_dev; lp.n_jobs = (int)P->layers.size();
+  lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
+  lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
+  DM_CUDA(launch_sample_loop(lp, P->loop_smem, s));
+  // the pinned step table is reused by the next call: wait until the copy engine has consumed it
+  DM_CUDA(cudaEventRecord(P->steps_event, s));
+  P->steps_pending = true;
+  P->last_launches = 1;
   return DM_OK;
 }
 

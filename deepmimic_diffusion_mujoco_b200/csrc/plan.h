@@ -33,20 +33,6 @@ struct HostTensor {
   std::vector<int64_t> shape;
 };
 
-struct GraphKey {
-  const float* x;
-  const float* noise;
-  const float* chain;
-  const void* mask;
-  const void* value;
-  int have_start, timesteps, pe, clip, mb, vb;
-  bool operator==(const GraphKey& o) const {
-    return x == o.x && noise == o.noise && chain == o.chain && mask == o.mask && value == o.value &&
-           have_start == o.have_start && timesteps == o.timesteps && pe == o.pe && clip == o.clip && mb == o.mb &&
-           vb == o.vb;
-  }
-};
-
 }  // namespace dm
 
 struct dm_plan {
@@ -67,9 +53,13 @@ struct dm_plan {
   int last_launches = 0;
   unsigned long long rng_calls = 0;
   unsigned long long* seed_dev = nullptr;
-  // one cached CUDA graph of the whole sampling loop
-  bool graph_valid = false;
-  dm::GraphKey graph_key{};
-  cudaGraphExec_t graph_exec = nullptr;
-  int graph_launches = 0;
+  // persistent sampling-loop kernel arguments
+  dm::ConvJob* jobs_dev = nullptr;
+  int* slices_dev = nullptr;
+  int* tboff_dev = nullptr;
+  size_t loop_smem = 0;
+  dm::StepParams* steps_dev = nullptr;
+  dm::StepParams* steps_host = nullptr;   // pinned staging
+  cudaEvent_t steps_event = nullptr;
+  bool steps_pending = false;
 };

@@ -159,6 +159,25 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_f16(uint32_t M, uint32_t
   return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
+// ------------------------------------------- clusters ------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_id_x() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+  return r;
+}
+// all threads of all CTAs in the cluster: release/acquire at cluster scope
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// make this thread's generic-proxy writes (global and shared) visible to the async proxy (TMA)
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 // split an fp32 value into fp16 hi + fp16 lo (hi + lo reproduces v to ~2^-22 relative)
 __device__ __forceinline__ void split_half(float v, __half& hi, __half& lo) {
   hi = __float2half_rn(v);

@@ -19,6 +19,7 @@ struct TimeMlpParams {
 
 struct StepParams {
   int mode;            // 0 = denoise step, 1 = init (x = starting motion or noise; then inpaint)
+  int t_index;         // timestep of this step (row of the time-bias table)
   float* x;            // [B,H,T] fp32, updated in place
   const float* model_out;
   const float* noise;  // injected noise [B,H,T] or null -> Philox(seed, offset)
@@ -40,6 +41,21 @@ struct StepParams {
   int B, H, T;
   long long n_elems;   // B*H*T (multiple of 4 because H % 8 == 0)
 };
+
+struct ConvJob;
+// Arguments of the persistent sampling-loop kernel (conv_kernel.cu).  All pointers are device pointers.
+struct LoopParams {
+  const ConvJob* jobs;        // [n_jobs] layer descriptors (TMA maps inside), in execution order
+  const int* slices;          // [n_jobs] number of N slices of each layer
+  const int* tb_off;          // [n_jobs] offset of the layer's time bias inside a table row, or -1
+  int n_jobs;
+  const StepParams* steps;    // [n_steps + 1]: entry 0 = init, entry k = k-th executed denoising step
+  int n_steps;
+  const float* tb_table;      // [n_timesteps, TB]
+  int TB;
+  int G, B, H, T;
+};
+cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStream_t stream);
 
 cudaError_t launch_time_bias(const TimeMlpParams& p, const float* t_dev, int nt, float* out, cudaStream_t s);
 cudaError_t launch_ddpm_step(const StepParams& p, cudaStream_t s);

@@ -1,8 +1,8 @@
 """Drop-in for the reference's diffuser/models/diffusion.py sampling half (:16-41, :44-115, :147-240, :279-280).
 
 GaussianDiffusion keeps the reference constructor, buffers and p_sample_loop / conditional_sample signatures; the
-100-step loop itself is ONE call into libdm_b200.so (dm_sample_loop: a CUDA graph of tcgen05 conv launches and
-the fused posterior+noise+inpaint kernel).  Training (p_losses/loss, :242-277) is out of scope.
+100-step loop itself is ONE call into libdm_b200.so (dm_sample_loop: one persistent cluster kernel that runs every
+tcgen05 conv layer and the fused posterior+noise+inpaint update of every step).  Training (p_losses/loss, :242-277) is out of scope.
 """
 import ctypes
 from collections import namedtuple
@@ -100,7 +100,7 @@ class GaussianDiffusion(nn.Module):
     @torch.no_grad()
     def p_sample_loop(self, shape, cond, verbose=True, return_chain=False, sample_fn=default_sample_fn,
                       conditioning_fn=apply_conditioning, starting_motion=None, max_timesteps=None,
-                      use_graph=True, seed=None, **sample_kwargs):
+                      fused=True, seed=None, **sample_kwargs):
         device = self.betas.device
         if device.type != "cuda":
             raise _lib.DmError("GaussianDiffusion.p_sample_loop needs the module on a B200 (no CPU fallback)")
@@ -119,7 +119,7 @@ class GaussianDiffusion(nn.Module):
                                "or InjectedNoise (no fallback)")
 
         with torch.cuda.device(device):
-            # persistent device buffers: stable pointers let the captured CUDA graph be replayed across calls
+            # persistent device buffers: no allocator traffic on the sampling path
             x = self._persistent(("x", B, H, T), (B, H, T), torch.float32, device)
             if starting_motion is not None:
                 if tuple(starting_motion.shape) != (B, H, T):
@@ -146,7 +146,7 @@ class GaussianDiffusion(nn.Module):
                 plan.handle, x.data_ptr(), int(starting_motion is not None),
                 noise.data_ptr() if noise is not None else None, ctypes.c_uint64(seed & (2 ** 64 - 1)), timesteps,
                 int(self.predict_epsilon), int(self.clip_denoised), ctypes.byref(c),
-                chain.data_ptr() if chain is not None else None, int(bool(use_graph) and noise is None and chain is None),
+                chain.data_ptr() if chain is not None else None, int(bool(fused)),
                 _lib.stream_ptr()))
             self.last_launch_count = plan.last_launch_count()
             values = torch.zeros(B, device=device)

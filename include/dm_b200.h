@@ -85,10 +85,11 @@ int dm_ddpm_step(dm_plan_t* plan, float* x_dev, const float* model_out_dev, cons
  *   noise_stack_dev  NULL (Philox) or fp32 [timesteps+1,B,H,T]: slot 0 = initial draw, slot k = k-th step's draw
  *   timesteps    n_timesteps, or max_timesteps (:210)
  *   chain_dev    NULL or fp32 [B,timesteps+1,H,T] (return_chain, :208,220-227)
- *   use_graph    replay the whole loop as one CUDA graph (captured once per argument set) */
+ *   fused        1: ONE launch of the persistent cluster kernel (a 2-CTA cluster owns 16 samples and runs every
+ *                layer of every step with cluster-local barriers); 0: one launch per layer (debug / A-B check) */
 int dm_sample_loop(dm_plan_t* plan, float* x_dev, int have_start, const float* noise_stack_dev, uint64_t seed,
                    int timesteps, int predict_epsilon, int clip_denoised, const dm_cond_t* cond, float* chain_dev,
-                   int use_graph, dm_stream_t stream);
+                   int fused, dm_stream_t stream);
 
 /* Batched humanoid forward kinematics (MuJoCo mj_kinematics semantics on assets/dp_env_v2.xml; replaces
  * sim.forward() at mocap_player.py:67-73) + DeepMimic tracking reward.

@@ -22,6 +22,6 @@ net = dm.TemporalUnet(H, 35, 35)
 net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
 diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=steps, predict_epsilon=False).cuda()
 for _ in range(2):
-    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=box, use_graph=False, seed=1)
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=box, fused=(os.environ.get('DM_FUSED','1')=='1'), seed=1)
 torch.cuda.synchronize()
 print("ok", out.trajectories.abs().mean().item(), diff.last_launch_count)

@@ -74,8 +74,9 @@ def test_forward_matches_reference_fixture(dm, golden_dir, name):
     assert rel(y, torch.from_numpy(z["fwd_y"])) < 1e-4
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("name", ["unet_chain_plain", "unet_chain_box_eps_clip", "unet_chain_start_maxt"])
-def test_chain_matches_reference_fixture(dm, golden_dir, name):
+def test_chain_matches_reference_fixture(dm, golden_dir, name, fused):
     """Full p_sample_loop with injected noise against the chain recorded from the UNMODIFIED reference."""
     z = np.load(os.path.join(golden_dir, name + ".npz"))
     B, H, n_steps, pe, clip, cond, start, max_t, seed = [int(v) for v in z["meta"]]
@@ -90,7 +91,7 @@ def test_chain_matches_reference_fixture(dm, golden_dir, name):
     if max_t >= 0:
         kw["max_timesteps"] = max_t
     out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True,
-                             sample_fn=dm.InjectedNoise(torch.from_numpy(z["noise"])), **kw)
+                             sample_fn=dm.InjectedNoise(torch.from_numpy(z["noise"])), fused=fused, **kw)
     ref = torch.from_numpy(z["chain"])
     chain = out.chains.cpu()
     assert chain.shape == ref.shape
@@ -154,8 +155,8 @@ def test_ddpm_step_kernel_matches_oracle(dm):
 
 
 def test_philox_sampling_statistics_and_determinism(dm):
-    """Built-in sampler (in-kernel Philox noise, CUDA-graph replay): deterministic per seed, finite, conditioned
-    entries exact, different seeds differ."""
+    """Built-in sampler (in-kernel Philox noise, persistent cluster kernel): deterministic per seed, finite,
+    conditioned entries exact, different seeds differ, and bit-identical to the one-launch-per-layer path."""
     B, H = 32, 64
     net = dm.TemporalUnet(H, 35, 35)
     net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
@@ -168,7 +169,10 @@ def test_philox_sampling_statistics_and_determinism(dm):
     assert not torch.equal(a, c)
     assert torch.equal(a[:, :, 16], torch.full((B, H), 1.57, device="cuda"))
     assert torch.equal(a[:, :, 13:16], torch.zeros(B, H, 3, device="cuda"))
+    assert diff.last_launch_count == 1
+    d = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=11, fused=False).trajectories
     assert diff.last_launch_count > 20 * 40
+    assert torch.equal(a, d)
 
 
 def test_initial_noise_is_standard_normal(dm):
