@@ -35,6 +35,15 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 
 constexpr int kEpiThreads = kEpiWarps * 32;
 
+// Optional phase trace (debug): tr points at 16 slots of this (job, unit); null in production.
+__device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
+  if (tr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    tr[ev] = t;
+  }
+}
+
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full;
   uint32_t tmem_slot;
@@ -60,8 +69,9 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
 // ================================ TMA producer (one thread) ================================
 __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
                                               int g, int b0, int n0, uint8_t* a_smem, uint8_t* w_smem, ConvShared& sh,
-                                              RoleState& rs) {
+                                              RoleState& rs, unsigned long long* tr) {
   int as = 0, ws = 0;
+  trace_mark(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
     int cin_off = 0;
@@ -71,6 +81,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
         mbar_arrive_expect_tx(&sh.a_full[as], job.a_tx_bytes);
         tma_load_5d(a_smem + (size_t)as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
         rs.a_bits ^= 1u << as;
+        if (lt == 0 && src == 0 && ch == 0) trace_mark(tr, 3);
         for (int t = 0; t < job.ntaps; ++t) {
           mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
           mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
@@ -84,11 +95,12 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
       cin_off += job.src_chunks[src] * job.Cc;
     }
   }
+  trace_mark(tr, 4);
 }
 
 // ================================ MMA issuer (one thread) ==================================
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint8_t* a_smem, uint8_t* w_smem, ConvShared& sh,
-                                         uint32_t tmem_base, RoleState& rs) {
+                                         uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
   const int S = job.S, Nc = job.Nc;
   const int MT = job.n_ltiles * job.Mt;
   const uint32_t idesc = umma_idesc_f16(128, Nc);
@@ -103,11 +115,13 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint8_t* a_smem, ui
       for (int ch = 0; ch < job.src_chunks[src]; ++ch, ++cidx) {
         mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
         rs.a_bits ^= 1u << as;
+        if (lt == 0 && cidx == 0) trace_mark(tr, 5);
         tc_fence_after();
         const uint32_t a_base = smem_u32(a_smem + (size_t)as * job.a_stage_bytes);
         for (int t = 0; t < job.ntaps; ++t) {
           mbar_wait(&sh.w_full[ws], (rs.w_bits >> ws) & 1, 0x400 + ws);
           rs.w_bits ^= 1u << ws;
+          if (lt == 0 && cidx == 0 && t == 0) trace_mark(tr, 6);
           tc_fence_after();
           const uint32_t w_base = smem_u32(w_smem + (size_t)ws * job.w_stage_bytes);
           const ConvTap tap = job.taps[t];
@@ -135,15 +149,18 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint8_t* a_smem, ui
     }
   }
   umma_commit(&sh.acc_full);
+  trace_mark(tr, 7);
 }
 
 // ================================ epilogue (warps 0..15) ===================================
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
 __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0, int n0, const float* tbias,
-                                              int tbias_stride, ConvShared& sh, uint32_t tmem_base, RoleState& rs) {
+                                              int tbias_stride, ConvShared& sh, uint32_t tmem_base, RoleState& rs,
+                                              unsigned long long* tr) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tid = threadIdx.x;                 // 0..511
+  if (tid != 0) tr = nullptr;
   const int S = job.S, Nc = job.Nc;
   const int MT = job.n_ltiles * job.Mt;
   const int row = (warp & 3) * 32 + lane;      // row inside a 128-row tile == TMEM lane
@@ -164,9 +181,11 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0,
   }
   named_bar_sync(1, kEpiThreads);
 
+  trace_mark(tr, 8);
   mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x500);
   rs.acc_count++;
   tc_fence_after();
+  trace_mark(tr, 9);
   const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
   const int nchunks = Nc >> 5;
   float v[32];
@@ -214,6 +233,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0,
     named_bar_sync(1, kEpiThreads);
   }
 
+  trace_mark(tr, 10);
   // ---- pass 2: normalise, Mish, + time bias, + residual, split to fp16 hi/lo, store ----
   const float inv_n = 1.f / (float)(job.cg * job.Lj);
   const int bg = g * kGroupSamples + b0 + b;
@@ -307,18 +327,19 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0,
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
 __device__ __forceinline__ void run_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map, int g,
                                          int b0, int n0, const float* tbias, int tbias_stride, uint8_t* smem,
-                                         ConvShared& sh, uint32_t tmem_base, RoleState& rs) {
+                                         ConvShared& sh, uint32_t tmem_base, RoleState& rs,
+                                         unsigned long long* tr = nullptr) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* a_smem = smem;
   uint8_t* w_smem = smem + (size_t)job.n_a_stages * job.a_stage_bytes;
   if (warp == kProducerWarp) {
-    if (lane == 0) producer_unit(job, a_maps, w_map, g, b0, n0, a_smem, w_smem, sh, rs);
+    if (lane == 0) producer_unit(job, a_maps, w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr);
     __syncwarp();
   } else if (warp == kMmaWarp) {
-    if (lane == 0) mma_unit(job, a_smem, w_smem, sh, tmem_base, rs);
+    if (lane == 0) mma_unit(job, a_smem, w_smem, sh, tmem_base, rs, tr);
     __syncwarp();
   } else {
-    epilogue_unit(job, g, b0, n0, tbias, tbias_stride, sh, tmem_base, rs);
+    epilogue_unit(job, g, b0, n0, tbias, tbias_stride, sh, tmem_base, rs, tr);
   }
 }
 
@@ -392,12 +413,16 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
     if (k > 0) {
       const int t_index = lp.steps[k].t_index;
       for (int ji = 0; ji < lp.n_jobs; ++ji) {
+        unsigned long long* tr = (lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
+                                     ? lp.trace + (size_t)ji * 16 : nullptr;
+        if (threadIdx.x == 0) trace_mark(tr, 0);
         {  // stage the layer descriptor in shared memory
           const uint32_t* src = reinterpret_cast<const uint32_t*>(lp.jobs + ji);
           uint32_t* dst = reinterpret_cast<uint32_t*>(&sjob);
           for (int i = threadIdx.x; i < (int)(sizeof(ConvJob) / 4); i += kConvThreads) dst[i] = __ldg(src + i);
         }
         __syncthreads();
+        if (threadIdx.x == 0) trace_mark(tr, 1);
         const ConvJob& job = sjob;
         const int slices = lp.slices[ji];
         const int off = lp.tb_off[ji];
@@ -407,14 +432,16 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         const int first = job.S == 8 ? 0 : rank, stride = job.S == 8 ? 1 : 2;
         const int b0 = job.S == 8 ? rank * 8 : 0;
         for (int sl = first; sl < slices; sl += stride) {
-          run_unit(job, a_maps, w_map, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs);
+          run_unit(job, a_maps, w_map, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr);
           if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit
             tc_fence_before();
             __syncthreads();
             tc_fence_after();
           }
         }
+        if (threadIdx.x == 0) trace_mark(tr, 12);
         job_sync(warp < kEpiWarps);
+        if (threadIdx.x == 0) trace_mark(tr, 13);
       }
     }
     // ---- K4: init (k == 0) or fused posterior + noise + inpaint + operand re-pack for this CTA's samples ----

@@ -760,6 +760,7 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   lp.jobs = P->jobs_dev; lp.slices = P->slices_dev; lp.tb_off = P->tboff_dev; lp.n_jobs = (int)P->layers.size();
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
+  lp.trace = P->trace_dev; lp.trace_cluster = P->trace_cluster; lp.trace_step = P->trace_step;
   DM_CUDA(launch_sample_loop(lp, P->loop_smem, s));
   // the pinned step table is reused by the next call: wait until the copy engine has consumed it
   DM_CUDA(cudaEventRecord(P->steps_event, s));
@@ -787,6 +788,12 @@ extern "C" int dm_plan_read_layer(dm_plan_t* P, int i, float* out_dev, dm_stream
   // unpack only the real channels: out is [B, Cout, L]
   if (a.C != ly.job.Cout) return fail(DM_ERR_ARG, "layer %d output is channel padded", i);
   DM_CUDA(launch_unpack_act(a.p, a.plane, a.C, a.L, P->B, out_dev, static_cast<cudaStream_t>(st)));
+  return DM_OK;
+}
+
+extern "C" int dm_plan_set_trace(dm_plan_t* P, unsigned long long* trace_dev, int cluster, int step) {
+  if (!P) return fail(DM_ERR_ARG, "null argument");
+  P->trace_dev = trace_dev; P->trace_cluster = cluster; P->trace_step = step;
   return DM_OK;
 }
 

@@ -62,4 +62,6 @@ struct dm_plan {
   dm::StepParams* steps_host = nullptr;   // pinned staging
   cudaEvent_t steps_event = nullptr;
   bool steps_pending = false;
+  unsigned long long* trace_dev = nullptr;   // debug phase trace (dm_plan_set_trace)
+  int trace_cluster = 0, trace_step = 0;
 };

@@ -54,6 +54,8 @@ struct LoopParams {
   const float* tb_table;      // [n_timesteps, TB]
   int TB;
   int G, B, H, T;
+  unsigned long long* trace;  // debug: [n_jobs][16] globaltimer stamps of one (cluster, step); null in production
+  int trace_cluster, trace_step;
 };
 cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStream_t stream);
 

@@ -107,6 +107,9 @@ int dm_fid_moments(const float* X_dev, int N, int D, double* sum_dev, double* sx
 int dm_plan_num_layers(const dm_plan_t* plan);
 int dm_plan_layer_info(const dm_plan_t* plan, int i, char* name, int name_cap, int* C, int* L);
 int dm_plan_read_layer(dm_plan_t* plan, int i, float* out_dev, dm_stream_t stream);
+/* Debug: record %globaltimer stamps of the phases of every layer of one (cluster, step) of the fused loop into
+ * trace_dev (uint64 [num_layers][16]); NULL switches tracing off. */
+int dm_plan_set_trace(dm_plan_t* plan, unsigned long long* trace_dev, int cluster, int step);
 /* Kernel launches issued by the last dm_unet_forward / dm_sample_loop call. */
 int dm_plan_last_launch_count(const dm_plan_t* plan);
 /* Non-zero if device code recorded a protocol failure (barrier timeout code). */

@@ -1,0 +1,33 @@
+"""Diagnostic (GPU box): per-layer phase timeline of the fused sampling-loop kernel for one cluster / one step."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import deepmimic_diffusion_mujoco_b200 as dm
+from deepmimic_diffusion_mujoco_b200 import _lib
+from oracle import diffusion_oracle as O
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
+H = int(sys.argv[2]) if len(sys.argv) > 2 else 64
+steps = 6
+net = dm.TemporalUnet(H, 35, 35)
+net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
+diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=steps, predict_epsilon=False).cuda()
+plan = net.plan_for(B, H)
+names = plan.layer_names()
+tr = torch.zeros(len(names), 16, dtype=torch.int64, device="cuda")
+_lib.check(_lib.lib().dm_plan_set_trace(plan.handle, tr.data_ptr(), 3, 4))
+for _ in range(2):
+    diff.p_sample_loop((B, H, 35), {}, verbose=False, seed=1)
+torch.cuda.synchronize()
+t = tr.cpu().numpy().astype("float64")
+t0 = t[0, 0]
+ev = ["start", "jobcp", "prod0", "A_iss", "prodE", "A_arr", "W_arr", "mmaIs", "epi0", "accF", "pass1", "pass2", "unitE", "sync"]
+print("layer".ljust(28), " ".join(e.rjust(6) for e in ev), "  total_us")
+tot = 0
+for i, (n, C, L) in enumerate(names):
+    r = t[i]
+    base = r[0]
+    vals = [(r[k] - base) / 1e3 if r[k] > 0 else float("nan") for k in range(14)]
+    print(f"{n[:27]:28s}", " ".join(f"{v:6.1f}" for v in vals), f"  {(r[13]-r[0])/1e3:7.1f}")
+    tot += r[13] - r[0]
+print("sum of layers us", tot / 1e3, " step span us", (t[-1, 13] - t[0, 0]) / 1e3)
