@@ -30,9 +30,15 @@ struct ConvTap {
 
 enum { EPI_BIAS = 0, EPI_GN_MISH = 1 };
 
-struct ConvJob {
+// TMA descriptors of one layer; they live in global memory (or in a __grid_constant__ kernel parameter).
+struct ConvMaps {
   CUtensorMap a_map[2];   // 5-D (C, 16, L, G, plane) fp16, one per input source (2 = channel concat)
   CUtensorMap w_map;      // 4-D (CinTot, CoutPad, ntaps, plane) fp16
+};
+
+// Plain-data layer descriptor.  It is always read from kernel-parameter (constant-bank) space, so every field
+// is warp-uniform for the compiler: the MMA / TMA issue loops stay on the uniform datapath.
+struct ConvJob {
   int nsrc;
   int src_chunks[2];      // channel chunks per source
   int Cc;                 // channels per chunk (64 -> SWIZZLE_128B rows, 32 -> SWIZZLE_64B rows)
@@ -73,6 +79,11 @@ struct ConvJob {
   long long out_plane_stride;
   float* out_f32;         // public layout [B][Lout][out_f32_C]; null if none
   int out_f32_C;
+  // fused-loop bookkeeping
+  int slices;             // number of N slices (units per sample sub-group)
+  int tb_off;             // offset of the layer's time bias inside a time-bias table row, or -1
 };
+
+constexpr int kMaxLoopJobs = 80;   // layers of one U-Net inside the fused-loop kernel parameter block
 
 }  // namespace dm

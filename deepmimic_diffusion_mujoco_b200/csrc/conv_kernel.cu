@@ -13,6 +13,12 @@
 // conv are five UMMA descriptors over one TMA-loaded box (halo rows zero-filled by TMA out-of-bounds handling).
 // The whole per-sample conv output lives in TMEM until GroupNorm statistics are known; no cross-CTA reduce.
 //
+// Issue discipline: the layer descriptor (ConvJob) is read from kernel-parameter space, the TMA and MMA warps
+// run their loops warp-converged and issue through elect_one_sync(), so descriptors, coordinates and loop
+// counters stay in uniform registers (no per-lane R2UR waterfall in front of every UTCHMMA / UTMALDG).  The
+// 16 epilogue warps do not poll the accumulator barrier: one warp waits on the mbarrier, the others block on a
+// hardware named barrier, which leaves the issue slots to the MMA / TMA warps.
+//
 // Reference: Conv1dBlock helpers.py:50-69; ResidualTemporalBlock temporal.py:37-46; Downsample1d/Upsample1d
 // helpers.py:32-47; p_sample_loop diffusion.py:186-228 (under /root/reference/diffusion/diffuser/models/).
 #include "conv_job.h"
@@ -34,6 +40,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kPollWarp = 2;   // epilogue warp that waits on the accumulator mbarrier (SMSP 2: neither TMA nor MMA warp)
 
 // Optional phase trace (debug): tr points at 16 slots of this (job, unit); null in production.
 __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
@@ -47,7 +54,8 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full;
   uint32_t tmem_slot;
-  alignas(16) float par[4][256];                    // bias, gamma, beta, time bias of this unit's Nc channels
+  alignas(16) float par[4][256];        // bias, gamma, beta, time bias of this unit's Nc channels
+  alignas(16) unsigned char qgrp[64];   // GroupNorm group (within the unit) of every 4-channel quad
   float stat[16][8][2];                 // per (sample, group): sum, sum of squares
   float part[kEpiWarps][16][8][2];      // per-warp partials, combined in a fixed order (deterministic)
 };
@@ -66,102 +74,119 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
   fence_barrier_init();
 }
 
-// ================================ TMA producer (one thread) ================================
+// ================================ TMA producer (one warp, one elected lane issues) =========================
 __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
-                                              int g, int b0, int n0, uint8_t* a_smem, uint8_t* w_smem, ConvShared& sh,
+                                              int g, int b0, int n0, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
                                               RoleState& rs, unsigned long long* tr) {
+  const bool leader = elect_one_sync();
   int as = 0, ws = 0;
-  trace_mark(tr, 2);
+  if (leader) trace_mark(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
     int cin_off = 0;
     for (int src = 0; src < job.nsrc; ++src) {
-      for (int ch = 0; ch < job.src_chunks[src]; ++ch) {
+      const int nch = job.src_chunks[src];
+      for (int ch = 0; ch < nch; ++ch) {
         mbar_wait(&sh.a_empty[as], ((rs.a_bits >> as) & 1) ^ 1, 0x100 + as);
-        mbar_arrive_expect_tx(&sh.a_full[as], job.a_tx_bytes);
-        tma_load_5d(a_smem + (size_t)as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
+        if (leader) {
+          mbar_arrive_expect_tx(&sh.a_full[as], job.a_tx_bytes);
+          tma_load_5d(a_smem + as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
+        }
         rs.a_bits ^= 1u << as;
-        if (lt == 0 && src == 0 && ch == 0) trace_mark(tr, 3);
         for (int t = 0; t < job.ntaps; ++t) {
           mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
-          mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
-          tma_load_4d(w_smem + (size_t)ws * job.w_stage_bytes, w_map, &sh.w_full[ws], cin_off + ch * job.Cc, n0,
-                      job.taps[t].wtap, 0);
+          if (leader) {
+            mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
+            tma_load_4d(w_smem + ws * job.w_stage_bytes, w_map, &sh.w_full[ws], cin_off + ch * job.Cc, n0,
+                        job.taps[t].wtap, 0);
+          }
           rs.w_bits ^= 1u << ws;
           if (++ws == job.n_w_stages) ws = 0;
         }
         if (++as == job.n_a_stages) as = 0;
       }
-      cin_off += job.src_chunks[src] * job.Cc;
+      cin_off += nch * job.Cc;
     }
   }
-  trace_mark(tr, 4);
+  if (leader) trace_mark(tr, 4);
+  __syncwarp();
 }
 
-// ================================ MMA issuer (one thread) ==================================
-__device__ __forceinline__ void mma_unit(const ConvJob& job, uint8_t* a_smem, uint8_t* w_smem, ConvShared& sh,
+// ================================ MMA issuer (one warp, one elected lane issues) ===========================
+__device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
                                          uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
+  const bool leader = elect_one_sync();
   const int S = job.S, Nc = job.Nc;
   const int MT = job.n_ltiles * job.Mt;
   const uint32_t idesc = umma_idesc_f16(128, Nc);
-  const uint32_t sbo_a = job.l_stride * 8 * job.row_bytes;
-  const uint32_t sbo_w = 8 * job.row_bytes;
-  const int ksteps = job.Cc / 16;
+  const int ksteps = job.Cc >> 4;
   const int pos_per_mt = 128 / S;
+  // descriptor high words are per-layer constants; only the 14-bit start address changes per MMA
+  const uint64_t hi_a = umma_smem_desc(0, job.l_stride * 8 * job.row_bytes, job.swz);
+  const uint64_t hi_w = umma_smem_desc(0, 8 * job.row_bytes, job.swz);
+  const uint32_t a_plane16 = job.a_plane_bytes >> 4, w_plane16 = job.w_plane_bytes >> 4;
+  const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
   int as = 0, ws = 0;
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     int cidx = 0;
     for (int src = 0; src < job.nsrc; ++src) {
-      for (int ch = 0; ch < job.src_chunks[src]; ++ch, ++cidx) {
+      const int nch = job.src_chunks[src];
+      for (int ch = 0; ch < nch; ++ch, ++cidx) {
         mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
         rs.a_bits ^= 1u << as;
-        if (lt == 0 && cidx == 0) trace_mark(tr, 5);
         tc_fence_after();
-        const uint32_t a_base = smem_u32(a_smem + (size_t)as * job.a_stage_bytes);
+        if (leader && lt == 0 && cidx == 0) trace_mark(tr, 5);
+        const uint32_t a_base16 = (a_smem + as * job.a_stage_bytes) >> 4;
         for (int t = 0; t < job.ntaps; ++t) {
           mbar_wait(&sh.w_full[ws], (rs.w_bits >> ws) & 1, 0x400 + ws);
           rs.w_bits ^= 1u << ws;
-          if (lt == 0 && cidx == 0 && t == 0) trace_mark(tr, 6);
           tc_fence_after();
-          const uint32_t w_base = smem_u32(w_smem + (size_t)ws * job.w_stage_bytes);
-          const ConvTap tap = job.taps[t];
-          for (int mt = 0; mt < job.Mt; ++mt) {
-            const uint32_t d = tmem_base + (uint32_t)((tap.phase * MT + lt * job.Mt + mt) * Nc);
-            const uint32_t a_row = (uint32_t)((job.l_stride * mt * pos_per_mt + tap.shift) * S);
-            const uint32_t a_addr = a_base + a_row * job.row_bytes;
-            for (int k = 0; k < ksteps; ++k) {
-              const uint32_t acc = !(cidx == 0 && tap.first && k == 0);
-              const uint64_t a_hi = umma_smem_desc(a_addr + k * 32, sbo_a, job.swz);
-              const uint64_t a_lo = umma_smem_desc(a_addr + job.a_plane_bytes + k * 32, sbo_a, job.swz);
-              const uint64_t w_hi = umma_smem_desc(w_base + k * 32, sbo_w, job.swz);
-              const uint64_t w_lo = umma_smem_desc(w_base + job.w_plane_bytes + k * 32, sbo_w, job.swz);
-              umma_f16(d, a_lo, w_hi, idesc, acc);
-              umma_f16(d, a_hi, w_lo, idesc, 1);
-              umma_f16(d, a_hi, w_hi, idesc, 1);
+          if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark(tr, 6);
+          const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
+          const int shift = job.taps[t].shift, phase = job.taps[t].phase;
+          const bool first = cidx == 0 && job.taps[t].first != 0;
+          uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * Nc);
+          uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
+          for (int mt = 0; mt < job.Mt; ++mt, d += Nc, a16 += mt_step16) {
+            if (leader) {
+              for (int k = 0; k < ksteps; ++k) {
+                const uint64_t a_hi = hi_a | ((a16 + 2 * k) & 0x3FFF);
+                const uint64_t a_lo = hi_a | ((a16 + a_plane16 + 2 * k) & 0x3FFF);
+                const uint64_t w_hi = hi_w | ((w16 + 2 * k) & 0x3FFF);
+                const uint64_t w_lo = hi_w | ((w16 + w_plane16 + 2 * k) & 0x3FFF);
+                umma_f16(d, a_lo, w_hi, idesc, !(first && k == 0));
+                umma_f16(d, a_hi, w_lo, idesc, 1);
+                umma_f16(d, a_hi, w_hi, idesc, 1);
+              }
             }
           }
-          umma_commit(&sh.w_empty[ws]);
+          __syncwarp();
+          if (leader) umma_commit(&sh.w_empty[ws]);
           if (++ws == job.n_w_stages) ws = 0;
         }
-        umma_commit(&sh.a_empty[as]);
+        if (leader) umma_commit(&sh.a_empty[as]);
         if (++as == job.n_a_stages) as = 0;
       }
     }
   }
-  umma_commit(&sh.acc_full);
-  trace_mark(tr, 7);
+  if (leader) {
+    umma_commit(&sh.acc_full);
+    trace_mark(tr, 7);
+  }
+  __syncwarp();
 }
 
 // ================================ epilogue (warps 0..15) ===================================
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
-__device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0, int n0, const float* tbias,
+__device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int g, int b0, int n0, const float* tbias,
                                               int tbias_stride, ConvShared& sh, uint32_t tmem_base, RoleState& rs,
                                               unsigned long long* tr) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31;
   const int tid = threadIdx.x;                 // 0..511
   if (tid != 0) tr = nullptr;
   const int S = job.S, Nc = job.Nc;
+  const int s_shift = S == 8 ? 3 : 4;
   const int MT = job.n_ltiles * job.Mt;
   const int row = (warp & 3) * 32 + lane;      // row inside a 128-row tile == TMEM lane
   const int slice = warp >> 2;
@@ -175,15 +200,16 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0,
     sh.par[2][i] = gn ? __ldg(job.beta + n0 + i) : 0.f;
     sh.par[3][i] = tb_uniform ? __ldg(tbias + n0 + i) : 0.f;
   }
+  if (tid < (Nc >> 2)) sh.qgrp[tid] = (unsigned char)((tid * 4) / job.cg);
   if (gn) {
     float* pp = &sh.part[0][0][0][0];
     for (int i = tid; i < kEpiWarps * 256; i += kEpiThreads) pp[i] = 0.f;
   }
-  named_bar_sync(1, kEpiThreads);
-
   trace_mark(tr, 8);
-  mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x500);
+  // one warp waits for the accumulator; everybody else parks on the hardware barrier (no issue slots burnt)
+  if (warp == kPollWarp) mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x500);
   rs.acc_count++;
+  named_bar_sync(1, kEpiThreads);
   tc_fence_after();
   trace_mark(tr, 9);
   const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
@@ -192,33 +218,33 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0,
 
   if (gn) {
     // ---- pass 1: GroupNorm statistics over (channels of group) x (all L positions), per sample ----
-    const int units = MT * nchunks;
-    for (int u = slice; u < units; u += 4) {
-      const int T = u / nchunks, cc = u - T * nchunks;
-      const int j = (T * 128 + row) / S;
-      tmem_ld32(trow + (uint32_t)(T * Nc + cc * 32), v);
-      tmem_ld_wait();
-      float s[8], q[8];
+    for (int T = 0; T < MT; ++T) {
+      const bool ok = ((T * 128 + row) >> s_shift) < job.Lj;
+      for (int cc = (slice - T * nchunks) & 3; cc < nchunks; cc += 4) {   // units u = T * nchunks + cc with u % 4 == slice
+        tmem_ld32(trow + (uint32_t)(T * Nc + cc * 32), v);
+        tmem_ld_wait();
+        float s[8], q[8];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cc * 32 + r * 4]);
-        const float x0 = v[r * 4] + bi.x, x1 = v[r * 4 + 1] + bi.y, x2 = v[r * 4 + 2] + bi.z, x3 = v[r * 4 + 3] + bi.w;
-        const bool ok = j < job.Lj;
-        s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
-        q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
-      }
-#pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
-        q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
-        if (S == 8) {
-          s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
-          q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
+        for (int r = 0; r < 8; ++r) {
+          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cc * 32 + r * 4]);
+          const float x0 = v[r * 4] + bi.x, x1 = v[r * 4 + 1] + bi.y, x2 = v[r * 4 + 2] + bi.z, x3 = v[r * 4 + 3] + bi.w;
+          s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
+          q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
         }
-        if (lane < S) {
-          const int gi = (cc * 32 + r * 4) / job.cg;   // fixed (u, r) order per warp: deterministic
-          sh.part[warp][lane][gi][0] += s[r];
-          sh.part[warp][lane][gi][1] += q[r];
+        const uint2 gq = *reinterpret_cast<const uint2*>(&sh.qgrp[cc * 8]);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
+          q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
+          if (S == 8) {
+            s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
+            q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
+          }
+          if (lane < S) {
+            const int gi = (int)(((r < 4 ? gq.x : gq.y) >> ((r & 3) * 8)) & 0xff);   // fixed (u, r) order: deterministic
+            sh.part[warp][lane][gi][0] += s[r];
+            sh.part[warp][lane][gi][1] += q[r];
+          }
         }
       }
     }
@@ -232,135 +258,139 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int g, int b0,
     }
     named_bar_sync(1, kEpiThreads);
   }
-
   trace_mark(tr, 10);
+
   // ---- pass 2: normalise, Mish, + time bias, + residual, split to fp16 hi/lo, store ----
   const float inv_n = 1.f / (float)(job.cg * job.Lj);
   const int bg = g * kGroupSamples + b0 + b;
-  const int units2 = job.nphase * MT * nchunks;
-  for (int u = slice; u < units2; u += 4) {
-    const int ph = u / (MT * nchunks);
-    const int u1 = u - ph * MT * nchunks;
-    const int T = u1 / nchunks, cc = u1 - T * nchunks;
-    const int j = (T * 128 + row) / S;
-    tmem_ld32(trow + (uint32_t)((ph * MT + T) * Nc + cc * 32), v);
-    tmem_ld_wait();
-    if (j >= job.Lj) continue;
+  const int PT = job.nphase * MT;
+  for (int pt = 0; pt < PT; ++pt) {
+    const int ph = pt >= MT ? 1 : 0;
+    const int T = pt - ph * MT;
+    const int j = (T * 128 + row) >> s_shift;
+    const bool ok = j < job.Lj;
     const int lrow = job.nphase == 2 ? 2 * j + ph : j;
     const size_t rowoff = ((size_t)g * job.Lout + lrow) * kGroupSamples + b0 + b;
-    const int cb = cc * 32;
+    for (int cc = (slice - pt * nchunks) & 3; cc < nchunks; cc += 4) {
+      tmem_ld32(trow + (uint32_t)(pt * Nc + cc * 32), v);
+      tmem_ld_wait();
+      if (!ok) continue;
+      const int cb = cc * 32;
+      const uint2 gq = *reinterpret_cast<const uint2*>(&sh.qgrp[cc * 8]);
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
-      float x[4] = {v[r * 4] + bi.x, v[r * 4 + 1] + bi.y, v[r * 4 + 2] + bi.z, v[r * 4 + 3] + bi.w};
-      if (gn) {
-        const int gi = (cb + r * 4) / job.cg;
-        const float mean = sh.stat[b][gi][0] * inv_n;
-        const float var = fmaxf(sh.stat[b][gi][1] * inv_n - mean * mean, 0.f);
-        const float rstd = rsqrtf(var + 1e-5f);
-        const float4 ga = *reinterpret_cast<const float4*>(&sh.par[1][cb + r * 4]);
-        const float4 be = *reinterpret_cast<const float4*>(&sh.par[2][cb + r * 4]);
-        const float4 tb = *reinterpret_cast<const float4*>(&sh.par[3][cb + r * 4]);
-        x[0] = mish_f(fmaf((x[0] - mean) * rstd, ga.x, be.x)) + tb.x;
-        x[1] = mish_f(fmaf((x[1] - mean) * rstd, ga.y, be.y)) + tb.y;
-        x[2] = mish_f(fmaf((x[2] - mean) * rstd, ga.z, be.z)) + tb.z;
-        x[3] = mish_f(fmaf((x[3] - mean) * rstd, ga.w, be.w)) + tb.w;
+      for (int r = 0; r < 8; ++r) {
+        const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
+        float x[4] = {v[r * 4] + bi.x, v[r * 4 + 1] + bi.y, v[r * 4 + 2] + bi.z, v[r * 4 + 3] + bi.w};
+        if (gn) {
+          const int gi = (int)(((r < 4 ? gq.x : gq.y) >> ((r & 3) * 8)) & 0xff);
+          const float2 st = *reinterpret_cast<const float2*>(&sh.stat[b][gi][0]);
+          const float mean = st.x * inv_n;
+          const float var = fmaxf(st.y * inv_n - mean * mean, 0.f);
+          const float rstd = rsqrtf(var + 1e-5f);
+          const float4 ga = *reinterpret_cast<const float4*>(&sh.par[1][cb + r * 4]);
+          const float4 be = *reinterpret_cast<const float4*>(&sh.par[2][cb + r * 4]);
+          const float4 tb = *reinterpret_cast<const float4*>(&sh.par[3][cb + r * 4]);
+          x[0] = mish_f(fmaf((x[0] - mean) * rstd, ga.x, be.x)) + tb.x;
+          x[1] = mish_f(fmaf((x[1] - mean) * rstd, ga.y, be.y)) + tb.y;
+          x[2] = mish_f(fmaf((x[2] - mean) * rstd, ga.z, be.z)) + tb.z;
+          x[3] = mish_f(fmaf((x[3] - mean) * rstd, ga.w, be.w)) + tb.w;
+        }
+        v[r * 4] = x[0]; v[r * 4 + 1] = x[1]; v[r * 4 + 2] = x[2]; v[r * 4 + 3] = x[3];
       }
-      v[r * 4] = x[0]; v[r * 4 + 1] = x[1]; v[r * 4 + 2] = x[2]; v[r * 4 + 3] = x[3];
-    }
-    if (gn && tbias != nullptr && tbias_stride != 0) {
-      const float4* tb = reinterpret_cast<const float4*>(tbias + (size_t)bg * tbias_stride + n0 + cb);
+      if (gn && tbias != nullptr && tbias_stride != 0) {
+        const float4* tb = reinterpret_cast<const float4*>(tbias + (size_t)bg * tbias_stride + n0 + cb);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float4 t4 = __ldg(tb + e);
-        v[e * 4] += t4.x; v[e * 4 + 1] += t4.y; v[e * 4 + 2] += t4.z; v[e * 4 + 3] += t4.w;
-      }
-    }
-    if (job.res) {
-      // L2-coherent loads: inside the persistent kernel this data was written by another SM moments ago
-      const uint4* rh = reinterpret_cast<const uint4*>(job.res + rowoff * job.res_C + n0 + cb);
-      const uint4* rl = reinterpret_cast<const uint4*>(job.res + job.res_plane_stride + rowoff * job.res_C + n0 + cb);
-#pragma unroll
-      for (int q4 = 0; q4 < 4; ++q4) {
-        const uint4 hv = __ldcg(rh + q4), lv = __ldcg(rl + q4);
-        const __half2* hh = reinterpret_cast<const __half2*>(&hv);
-        const __half2* ll = reinterpret_cast<const __half2*>(&lv);
-#pragma unroll
-        for (int w = 0; w < 4; ++w) {
-          const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
-          v[q4 * 8 + w * 2] += fh.x + fl.x;
-          v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
+        for (int e = 0; e < 8; ++e) {
+          const float4 t4 = __ldg(tb + e);
+          v[e * 4] += t4.x; v[e * 4 + 1] += t4.y; v[e * 4 + 2] += t4.z; v[e * 4 + 3] += t4.w;
         }
       }
-    }
-    if (job.out) {
-      uint4* oh = reinterpret_cast<uint4*>(job.out + rowoff * job.out_C + n0 + cb);
-      uint4* ol = reinterpret_cast<uint4*>(job.out + job.out_plane_stride + rowoff * job.out_C + n0 + cb);
+      if (job.res) {
+        // L2-coherent loads: inside the persistent kernel this data was written by another SM moments ago
+        const uint4* rh = reinterpret_cast<const uint4*>(job.res + rowoff * job.res_C + n0 + cb);
+        const uint4* rl = reinterpret_cast<const uint4*>(job.res + job.res_plane_stride + rowoff * job.res_C + n0 + cb);
 #pragma unroll
-      for (int q4 = 0; q4 < 4; ++q4) {
-        uint4 hv, lv;
-        __half2* hh = reinterpret_cast<__half2*>(&hv);
-        __half2* ll = reinterpret_cast<__half2*>(&lv);
+        for (int q4 = 0; q4 < 4; ++q4) {
+          const uint4 hv = __ldcg(rh + q4), lv = __ldcg(rl + q4);
+          const __half2* hh = reinterpret_cast<const __half2*>(&hv);
+          const __half2* ll = reinterpret_cast<const __half2*>(&lv);
 #pragma unroll
-        for (int w = 0; w < 4; ++w) {
-          __half h0, l0, h1, l1;
-          split_half(v[q4 * 8 + w * 2], h0, l0);
-          split_half(v[q4 * 8 + w * 2 + 1], h1, l1);
-          hh[w] = __halves2half2(h0, h1);
-          ll[w] = __halves2half2(l0, l1);
+          for (int w = 0; w < 4; ++w) {
+            const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
+            v[q4 * 8 + w * 2] += fh.x + fl.x;
+            v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
+          }
         }
-        oh[q4] = hv;
-        ol[q4] = lv;
       }
-    }
-    if (job.out_f32 && bg < job.B) {
-      float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
+      if (job.out) {
+        uint4* oh = reinterpret_cast<uint4*>(job.out + rowoff * job.out_C + n0 + cb);
+        uint4* ol = reinterpret_cast<uint4*>(job.out + job.out_plane_stride + rowoff * job.out_C + n0 + cb);
 #pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const int c = n0 + cb + e;
-        if (c < job.Cout) of[c] = v[e];
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint4 hv, lv;
+          __half2* hh = reinterpret_cast<__half2*>(&hv);
+          __half2* ll = reinterpret_cast<__half2*>(&lv);
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            __half h0, l0, h1, l1;
+            split_half(v[q4 * 8 + w * 2], h0, l0);
+            split_half(v[q4 * 8 + w * 2 + 1], h1, l1);
+            hh[w] = __halves2half2(h0, h1);
+            ll[w] = __halves2half2(l0, l1);
+          }
+          oh[q4] = hv;
+          ol[q4] = lv;
+        }
+      }
+      if (job.out_f32 && bg < job.B) {
+        float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          const int c = n0 + cb + e;
+          if (c < job.Cout) of[c] = v[e];
+        }
       }
     }
   }
+  trace_mark(tr, 11);
 }
 
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
-__device__ __forceinline__ void run_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map, int g,
-                                         int b0, int n0, const float* tbias, int tbias_stride, uint8_t* smem,
+__device__ __forceinline__ void run_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map, int warp,
+                                         int g, int b0, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
                                          unsigned long long* tr = nullptr) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint8_t* a_smem = smem;
-  uint8_t* w_smem = smem + (size_t)job.n_a_stages * job.a_stage_bytes;
+  const uint32_t a_smem = smem;
+  const uint32_t w_smem = smem + job.n_a_stages * job.a_stage_bytes;
   if (warp == kProducerWarp) {
-    if (lane == 0) producer_unit(job, a_maps, w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr);
-    __syncwarp();
+    producer_unit(job, a_maps, w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr);
   } else if (warp == kMmaWarp) {
-    if (lane == 0) mma_unit(job, a_smem, w_smem, sh, tmem_base, rs, tr);
-    __syncwarp();
+    mma_unit(job, a_smem, w_smem, sh, tmem_base, rs, tr);
   } else {
-    epilogue_unit(job, g, b0, n0, tbias, tbias_stride, sh, tmem_base, rs, tr);
+    epilogue_unit(job, warp, g, b0, n0, tbias, tbias_stride, sh, tmem_base, rs, tr);
   }
 }
 
-__device__ __forceinline__ uint8_t* align_smem(uint8_t* p) {
-  return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
+// 1024-byte aligned start of the dynamic shared memory, as a shared-window address (warp-uniform)
+__device__ __forceinline__ uint32_t aligned_dyn_smem() {
+  extern __shared__ uint8_t smem_raw[];
+  return (smem_u32(smem_raw) + 1023u) & ~1023u;
 }
 
 // ------------------------------------------------------------------------------------------------
 // per-layer launch: grid = (groups * 16/S, N slices)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kConvThreads, 1) conv_gemm_kernel(const __grid_constant__ ConvJob job) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = align_smem(smem_raw);
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvJob job) {
+  const uint32_t smem = aligned_dyn_smem();
   __shared__ ConvShared sh;
-  const int warp = threadIdx.x >> 5;
+  const int warp = warp_idx_sync();
   const int subs = kGroupSamples / job.S;
   if (threadIdx.x == 0) init_shared(sh);
-  if (warp == kProducerWarp && (threadIdx.x & 31) == 0) {
-    tma_prefetch_desc(&job.a_map[0]);
-    if (job.nsrc > 1) tma_prefetch_desc(&job.a_map[1]);
-    tma_prefetch_desc(&job.w_map);
+  if (warp == kProducerWarp && elect_one_sync()) {
+    tma_prefetch_desc(&maps.a_map[0]);
+    if (job.nsrc > 1) tma_prefetch_desc(&maps.a_map[1]);
+    tma_prefetch_desc(&maps.w_map);
   }
   if (warp == kMmaWarp) tmem_alloc(&sh.tmem_slot, job.tmem_cols);
   tc_fence_before();
@@ -368,7 +398,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_gemm_kernel(const __grid
   tc_fence_after();
   const uint32_t tmem_base = sh.tmem_slot;
   RoleState rs;
-  run_unit(job, &job.a_map[0], &job.w_map, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
+  run_unit(job, &maps.a_map[0], &maps.w_map, warp, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
            job.tbias, job.tbias_stride, smem, sh, tmem_base, rs);
   tc_fence_before();
   __syncthreads();
@@ -389,12 +419,10 @@ __device__ __forceinline__ void job_sync(bool wrote_global) {
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = align_smem(smem_raw);
+  const uint32_t smem = aligned_dyn_smem();
   __shared__ ConvShared sh;
-  __shared__ ConvJob sjob;
   __shared__ StepParams sstep;
-  const int warp = threadIdx.x >> 5;
+  const int warp = warp_idx_sync();
   const int rank = (int)cluster_ctarank();
   const int g = (int)cluster_id_x();
   if (threadIdx.x == 0) init_shared(sh);
@@ -413,26 +441,23 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
     if (k > 0) {
       const int t_index = lp.steps[k].t_index;
       for (int ji = 0; ji < lp.n_jobs; ++ji) {
+        const ConvJob& job = lp.jobs[ji];   // kernel-parameter (constant) space: warp-uniform
         unsigned long long* tr = (lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
                                      ? lp.trace + (size_t)ji * 16 : nullptr;
         if (threadIdx.x == 0) trace_mark(tr, 0);
-        {  // stage the layer descriptor in shared memory
-          const uint32_t* src = reinterpret_cast<const uint32_t*>(lp.jobs + ji);
-          uint32_t* dst = reinterpret_cast<uint32_t*>(&sjob);
-          for (int i = threadIdx.x; i < (int)(sizeof(ConvJob) / 4); i += kConvThreads) dst[i] = __ldg(src + i);
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) trace_mark(tr, 1);
-        const ConvJob& job = sjob;
-        const int slices = lp.slices[ji];
-        const int off = lp.tb_off[ji];
+        const int slices = job.slices;
+        const int off = job.tb_off;
         const float* tb = off >= 0 ? lp.tb_table + (size_t)t_index * lp.TB + off : nullptr;
-        const CUtensorMap* a_maps = &lp.jobs[ji].a_map[0];
-        const CUtensorMap* w_map = &lp.jobs[ji].w_map;
+        const CUtensorMap* a_maps = &lp.maps[ji].a_map[0];
+        const CUtensorMap* w_map = &lp.maps[ji].w_map;
+        if (warp == kProducerWarp && ji + 1 < lp.n_jobs && elect_one_sync()) {   // hide next layer's descriptor fetch
+          tma_prefetch_desc(&lp.maps[ji + 1].a_map[0]);
+          tma_prefetch_desc(&lp.maps[ji + 1].w_map);
+        }
         const int first = job.S == 8 ? 0 : rank, stride = job.S == 8 ? 1 : 2;
         const int b0 = job.S == 8 ? rank * 8 : 0;
         for (int sl = first; sl < slices; sl += stride) {
-          run_unit(job, a_maps, w_map, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr);
+          run_unit(job, a_maps, w_map, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr);
           if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit
             tc_fence_before();
             __syncthreads();
@@ -460,7 +485,8 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 }
 
-cudaError_t launch_conv_job(const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes, cudaStream_t stream) {
+cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes,
+                            cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
@@ -468,7 +494,7 @@ cudaError_t launch_conv_job(const ConvJob& job, int n_groups, int n_slices, size
     attr_set = true;
   }
   dim3 grid(n_groups * (kGroupSamples / job.S), n_slices);
-  conv_gemm_kernel<<<grid, kConvThreads, smem_bytes, stream>>>(job);
+  conv_gemm_kernel<<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
   return cudaGetLastError();
 }
 

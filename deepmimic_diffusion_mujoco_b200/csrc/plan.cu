@@ -11,7 +11,8 @@
 
 namespace dm {
 
-cudaError_t launch_conv_job(const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes, cudaStream_t stream);
+cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes,
+                            cudaStream_t stream);
 cudaError_t read_device_error(unsigned int* code);
 
 static thread_local char g_err[512] = "";
@@ -131,6 +132,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   Layer ly;
   ConvJob& j = ly.job;
   memset(&j, 0, sizeof(j));
+  memset(&ly.maps, 0, sizeof(ly.maps));
   ly.name = sp.name;
   ly.tb_off = sp.tb_off;
 
@@ -212,6 +214,8 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (gn && Nc % cg) return fail(DM_ERR_ARG, "%s: N slice does not hold whole GroupNorm groups", sp.name.c_str());
   j.Nc = Nc;
   ly.slices = cout_pad / Nc;
+  j.slices = ly.slices;
+  j.tb_off = sp.tb_off;
   int cols = 32;
   while (cols < j.nphase * mt_all * Nc) cols *= 2;
   j.tmem_cols = cols;
@@ -270,7 +274,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     const uint64_t dims[4] = {(uint64_t)cin_tot, (uint64_t)cout_pad, (uint64_t)ktaps, 2};
     const uint64_t str[3] = {(uint64_t)cin_tot * 2, (uint64_t)cin_tot * cout_pad * 2, (uint64_t)wplane * 2};
     const uint32_t box[4] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 2};
-    if ((rc = encode_map(&j.w_map, wdev, 4, dims, str, box, j.swz))) return rc;
+    if ((rc = encode_map(&ly.maps.w_map, wdev, 4, dims, str, box, j.swz))) return rc;
   }
   for (int s = 0; s < sp.nsrc; ++s) {
     const Act& a = P->acts[sp.src[s]];
@@ -278,7 +282,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     const uint64_t str[4] = {(uint64_t)a.C * 2, (uint64_t)a.C * 2 * kGroupSamples,
                              (uint64_t)a.C * 2 * kGroupSamples * a.L, (uint64_t)a.plane * 2};
     const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)j.S, (uint32_t)j.box_l, 1, 2};
-    if ((rc = encode_map(&j.a_map[s], a.p, 5, dims, str, box, j.swz))) return rc;
+    if ((rc = encode_map(&ly.maps.a_map[s], a.p, 5, dims, str, box, j.swz))) return rc;
   }
 
   // ---- epilogue parameters ----
@@ -516,21 +520,15 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
   if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->seed_dev), sizeof(unsigned long long)))) return rc;
   {
     const int n = (int)P->layers.size();
-    std::vector<ConvJob> jobs(n);
-    std::vector<int> slices(n), tboff(n);
+    if (n > kMaxLoopJobs) return fail(DM_ERR_ARG, "U-Net has %d layer launches; the fused loop supports %d", n, kMaxLoopJobs);
+    std::vector<ConvMaps> maps(n);
     P->loop_smem = 0;
     for (int i = 0; i < n; ++i) {
-      jobs[i] = P->layers[i].job;
-      slices[i] = P->layers[i].slices;
-      tboff[i] = P->layers[i].tb_off;
+      maps[i] = P->layers[i].maps;
       if (P->layers[i].smem > P->loop_smem) P->loop_smem = P->layers[i].smem;
     }
-    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->jobs_dev), n * sizeof(ConvJob), false))) return rc;
-    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->slices_dev), n * sizeof(int), false))) return rc;
-    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tboff_dev), n * sizeof(int), false))) return rc;
-    DM_CUDA(cudaMemcpy(P->jobs_dev, jobs.data(), n * sizeof(ConvJob), cudaMemcpyHostToDevice));
-    DM_CUDA(cudaMemcpy(P->slices_dev, slices.data(), n * sizeof(int), cudaMemcpyHostToDevice));
-    DM_CUDA(cudaMemcpy(P->tboff_dev, tboff.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->maps_dev), n * sizeof(ConvMaps), false))) return rc;
+    DM_CUDA(cudaMemcpy(P->maps_dev, maps.data(), n * sizeof(ConvMaps), cudaMemcpyHostToDevice));
   }
   if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tb_rows), (size_t)P->G * kGroupSamples * P->TB * sizeof(float))))
     return rc;
@@ -546,7 +544,7 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
       j.tbias_stride = tb_stride;
     }
     if (j.out_f32) j.out_f32 = out_f32;
-    DM_CUDA(launch_conv_job(j, P->G, ly.slices, ly.smem, s));
+    DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));
     P->last_launches++;
   }
   return DM_OK;
@@ -756,8 +754,10 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
     sp[k].chain = chain_dev; sp[k].chain_len = timesteps + 1; sp[k].chain_slot = k;
   }
   DM_CUDA(cudaMemcpyAsync(P->steps_dev, sp, (size_t)(timesteps + 1) * sizeof(StepParams), cudaMemcpyHostToDevice, s));
-  LoopParams lp;
-  lp.jobs = P->jobs_dev; lp.slices = P->slices_dev; lp.tb_off = P->tboff_dev; lp.n_jobs = (int)P->layers.size();
+  static thread_local LoopParams lp;   // ~19 KB: keep it off the stack
+  lp.n_jobs = (int)P->layers.size();
+  for (int i = 0; i < lp.n_jobs; ++i) lp.jobs[i] = P->layers[i].job;
+  lp.maps = P->maps_dev;
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
   lp.trace = P->trace_dev; lp.trace_cluster = P->trace_cluster; lp.trace_step = P->trace_step;

@@ -21,6 +21,7 @@ struct Act {
 
 struct Layer {
   ConvJob job;
+  ConvMaps maps;
   int slices = 1;
   size_t smem = 0;
   int tb_off = -1;       // offset into a time-bias row, or -1
@@ -54,9 +55,7 @@ struct dm_plan {
   unsigned long long rng_calls = 0;
   unsigned long long* seed_dev = nullptr;
   // persistent sampling-loop kernel arguments
-  dm::ConvJob* jobs_dev = nullptr;
-  int* slices_dev = nullptr;
-  int* tboff_dev = nullptr;
+  dm::ConvMaps* maps_dev = nullptr;
   size_t loop_smem = 0;
   dm::StepParams* steps_dev = nullptr;
   dm::StepParams* steps_host = nullptr;   // pinned staging

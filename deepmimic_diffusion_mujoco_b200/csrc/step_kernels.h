@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "conv_job.h"
+
 namespace dm {
 
 struct TimeMlpParams {
@@ -42,12 +44,11 @@ struct StepParams {
   long long n_elems;   // B*H*T (multiple of 4 because H % 8 == 0)
 };
 
-struct ConvJob;
 // Arguments of the persistent sampling-loop kernel (conv_kernel.cu).  All pointers are device pointers.
+// The whole block is a __grid_constant__ kernel parameter (~19 KB; CUDA >= 12.1 allows 32 KB).
 struct LoopParams {
-  const ConvJob* jobs;        // [n_jobs] layer descriptors (TMA maps inside), in execution order
-  const int* slices;          // [n_jobs] number of N slices of each layer
-  const int* tb_off;          // [n_jobs] offset of the layer's time bias inside a table row, or -1
+  ConvJob jobs[kMaxLoopJobs]; // layer descriptors in execution order (constant bank -> uniform registers)
+  const ConvMaps* maps;       // [n_jobs] TMA descriptors (global memory)
   int n_jobs;
   const StepParams* steps;    // [n_steps + 1]: entry 0 = init, entry k = k-th executed denoising step
   int n_steps;
