@@ -7,7 +7,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdm_b200.so")
+# DM_B200_LIB: developer override used to A/B two builds of the same library on one GPU box
+LIB_PATH = os.environ.get("DM_B200_LIB") or os.path.join(_HERE, "libdm_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 EXPORTS = [

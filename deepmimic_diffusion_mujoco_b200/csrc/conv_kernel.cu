@@ -29,10 +29,11 @@ namespace dm {
 
 __device__ __forceinline__ float mish_f(float x) {
   // x * tanh(softplus(x)) == x * n(n+2) / (n(n+2) + 2), n = e^x ; torch uses softplus threshold 20
-  if (x > 20.f) return x;
-  float n = __expf(x);
-  float a = n * (n + 2.f);
-  return x * __fdividef(a, a + 2.f);
+  // branch-free: for x > 20 the ratio rounds to 1 long before exp overflows (clamped at 30)
+  const float n = __expf(fminf(x, 30.f));
+  const float a = n * (n + 2.f);
+  const float r = x * __fdividef(a, a + 2.f);
+  return x > 20.f ? x : r;
 }
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -272,10 +273,10 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
     const int lrow = job.nphase == 2 ? 2 * j + ph : j;
     const size_t rowoff = ((size_t)g * job.Lout + lrow) * kGroupSamples + b0 + b;
     for (int cc = (slice - pt * nchunks) & 3; cc < nchunks; cc += 4) {
+      const int cb = cc * 32;
       tmem_ld32(trow + (uint32_t)(pt * Nc + cc * 32), v);
       tmem_ld_wait();
       if (!ok) continue;
-      const int cb = cc * 32;
       const uint2 gq = *reinterpret_cast<const uint2*>(&sh.qgrp[cc * 8]);
 #pragma unroll
       for (int r = 0; r < 8; ++r) {
@@ -306,7 +307,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
         }
       }
       if (job.res) {
-        // L2-coherent loads: inside the persistent kernel this data was written by another SM moments ago
+        // (L2-coherent loads: inside the persistent kernel this data was written by another SM moments ago)
         const uint4* rh = reinterpret_cast<const uint4*>(job.res + rowoff * job.res_C + n0 + cb);
         const uint4* rl = reinterpret_cast<const uint4*>(job.res + job.res_plane_stride + rowoff * job.res_C + n0 + cb);
 #pragma unroll
@@ -331,13 +332,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
           __half2* hh = reinterpret_cast<__half2*>(&hv);
           __half2* ll = reinterpret_cast<__half2*>(&lv);
 #pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            __half h0, l0, h1, l1;
-            split_half(v[q4 * 8 + w * 2], h0, l0);
-            split_half(v[q4 * 8 + w * 2 + 1], h1, l1);
-            hh[w] = __halves2half2(h0, h1);
-            ll[w] = __halves2half2(l0, l1);
-          }
+          for (int w = 0; w < 4; ++w) split_half2(v[q4 * 8 + w * 2], v[q4 * 8 + w * 2 + 1], hh[w], ll[w]);
           oh[q4] = hv;
           ol[q4] = lv;
         }
@@ -408,13 +403,13 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
 // ------------------------------------------------------------------------------------------------
 // persistent sampling loop: cluster c of 2 CTAs owns samples [16c, 16c+16)
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void job_sync(bool wrote_global) {
-  if (wrote_global) fence_proxy_async_all();   // generic-proxy stores -> visible to later TMA (async proxy) loads
+__device__ __forceinline__ void job_sync(bool wrote_global, bool issues_tma) {
+  if (wrote_global) fence_proxy_async_global();   // generic-proxy stores -> visible to later TMA (async proxy) loads
   tc_fence_before();
   __syncwarp();
   cluster_sync_all();
   tc_fence_after();
-  fence_proxy_async_all();
+  if (issues_tma) fence_proxy_async_global();
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
@@ -465,7 +460,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
           }
         }
         if (threadIdx.x == 0) trace_mark(tr, 12);
-        job_sync(warp < kEpiWarps);
+        job_sync(warp < kEpiWarps, warp == kProducerWarp);
         if (threadIdx.x == 0) trace_mark(tr, 13);
       }
     }
@@ -478,7 +473,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
     __syncthreads();
     if (warp < kEpiWarps && s_hi > s_lo)
       ddpm_step_range<true>(sstep, s_lo * ht4, s_hi * ht4, threadIdx.x, kEpiThreads);
-    job_sync(warp < kEpiWarps);
+    job_sync(warp < kEpiWarps, warp == kProducerWarp);
   }
   tc_fence_before();
   __syncthreads();

@@ -192,11 +192,20 @@ __device__ __forceinline__ void cluster_sync_all() {
 }
 // make this thread's generic-proxy writes (global and shared) visible to the async proxy (TMA)
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
 // split an fp32 value into fp16 hi + fp16 lo (hi + lo reproduces v to ~2^-22 relative)
 __device__ __forceinline__ void split_half(float v, __half& hi, __half& lo) {
   hi = __float2half_rn(v);
   lo = __float2half_rn(v - __half2float(hi));
+}
+
+// two values at once with the packed converter (cvt.rn.f16x2.f32 is a full-rate ALU op; the scalar
+// cvt.rn.f16.f32 goes through the XU pipe that Mish's ex2/rcp already saturate).  Same rounding as split_half.
+__device__ __forceinline__ void split_half2(float a, float b, __half2& hi, __half2& lo) {
+  hi = __floats2half2_rn(a, b);
+  const float2 hf = __half22float2(hi);
+  lo = __floats2half2_rn(a - hf.x, b - hf.y);
 }
 
 }  // namespace dm
