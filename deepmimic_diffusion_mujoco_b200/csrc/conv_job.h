@@ -34,6 +34,8 @@ enum { EPI_BIAS = 0, EPI_GN_MISH = 1 };
 struct ConvMaps {
   CUtensorMap a_map[2];   // 5-D (C, 16, L, G, plane) fp16, one per input source (2 = channel concat)
   CUtensorMap w_map;      // 4-D (CinTot, CoutPad, ntaps, plane) fp16
+  CUtensorMap o_map;      // 5-D store map of the output activation (box = one staged plane x channel block)
+  CUtensorMap r_map;      // 5-D load map of the residual activation, same box as o_map
 };
 
 // Plain-data layer descriptor.  It is always read from kernel-parameter (constant-bank) space, so every field
@@ -79,6 +81,12 @@ struct ConvJob {
   long long out_plane_stride;
   float* out_f32;         // public layout [B][Lout][out_f32_C]; null if none
   int out_f32_C;
+  // staged epilogue: the unit's output tile is assembled in shared memory (same swizzle as a TMA box) and
+  // written with TMA stores; the residual tile is TMA-loaded into the same buffer.  st_cw == 0: direct path.
+  int st_cw;              // channels per staged block (64 -> SWIZZLE_128B rows, 32 -> SWIZZLE_64B rows)
+  int st_nq;              // channel blocks per unit (Nc / st_cw)
+  int st_rows;            // rows (l, b) per block = nphase * n_ltiles * Mt * 128
+  int st_lbox;            // l extent of the store box = st_rows / S
   // fused-loop bookkeeping
   int slices;             // number of N slices (units per sample sub-group)
   int tb_off;             // offset of the layer's time bias inside a time-bias table row, or -1

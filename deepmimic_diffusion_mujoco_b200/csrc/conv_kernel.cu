@@ -53,7 +53,7 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 }
 
 struct ConvShared {
-  uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full;
+  uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full, res_full;
   uint32_t tmem_slot;
   alignas(16) float par[4][256];        // bias, gamma, beta, time bias of this unit's Nc channels
   alignas(16) unsigned char qgrp[64];   // GroupNorm group (within the unit) of every 4-channel quad
@@ -65,13 +65,14 @@ struct ConvShared {
 // used; producer and MMA issuer walk the same stage sequence, so their private copies stay in step even
 // though ring depths change from layer to layer inside the persistent kernel.
 struct RoleState {
-  uint32_t a_bits = 0, w_bits = 0, acc_count = 0;
+  uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0;
 };
 
 __device__ __forceinline__ void init_shared(ConvShared& sh) {
   for (int i = 0; i < 2; ++i) { mbar_init(&sh.a_full[i], 1); mbar_init(&sh.a_empty[i], 1); }
   for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], 1); }
   mbar_init(&sh.acc_full, 1);
+  mbar_init(&sh.res_full, 1);
   fence_barrier_init();
 }
 
@@ -180,9 +181,9 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t a_smem, ui
 // ================================ epilogue (warps 0..15) ===================================
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
-__device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int g, int b0, int n0, const float* tbias,
-                                              int tbias_stride, ConvShared& sh, uint32_t tmem_base, RoleState& rs,
-                                              unsigned long long* tr) {
+__device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps* maps, int warp, int g, int b0, int n0,
+                                              const float* tbias, int tbias_stride, uint32_t stg, ConvShared& sh,
+                                              uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
   const int lane = threadIdx.x & 31;
   const int tid = threadIdx.x;                 // 0..511
   if (tid != 0) tr = nullptr;
@@ -213,6 +214,22 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
   named_bar_sync(1, kEpiThreads);
   tc_fence_after();
   trace_mark(tr, 9);
+  // Staged epilogue: every MMA has completed, so the operand stages are dead and the unit's output tile is
+  // assembled there.  The residual tile (temporal.py:46) is TMA-loaded into the same buffer now; it lands
+  // while pass 1 runs.  Block (plane p, channel block q) lives at stg + (p * st_nq + q) * blk_bytes.
+  const bool staged = job.st_cw != 0;
+  const bool res_staged = staged && job.res != nullptr;
+  const uint32_t blk_bytes = (uint32_t)(job.st_rows * job.st_cw * 2);
+  if (res_staged) {
+    if (warp == 0 && elect_one_sync()) {
+      mbar_arrive_expect_tx(&sh.res_full, 2u * job.st_nq * blk_bytes);
+      for (int p = 0; p < 2; ++p)
+        for (int q = 0; q < job.st_nq; ++q)
+          tma_load_5d(stg + (uint32_t)(p * job.st_nq + q) * blk_bytes, &maps->r_map, &sh.res_full, n0 + q * job.st_cw, b0,
+                      0, g, p);
+    }
+    __syncwarp();
+  }
   const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
   const int nchunks = Nc >> 5;
   float v[32];
@@ -265,6 +282,13 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
   const float inv_n = 1.f / (float)(job.cg * job.Lj);
   const int bg = g * kGroupSamples + b0 + b;
   const int PT = job.nphase * MT;
+  if (res_staged) {
+    mbar_wait(&sh.res_full, rs.res_count & 1, 0x600);
+    rs.res_count++;
+  }
+  const int cw_shift = job.st_cw == 64 ? 6 : 5;
+  const uint32_t row_bytes = (uint32_t)job.st_cw * 2;
+  const uint32_t plane_bytes = (uint32_t)job.st_nq * blk_bytes;
   for (int pt = 0; pt < PT; ++pt) {
     const int ph = pt >= MT ? 1 : 0;
     const int T = pt - ph * MT;
@@ -306,6 +330,36 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
           v[e * 4] += t4.x; v[e * 4 + 1] += t4.y; v[e * 4 + 2] += t4.z; v[e * 4 + 3] += t4.w;
         }
       }
+      if (staged) {
+        // this thread's 64 B (hi) + 64 B (lo) of staged row srow; 16-byte slots XOR-swizzled like a TMA box
+        const int srow = lrow * S + b;
+        const uint32_t xr = job.st_cw == 64 ? (uint32_t)(srow & 7) : (uint32_t)((srow >> 1) & 3);
+        const uint32_t i0 = (uint32_t)(cb & (job.st_cw - 1)) >> 3;
+        const uint32_t base = stg + (uint32_t)(cb >> cw_shift) * blk_bytes + (uint32_t)srow * row_bytes;
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          const uint32_t a_hi = base + (((i0 + q4) ^ xr) << 4);
+          const uint32_t a_lo = a_hi + plane_bytes;
+          if (res_staged) {
+            const uint4 hv = lds128(a_hi), lv = lds128(a_lo);
+            const __half2* hh = reinterpret_cast<const __half2*>(&hv);
+            const __half2* ll = reinterpret_cast<const __half2*>(&lv);
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+              const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
+              v[q4 * 8 + w * 2] += fh.x + fl.x;
+              v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
+            }
+          }
+          uint4 hv, lv;
+          __half2* hh = reinterpret_cast<__half2*>(&hv);
+          __half2* ll = reinterpret_cast<__half2*>(&lv);
+#pragma unroll
+          for (int w = 0; w < 4; ++w) split_half2(v[q4 * 8 + w * 2], v[q4 * 8 + w * 2 + 1], hh[w], ll[w]);
+          sts128(a_hi, hv);
+          sts128(a_lo, lv);
+        }
+      } else {
       if (job.res) {
         // (L2-coherent loads: inside the persistent kernel this data was written by another SM moments ago)
         const uint4* rh = reinterpret_cast<const uint4*>(job.res + rowoff * job.res_C + n0 + cb);
@@ -337,6 +391,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
           ol[q4] = lv;
         }
       }
+      }
       if (job.out_f32 && bg < job.B) {
         float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
 #pragma unroll
@@ -347,22 +402,34 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, int warp, int 
       }
     }
   }
+  if (staged) {
+    fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine
+    named_bar_sync(1, kEpiThreads);
+    if (warp == 0 && elect_one_sync()) {
+      for (int p = 0; p < 2; ++p)
+        for (int q = 0; q < job.st_nq; ++q)
+          tma_store_5d(&maps->o_map, stg + (uint32_t)(p * job.st_nq + q) * blk_bytes, n0 + q * job.st_cw, b0, 0, g, p);
+      tma_store_commit();
+      tma_store_wait_all();               // staging is reused by the next unit's loads; writes must be performed
+    }
+    __syncwarp();
+  }
   trace_mark(tr, 11);
 }
 
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
-__device__ __forceinline__ void run_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map, int warp,
+__device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp,
                                          int g, int b0, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
                                          unsigned long long* tr = nullptr) {
   const uint32_t a_smem = smem;
   const uint32_t w_smem = smem + job.n_a_stages * job.a_stage_bytes;
   if (warp == kProducerWarp) {
-    producer_unit(job, a_maps, w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr);
+    producer_unit(job, &maps->a_map[0], &maps->w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr);
   } else if (warp == kMmaWarp) {
     mma_unit(job, a_smem, w_smem, sh, tmem_base, rs, tr);
   } else {
-    epilogue_unit(job, warp, g, b0, n0, tbias, tbias_stride, sh, tmem_base, rs, tr);
+    epilogue_unit(job, maps, warp, g, b0, n0, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
 }
 
@@ -393,7 +460,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = sh.tmem_slot;
   RoleState rs;
-  run_unit(job, &maps.a_map[0], &maps.w_map, warp, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
+  run_unit(job, &maps, warp, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
            job.tbias, job.tbias_stride, smem, sh, tmem_base, rs);
   tc_fence_before();
   __syncthreads();
@@ -443,8 +510,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         const int slices = job.slices;
         const int off = job.tb_off;
         const float* tb = off >= 0 ? lp.tb_table + (size_t)t_index * lp.TB + off : nullptr;
-        const CUtensorMap* a_maps = &lp.maps[ji].a_map[0];
-        const CUtensorMap* w_map = &lp.maps[ji].w_map;
+        const ConvMaps* maps = &lp.maps[ji];
         if (warp == kProducerWarp && ji + 1 < lp.n_jobs && elect_one_sync()) {   // hide next layer's descriptor fetch
           tma_prefetch_desc(&lp.maps[ji + 1].a_map[0]);
           tma_prefetch_desc(&lp.maps[ji + 1].w_map);
@@ -452,7 +518,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         const int first = job.S == 8 ? 0 : rank, stride = job.S == 8 ? 1 : 2;
         const int b0 = job.S == 8 ? rank * 8 : 0;
         for (int sl = first; sl < slices; sl += stride) {
-          run_unit(job, a_maps, w_map, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr);
+          run_unit(job, maps, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr);
           if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit
             tc_fence_before();
             __syncthreads();

@@ -327,6 +327,36 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     j.out_f32 = P->model_out;
     j.out_f32_C = sp.Cout;
   }
+  // ---- staged epilogue (TMA store of the output tile, TMA load of the residual tile) ----
+  j.st_cw = 0;
+  if (sp.want_act_out) {
+    const int rows = j.nphase * mt_all * 128;
+    const int lbox = rows / j.S;
+    const size_t st_bytes = (size_t)4 * rows * Nc;
+    if (lbox <= 256 && st_bytes + 1024 <= (size_t)budget + 1024) {
+      j.st_cw = Nc % 64 == 0 ? 64 : 32;
+      j.st_nq = Nc / j.st_cw;
+      j.st_rows = rows;
+      j.st_lbox = lbox;
+      if (ly.smem < st_bytes + 1024) ly.smem = st_bytes + 1024;
+      const int st_swz = j.st_cw == 64 ? 2 : 4;
+      const uint32_t box[5] = {(uint32_t)j.st_cw, (uint32_t)j.S, (uint32_t)lbox, 1, 1};
+      {
+        const Act& o = P->acts[ly.out_act];
+        const uint64_t dims[5] = {(uint64_t)o.C, kGroupSamples, (uint64_t)o.L, (uint64_t)P->G, 2};
+        const uint64_t str[4] = {(uint64_t)o.C * 2, (uint64_t)o.C * 2 * kGroupSamples,
+                                 (uint64_t)o.C * 2 * kGroupSamples * o.L, (uint64_t)o.plane * 2};
+        if ((rc = encode_map(&ly.maps.o_map, o.p, 5, dims, str, box, st_swz))) return rc;
+      }
+      if (sp.res >= 0) {
+        const Act& r = P->acts[sp.res];
+        const uint64_t dims[5] = {(uint64_t)r.C, kGroupSamples, (uint64_t)r.L, (uint64_t)P->G, 2};
+        const uint64_t str[4] = {(uint64_t)r.C * 2, (uint64_t)r.C * 2 * kGroupSamples,
+                                 (uint64_t)r.C * 2 * kGroupSamples * r.L, (uint64_t)r.plane * 2};
+        if ((rc = encode_map(&ly.maps.r_map, r.p, 5, dims, str, box, st_swz))) return rc;
+      }
+    }
+  }
   P->layers.push_back(ly);
   return DM_OK;
 }
