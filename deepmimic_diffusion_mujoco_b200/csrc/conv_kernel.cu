@@ -28,12 +28,11 @@
 namespace dm {
 
 __device__ __forceinline__ float mish_f(float x) {
-  // x * tanh(softplus(x)) == x * n(n+2) / (n(n+2) + 2), n = e^x ; torch uses softplus threshold 20
-  // branch-free: for x > 20 the ratio rounds to 1 long before exp overflows (clamped at 30)
+  // x * tanh(softplus(x)) == x * a / (a + 2), a = n (n + 2), n = e^x.  torch switches softplus to the identity
+  // above 20; here the ratio already rounds to 1 there (a > 2^57), and the clamp keeps n finite.
   const float n = __expf(fminf(x, 30.f));
   const float a = n * (n + 2.f);
-  const float r = x * __fdividef(a, a + 2.f);
-  return x > 20.f ? x : r;
+  return x * __fdividef(a, a + 2.f);
 }
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -57,8 +56,10 @@ struct ConvShared {
   uint32_t tmem_slot;
   alignas(16) float par[4][256];        // bias, gamma, beta, time bias of this unit's Nc channels
   alignas(16) unsigned char qgrp[64];   // GroupNorm group (within the unit) of every 4-channel quad
-  float stat[16][8][2];                 // per (sample, group): sum, sum of squares
-  float part[kEpiWarps][16][8][2];      // per-warp partials, combined in a fixed order (deterministic)
+  float stat[16][8][2];                 // per (sample, group): mean, rstd
+  // per-warp partial sums [warp][sample][group][2], combined in a fixed order (deterministic); after the
+  // combine the same storage holds the per-(sample, channel) GroupNorm scale/shift table (kTabStride floats/row)
+  alignas(16) float part[kEpiWarps * 256 + 64];   // table row = 2 * Nc floats + 4 floats of bank skew, Nc <= 128
 };
 
 // Parity bookkeeping of the mbarrier rings.  Bit s of a mask = parity of the number of times stage s has been
@@ -204,8 +205,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   }
   if (tid < (Nc >> 2)) sh.qgrp[tid] = (unsigned char)((tid * 4) / job.cg);
   if (gn) {
-    float* pp = &sh.part[0][0][0][0];
-    for (int i = tid; i < kEpiWarps * 256; i += kEpiThreads) pp[i] = 0.f;
+    for (int i = tid; i < kEpiWarps * 256; i += kEpiThreads) sh.part[i] = 0.f;
   }
   trace_mark(tr, 8);
   // one warp waits for the accumulator; everybody else parks on the hardware barrier (no issue slots burnt)
@@ -260,26 +260,48 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
           }
           if (lane < S) {
             const int gi = (int)(((r < 4 ? gq.x : gq.y) >> ((r & 3) * 8)) & 0xff);   // fixed (u, r) order: deterministic
-            sh.part[warp][lane][gi][0] += s[r];
-            sh.part[warp][lane][gi][1] += q[r];
+            float2* pp = reinterpret_cast<float2*>(&sh.part[((warp * 16 + lane) * 8 + gi) * 2]);
+            float2 acc = *pp;
+            acc.x += s[r];
+            acc.y += q[r];
+            *pp = acc;
           }
         }
       }
     }
     named_bar_sync(1, kEpiThreads);
-    if (tid < 256) {
-      const float* pp = &sh.part[0][0][0][0];
-      float a = 0.f;
+    if (tid < 128) {                       // one thread per (sample, group): fixed-order sum over the warps
+      float a = 0.f, q2 = 0.f;
 #pragma unroll
-      for (int w = 0; w < kEpiWarps; ++w) a += pp[w * 256 + tid];
-      (&sh.stat[0][0][0])[tid] = a;
+      for (int w = 0; w < kEpiWarps; ++w) {
+        const float2 pv = *reinterpret_cast<const float2*>(&sh.part[(w * 128 + tid) * 2]);
+        a += pv.x;
+        q2 += pv.y;
+      }
+      const float inv_n = 1.f / (float)(job.cg * job.Lj);
+      const float mean = a * inv_n;
+      const float var = fmaxf(q2 * inv_n - mean * mean, 0.f);
+      (&sh.stat[0][0][0])[tid * 2] = mean;
+      (&sh.stat[0][0][0])[tid * 2 + 1] = rsqrtf(var + 1e-5f);
+    }
+    named_bar_sync(1, kEpiThreads);
+    // scale/shift table: y = x * sc + sf with sc = rstd * gamma, sf = (bias - mean) * sc + beta
+    const int tab_stride = 2 * Nc + 4;
+    for (int e = tid; e < S * Nc; e += kEpiThreads) {
+      const int bb = e / Nc, c = e - bb * Nc;
+      const int gi = c / job.cg;
+      const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
+      const float sc = st.y * sh.par[1][c];
+      float2 o;
+      o.x = sc;
+      o.y = fmaf(sh.par[0][c] - st.x, sc, sh.par[2][c]);
+      *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
     }
     named_bar_sync(1, kEpiThreads);
   }
   trace_mark(tr, 10);
 
   // ---- pass 2: normalise, Mish, + time bias, + residual, split to fp16 hi/lo, store ----
-  const float inv_n = 1.f / (float)(job.cg * job.Lj);
   const int bg = g * kGroupSamples + b0 + b;
   const int PT = job.nphase * MT;
   if (res_staged) {
@@ -301,26 +323,24 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       tmem_ld32(trow + (uint32_t)(pt * Nc + cc * 32), v);
       tmem_ld_wait();
       if (!ok) continue;
-      const uint2 gq = *reinterpret_cast<const uint2*>(&sh.qgrp[cc * 8]);
+      if (gn) {
+        const float* trow_tab = &sh.part[b * (2 * Nc + 4) + 2 * cb];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
-        float x[4] = {v[r * 4] + bi.x, v[r * 4 + 1] + bi.y, v[r * 4 + 2] + bi.z, v[r * 4 + 3] + bi.w};
-        if (gn) {
-          const int gi = (int)(((r < 4 ? gq.x : gq.y) >> ((r & 3) * 8)) & 0xff);
-          const float2 st = *reinterpret_cast<const float2*>(&sh.stat[b][gi][0]);
-          const float mean = st.x * inv_n;
-          const float var = fmaxf(st.y * inv_n - mean * mean, 0.f);
-          const float rstd = rsqrtf(var + 1e-5f);
-          const float4 ga = *reinterpret_cast<const float4*>(&sh.par[1][cb + r * 4]);
-          const float4 be = *reinterpret_cast<const float4*>(&sh.par[2][cb + r * 4]);
+        for (int r = 0; r < 8; ++r) {
+          const float4 s01 = *reinterpret_cast<const float4*>(trow_tab + r * 8);
+          const float4 s23 = *reinterpret_cast<const float4*>(trow_tab + r * 8 + 4);
           const float4 tb = *reinterpret_cast<const float4*>(&sh.par[3][cb + r * 4]);
-          x[0] = mish_f(fmaf((x[0] - mean) * rstd, ga.x, be.x)) + tb.x;
-          x[1] = mish_f(fmaf((x[1] - mean) * rstd, ga.y, be.y)) + tb.y;
-          x[2] = mish_f(fmaf((x[2] - mean) * rstd, ga.z, be.z)) + tb.z;
-          x[3] = mish_f(fmaf((x[3] - mean) * rstd, ga.w, be.w)) + tb.w;
+          v[r * 4] = mish_f(fmaf(v[r * 4], s01.x, s01.y)) + tb.x;
+          v[r * 4 + 1] = mish_f(fmaf(v[r * 4 + 1], s01.z, s01.w)) + tb.y;
+          v[r * 4 + 2] = mish_f(fmaf(v[r * 4 + 2], s23.x, s23.y)) + tb.z;
+          v[r * 4 + 3] = mish_f(fmaf(v[r * 4 + 3], s23.z, s23.w)) + tb.w;
         }
-        v[r * 4] = x[0]; v[r * 4 + 1] = x[1]; v[r * 4 + 2] = x[2]; v[r * 4 + 3] = x[3];
+      } else {
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
+          v[r * 4] += bi.x; v[r * 4 + 1] += bi.y; v[r * 4 + 2] += bi.z; v[r * 4 + 3] += bi.w;
+        }
       }
       if (gn && tbias != nullptr && tbias_stride != 0) {
         const float4* tb = reinterpret_cast<const float4*>(tbias + (size_t)bg * tbias_stride + n0 + cb);
