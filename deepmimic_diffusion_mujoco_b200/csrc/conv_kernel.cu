@@ -422,9 +422,11 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       }
     }
   }
+  trace_mark(tr, 14);
   if (staged) {
     fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine
     named_bar_sync(1, kEpiThreads);
+    trace_mark(tr, 15);
     if (warp == 0 && elect_one_sync()) {
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)

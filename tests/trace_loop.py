@@ -21,13 +21,13 @@ for _ in range(2):
 torch.cuda.synchronize()
 t = tr.cpu().numpy().astype("float64")
 t0 = t[0, 0]
-ev = ["start", "jobcp", "prod0", "A_iss", "prodE", "A_arr", "W_arr", "mmaIs", "epi0", "accF", "pass1", "pass2", "unitE", "sync"]
+ev = ["start", "jobcp", "prod0", "A_iss", "prodE", "A_arr", "W_arr", "mmaIs", "epi0", "accF", "pass1", "pass2", "unitE", "sync", "p2loop", "p2bar"]
 print("layer".ljust(28), " ".join(e.rjust(6) for e in ev), "  total_us")
 tot = 0
 for i, (n, C, L) in enumerate(names):
     r = t[i]
     base = r[0]
-    vals = [(r[k] - base) / 1e3 if r[k] > 0 else float("nan") for k in range(14)]
+    vals = [(r[k] - base) / 1e3 if r[k] > 0 else float("nan") for k in range(16)]
     print(f"{n[:27]:28s}", " ".join(f"{v:6.1f}" for v in vals), f"  {(r[13]-r[0])/1e3:7.1f}")
     tot += r[13] - r[0]
 print("sum of layers us", tot / 1e3, " step span us", (t[-1, 13] - t[0, 0]) / 1e3)
