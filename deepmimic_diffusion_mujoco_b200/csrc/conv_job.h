@@ -87,11 +87,22 @@ struct ConvJob {
   int st_nq;              // channel blocks per unit (Nc / st_cw)
   int st_rows;            // rows (l, b) per block = nphase * n_ltiles * Mt * 128
   int st_lbox;            // l extent of the store box = st_rows / S
+  int st_blk_stride;      // bytes between staged blocks: kStageGap zero rows | st_rows data rows | kStageGap zero rows
+  // resident links (fused loop only): when the next layer's only input is this CTA's staged output tile, the
+  // tile stays in shared memory (zero halo gaps around each block) and is read in place by the next layer's
+  // MMAs: no TMA round trip through L2, no cluster barrier, and the TMA store of the tile is not waited for.
+  int a_res;              // this layer's A operand is the previous layer's staged tile
+  int a_res_off;          // byte offset (from the smem base) of chunk 0 / plane 0 of the A view (row l = -halo_lo)
+  int a_res_chunk;        // bytes between channel chunks of the resident tile
+  int a_res_plane;        // bytes between the hi and lo planes of the resident tile
+  int w_off_res;          // weight ring offset when a_res (beyond every staged tile)
+  int next_res;           // the next layer reads this layer's staged tile in place (zero the gaps, defer the store wait)
   // fused-loop bookkeeping
   int slices;             // number of N slices (units per sample sub-group)
   int tb_off;             // offset of the layer's time bias inside a time-bias table row, or -1
 };
 
+constexpr int kStageGap = 2048;    // bytes of zero rows before and after every staged block (conv halo)
 constexpr int kMaxLoopJobs = 80;   // layers of one U-Net inside the fused-loop kernel parameter block
 
 }  // namespace dm

@@ -90,12 +90,14 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
     for (int src = 0; src < job.nsrc; ++src) {
       const int nch = job.src_chunks[src];
       for (int ch = 0; ch < nch; ++ch) {
-        mbar_wait(&sh.a_empty[as], ((rs.a_bits >> as) & 1) ^ 1, 0x100 + as);
-        if (leader) {
-          mbar_arrive_expect_tx(&sh.a_full[as], job.a_tx_bytes);
-          tma_load_5d(a_smem + as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
+        if (!job.a_res) {
+          mbar_wait(&sh.a_empty[as], ((rs.a_bits >> as) & 1) ^ 1, 0x100 + as);
+          if (leader) {
+            mbar_arrive_expect_tx(&sh.a_full[as], job.a_tx_bytes);
+            tma_load_5d(a_smem + as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
+          }
+          rs.a_bits ^= 1u << as;
         }
-        rs.a_bits ^= 1u << as;
         for (int t = 0; t < job.ntaps; ++t) {
           mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
           if (leader) {
@@ -106,7 +108,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
           rs.w_bits ^= 1u << ws;
           if (++ws == job.n_w_stages) ws = 0;
         }
-        if (++as == job.n_a_stages) as = 0;
+        if (!job.a_res && ++as == job.n_a_stages) as = 0;
       }
       cin_off += nch * job.Cc;
     }
@@ -116,8 +118,8 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
 }
 
 // ================================ MMA issuer (one warp, one elected lane issues) ===========================
-__device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
-                                         uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
+__device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
+                                         ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
   const bool leader = elect_one_sync();
   const int S = job.S, Nc = job.Nc;
   const int MT = job.n_ltiles * job.Mt;
@@ -127,7 +129,8 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t a_smem, ui
   // descriptor high words are per-layer constants; only the 14-bit start address changes per MMA
   const uint64_t hi_a = umma_smem_desc(0, job.l_stride * 8 * job.row_bytes, job.swz);
   const uint64_t hi_w = umma_smem_desc(0, 8 * job.row_bytes, job.swz);
-  const uint32_t a_plane16 = job.a_plane_bytes >> 4, w_plane16 = job.w_plane_bytes >> 4;
+  const uint32_t a_plane16 = (uint32_t)(job.a_res ? job.a_res_plane : job.a_plane_bytes) >> 4;
+  const uint32_t w_plane16 = job.w_plane_bytes >> 4;
   const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
   int as = 0, ws = 0;
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
@@ -135,11 +138,14 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t a_smem, ui
     for (int src = 0; src < job.nsrc; ++src) {
       const int nch = job.src_chunks[src];
       for (int ch = 0; ch < nch; ++ch, ++cidx) {
-        mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
-        rs.a_bits ^= 1u << as;
-        tc_fence_after();
+        if (!job.a_res) {
+          mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
+          rs.a_bits ^= 1u << as;
+          tc_fence_after();
+        }
         if (leader && lt == 0 && cidx == 0) trace_mark(tr, 5);
-        const uint32_t a_base16 = (a_smem + as * job.a_stage_bytes) >> 4;
+        const uint32_t a_base16 =
+            (job.a_res ? smem_base + (uint32_t)(job.a_res_off + cidx * job.a_res_chunk) : a_smem + as * job.a_stage_bytes) >> 4;
         for (int t = 0; t < job.ntaps; ++t) {
           mbar_wait(&sh.w_full[ws], (rs.w_bits >> ws) & 1, 0x400 + ws);
           rs.w_bits ^= 1u << ws;
@@ -167,8 +173,10 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t a_smem, ui
           if (leader) umma_commit(&sh.w_empty[ws]);
           if (++ws == job.n_w_stages) ws = 0;
         }
-        if (leader) umma_commit(&sh.a_empty[as]);
-        if (++as == job.n_a_stages) as = 0;
+        if (!job.a_res) {
+          if (leader) umma_commit(&sh.a_empty[as]);
+          if (++as == job.n_a_stages) as = 0;
+        }
       }
     }
   }
@@ -208,6 +216,8 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     for (int i = tid; i < kEpiWarps * 256; i += kEpiThreads) sh.part[i] = 0.f;
   }
   trace_mark(tr, 8);
+  // The previous layer's TMA store may still be reading the staging buffer (deferred wait of a resident link).
+  if (tid == 0) tma_store_wait_read();
   // one warp waits for the accumulator; everybody else parks on the hardware barrier (no issue slots burnt)
   if (warp == kPollWarp) mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x500);
   rs.acc_count++;
@@ -216,17 +226,20 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   trace_mark(tr, 9);
   // Staged epilogue: every MMA has completed, so the operand stages are dead and the unit's output tile is
   // assembled there.  The residual tile (temporal.py:46) is TMA-loaded into the same buffer now; it lands
-  // while pass 1 runs.  Block (plane p, channel block q) lives at stg + (p * st_nq + q) * blk_bytes.
+  // while pass 1 runs.  Block (plane p, channel block q) = kStageGap zero bytes | st_rows rows | kStageGap zero
+  // bytes at stg + (p * st_nq + q) * st_blk_stride; the gaps are the conv halo of a resident consumer.
   const bool staged = job.st_cw != 0;
   const bool res_staged = staged && job.res != nullptr;
   const uint32_t blk_bytes = (uint32_t)(job.st_rows * job.st_cw * 2);
+  const uint32_t blk_stride = (uint32_t)job.st_blk_stride;
+  const uint32_t stg_data = stg + kStageGap;
   if (res_staged) {
-    if (warp == 0 && elect_one_sync()) {
+    if (tid == 0) {
       mbar_arrive_expect_tx(&sh.res_full, 2u * job.st_nq * blk_bytes);
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
-          tma_load_5d(stg + (uint32_t)(p * job.st_nq + q) * blk_bytes, &maps->r_map, &sh.res_full, n0 + q * job.st_cw, b0,
-                      0, g, p);
+          tma_load_5d(stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, &maps->r_map, &sh.res_full,
+                      n0 + q * job.st_cw, b0, 0, g, p);
     }
     __syncwarp();
   }
@@ -310,7 +323,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   }
   const int cw_shift = job.st_cw == 64 ? 6 : 5;
   const uint32_t row_bytes = (uint32_t)job.st_cw * 2;
-  const uint32_t plane_bytes = (uint32_t)job.st_nq * blk_bytes;
+  const uint32_t plane_bytes = (uint32_t)job.st_nq * blk_stride;
   for (int pt = 0; pt < PT; ++pt) {
     const int ph = pt >= MT ? 1 : 0;
     const int T = pt - ph * MT;
@@ -355,7 +368,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         const int srow = lrow * S + b;
         const uint32_t xr = job.st_cw == 64 ? (uint32_t)(srow & 7) : (uint32_t)((srow >> 1) & 3);
         const uint32_t i0 = (uint32_t)(cb & (job.st_cw - 1)) >> 3;
-        const uint32_t base = stg + (uint32_t)(cb >> cw_shift) * blk_bytes + (uint32_t)srow * row_bytes;
+        const uint32_t base = stg_data + (uint32_t)(cb >> cw_shift) * blk_stride + (uint32_t)srow * row_bytes;
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4) {
           const uint32_t a_hi = base + (((i0 + q4) ^ xr) << 4);
@@ -424,15 +437,29 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   }
   trace_mark(tr, 14);
   if (staged) {
-    fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine
+    if (job.next_res) {
+      // zero the halo gaps of every block (other layers' operand stages alias this memory)
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      const int per_blk = 2 * kStageGap / 16;
+      for (int i = tid; i < 2 * job.st_nq * per_blk; i += kEpiThreads) {
+        const int blk = i / per_blk, o = i - blk * per_blk;
+        const uint32_t off = o < kStageGap / 16 ? (uint32_t)o * 16u : kStageGap + blk_bytes + (uint32_t)(o - kStageGap / 16) * 16u;
+        sts128(stg + (uint32_t)blk * blk_stride + off, z);
+      }
+    }
+    fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine / next MMAs
     named_bar_sync(1, kEpiThreads);
     trace_mark(tr, 15);
-    if (warp == 0 && elect_one_sync()) {
+    if (tid == 0) {
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
-          tma_store_5d(&maps->o_map, stg + (uint32_t)(p * job.st_nq + q) * blk_bytes, n0 + q * job.st_cw, b0, 0, g, p);
+          tma_store_5d(&maps->o_map, stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0, 0,
+                       g, p);
       tma_store_commit();
-      tma_store_wait_all();               // staging is reused by the next unit's loads; writes must be performed
+      // a non-resident consumer TMA-loads this tile from global, and the staging is reused by the next unit's
+      // operand loads: the store must be complete.  A resident consumer reads shared memory; the wait moves
+      // to its own epilogue (tma_store_wait_read above).
+      if (!job.next_res) tma_store_wait_all();
     }
     __syncwarp();
   }
@@ -445,11 +472,11 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
                                          unsigned long long* tr = nullptr) {
   const uint32_t a_smem = smem;
-  const uint32_t w_smem = smem + job.n_a_stages * job.a_stage_bytes;
+  const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
   if (warp == kProducerWarp) {
     producer_unit(job, &maps->a_map[0], &maps->w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr);
   } else if (warp == kMmaWarp) {
-    mma_unit(job, a_smem, w_smem, sh, tmem_base, rs, tr);
+    mma_unit(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr);
   } else {
     epilogue_unit(job, maps, warp, g, b0, n0, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
@@ -548,7 +575,13 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
           }
         }
         if (threadIdx.x == 0) trace_mark(tr, 12);
-        job_sync(warp < kEpiWarps, warp == kProducerWarp);
+        if (job.next_res) {   // CTA-local hand-over of the staged tile (writers fenced the async proxy already)
+          tc_fence_before();
+          __syncthreads();
+          tc_fence_after();
+        } else {
+          job_sync(warp < kEpiWarps && job.st_cw == 0, warp == kProducerWarp);
+        }
         if (threadIdx.x == 0) trace_mark(tr, 13);
       }
     }
@@ -563,6 +596,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
       ddpm_step_range<true>(sstep, s_lo * ht4, s_hi * ht4, threadIdx.x, kEpiThreads);
     job_sync(warp < kEpiWarps, warp == kProducerWarp);
   }
+  if (threadIdx.x == 0) tma_store_wait_all();
   tc_fence_before();
   __syncthreads();
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);

@@ -5,6 +5,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/dm_b200.h"
@@ -329,15 +330,19 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   }
   // ---- staged epilogue (TMA store of the output tile, TMA load of the residual tile) ----
   j.st_cw = 0;
+  size_t st_bytes = 0;
   if (sp.want_act_out) {
     const int rows = j.nphase * mt_all * 128;
     const int lbox = rows / j.S;
-    const size_t st_bytes = (size_t)4 * rows * Nc;
-    if (lbox <= 256 && st_bytes + 1024 <= (size_t)budget + 1024) {
-      j.st_cw = Nc % 64 == 0 ? 64 : 32;
-      j.st_nq = Nc / j.st_cw;
+    const int cw = Nc % 64 == 0 ? 64 : 32;
+    const int blk_stride = rows * cw * 2 + 2 * kStageGap;
+    st_bytes = (size_t)2 * (Nc / cw) * blk_stride;
+    if (lbox <= 256 && st_bytes <= (size_t)budget) {
+      j.st_cw = cw;
+      j.st_nq = Nc / cw;
       j.st_rows = rows;
       j.st_lbox = lbox;
+      j.st_blk_stride = blk_stride;
       if (ly.smem < st_bytes + 1024) ly.smem = st_bytes + 1024;
       const int st_swz = j.st_cw == 64 ? 2 : 4;
       const uint32_t box[5] = {(uint32_t)j.st_cw, (uint32_t)j.S, (uint32_t)lbox, 1, 1};
@@ -354,6 +359,34 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
         const uint64_t str[4] = {(uint64_t)r.C * 2, (uint64_t)r.C * 2 * kGroupSamples,
                                  (uint64_t)r.C * 2 * kGroupSamples * r.L, (uint64_t)r.plane * 2};
         if ((rc = encode_map(&ly.maps.r_map, r.p, 5, dims, str, box, st_swz))) return rc;
+      }
+    } else {
+      st_bytes = 0;
+    }
+  }
+  // ---- resident link: read the previous layer's staged tile in place (fused loop only) ----
+  if (!P->layers.empty() && !getenv("DM_B200_NO_RESIDENT")) {
+    Layer& pv = P->layers.back();
+    const ConvJob& pj = pv.job;
+    const int halo_hi_rows = (j.box_l - j.halo_lo - Lin) * j.S;
+    const bool ok = pj.st_cw != 0 && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
+                    ly.slices == 1 && pj.st_cw == j.Cc && j.src_chunks[0] == pj.st_nq && j.n_ltiles == 1 &&
+                    pj.Lout * pj.S == pj.st_rows && j.halo_lo * j.S * j.row_bytes <= kStageGap &&
+                    halo_hi_rows * j.row_bytes <= kStageGap;
+    if (ok) {
+      const int pv_bytes = 2 * pj.st_nq * pj.st_blk_stride;
+      const int w_off = round_up(pv_bytes, 1024);
+      int nwr = (budget - w_off) / j.w_stage_bytes;
+      if (nwr >= 1) {
+        if (nwr < j.n_w_stages) j.n_w_stages = nwr;
+        j.a_res = 1;
+        j.a_res_off = kStageGap - j.halo_lo * j.S * j.row_bytes;
+        j.a_res_chunk = pj.st_blk_stride;
+        j.a_res_plane = pj.st_nq * pj.st_blk_stride;
+        j.w_off_res = w_off;
+        pv.job.next_res = 1;
+        const size_t need = (size_t)w_off + (size_t)j.n_w_stages * j.w_stage_bytes + 1024;
+        if (ly.smem < need) ly.smem = need;
       }
     }
   }
@@ -374,17 +407,8 @@ struct BlockOut { int act; };
 static int add_resblock(dm_plan* P, const WeightMap& W, const std::string& key, const int* src, const int* src_real,
                         int nsrc, int cin_real, int Cout, int* tb_cursor, int* out_act) {
   int rc, mid = -1, res = -1, out = -1;
-  ConvSpec c0;
-  c0.name = key + ".blocks.0";
-  c0.wkey = key + ".blocks.0.block.0";
-  c0.gnkey = key + ".blocks.0.block.2";
-  c0.kind = CONV_K5;
-  c0.nsrc = nsrc;
-  for (int s = 0; s < nsrc; ++s) { c0.src[s] = src[s]; c0.src_real_c[s] = src_real[s]; }
-  c0.Cout = Cout;
-  c0.tb_off = *tb_cursor;
-  if ((rc = add_conv(P, W, c0, &mid))) return rc;
-
+  // job order: residual 1x1 conv first, then blocks.0 -> blocks.1 back to back, so that blocks.1 can read
+  // blocks.0's staged tile in place (resident link)
   if (cin_real != Cout) {
     ConvSpec cr;
     cr.name = key + ".residual_conv";
@@ -397,6 +421,16 @@ static int add_resblock(dm_plan* P, const WeightMap& W, const std::string& key, 
   } else {
     res = src[0];  // nn.Identity
   }
+  ConvSpec c0;
+  c0.name = key + ".blocks.0";
+  c0.wkey = key + ".blocks.0.block.0";
+  c0.gnkey = key + ".blocks.0.block.2";
+  c0.kind = CONV_K5;
+  c0.nsrc = nsrc;
+  for (int s = 0; s < nsrc; ++s) { c0.src[s] = src[s]; c0.src_real_c[s] = src_real[s]; }
+  c0.Cout = Cout;
+  c0.tb_off = *tb_cursor;
+  if ((rc = add_conv(P, W, c0, &mid))) return rc;
 
   ConvSpec c1;
   c1.name = key + ".blocks.1";
@@ -574,6 +608,8 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
       j.tbias_stride = tb_stride;
     }
     if (j.out_f32) j.out_f32 = out_f32;
+    j.a_res = 0;       // per-layer launches always go through global memory
+    j.next_res = 0;
     DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));
     P->last_launches++;
   }

@@ -99,6 +99,8 @@ __device__ __forceinline__ void tma_store_5d(const CUtensorMap* m, uint32_t src,
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all bulk groups of this thread complete: shared memory readable again AND the global writes performed
+// all bulk groups of this thread have finished READING shared memory (the global writes may still be in flight)
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ------------------------------------------- tcgen05 ------------------------------------------

@@ -21,11 +21,14 @@ if len(sys.argv) > 1 and sys.argv[1] == "--one":
         ts.append(e0.elapsed_time(e1))
     print(json.dumps({"ms": sorted(ts)[len(ts) // 2], "min": min(ts), "checksum": float(out.trajectories.double().sum())}))
     sys.exit(0)
-libs = [a for a in sys.argv[1:] if a.endswith(".so")]
-rest = [a for a in sys.argv[1:] if not a.endswith(".so")]
+libs = [a for a in sys.argv[1:] if ".so" in a]          # "lib.so" or "lib.so@ENVVAR" (sets ENVVAR=1 for that run)
+rest = [a for a in sys.argv[1:] if ".so" not in a]
 B = rest[0] if len(rest) > 0 else "1024"; H = rest[1] if len(rest) > 1 else "64"; reps = rest[2] if len(rest) > 2 else "5"
 for rnd in range(2):
     for l in libs:
-        env = dict(os.environ, DM_B200_LIB=os.path.abspath(l))
+        path, _, flag = l.partition("@")
+        env = dict(os.environ, DM_B200_LIB=os.path.abspath(path))
+        if flag:
+            env[flag] = "1"
         r = subprocess.run([sys.executable, __file__, "--one", B, H, reps], env=env, capture_output=True, text=True)
         print(rnd, l, r.stdout.strip()[-300:], r.stderr.strip()[-300:] if r.returncode else "", flush=True)
