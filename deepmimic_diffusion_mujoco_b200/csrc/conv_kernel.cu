@@ -67,6 +67,7 @@ struct ConvShared {
 // though ring depths change from layer to layer inside the persistent kernel.
 struct RoleState {
   uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0;
+  int pre_w = 0;   // producer: weight loads of the current unit that were already issued during the previous epilogue
 };
 
 __device__ __forceinline__ void init_shared(ConvShared& sh) {
@@ -80,7 +81,8 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
 // ================================ TMA producer (one warp, one elected lane issues) =========================
 __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
                                               int g, int b0, int n0, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
-                                              RoleState& rs, unsigned long long* tr) {
+                                              RoleState& rs, unsigned long long* tr, uint32_t smem_base,
+                                              const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0) {
   const bool leader = elect_one_sync();
   int as = 0, ws = 0;
   if (leader) trace_mark(tr, 2);
@@ -99,13 +101,17 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
           rs.a_bits ^= 1u << as;
         }
         for (int t = 0; t < job.ntaps; ++t) {
-          mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
-          if (leader) {
-            mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
-            tma_load_4d(w_smem + ws * job.w_stage_bytes, w_map, &sh.w_full[ws], cin_off + ch * job.Cc, n0,
-                        job.taps[t].wtap, 0);
+          if (rs.pre_w > 0) {
+            --rs.pre_w;            // issued during the previous layer's epilogue
+          } else {
+            mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
+            if (leader) {
+              mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
+              tma_load_4d(w_smem + ws * job.w_stage_bytes, w_map, &sh.w_full[ws], cin_off + ch * job.Cc, n0,
+                          job.taps[t].wtap, 0);
+            }
+            rs.w_bits ^= 1u << ws;
           }
-          rs.w_bits ^= 1u << ws;
           if (++ws == job.n_w_stages) ws = 0;
         }
         if (!job.a_res && ++as == job.n_a_stages) as = 0;
@@ -114,6 +120,23 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
     }
   }
   if (leader) trace_mark(tr, 4);
+  // Weight prefetch across the layer boundary: weights do not depend on activations.  Once this unit's MMAs
+  // have all completed (its operand stages are dead), the first weight tiles of the next layer are loaded into
+  // that layer's ring slots that lie beyond this layer's staged output tile; they land during the epilogue.
+  if (nj != nullptr && job.pre_next > 0) {
+    mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x700);
+    const uint32_t nw_smem = smem_base + (uint32_t)(nj->a_res ? nj->w_off_res : nj->n_a_stages * nj->a_stage_bytes);
+    for (int i = 0; i < job.pre_next; ++i) {
+      mbar_wait(&sh.w_empty[i], ((rs.w_bits >> i) & 1) ^ 1, 0x780 + i);
+      if (leader) {
+        mbar_arrive_expect_tx(&sh.w_full[i], nj->w_tx_bytes);
+        tma_load_4d(nw_smem + i * nj->w_stage_bytes, n_w_map, &sh.w_full[i], 0, n_n0, nj->taps[i].wtap, 0);
+      }
+      rs.w_bits ^= 1u << i;
+    }
+    rs.pre_w = job.pre_next;
+  }
+  rs.acc_count++;
   __syncwarp();
 }
 
@@ -470,11 +493,12 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
 __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp,
                                          int g, int b0, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
-                                         unsigned long long* tr = nullptr) {
+                                         unsigned long long* tr = nullptr, const ConvJob* nj = nullptr,
+                                         const CUtensorMap* n_w_map = nullptr, int n_n0 = 0) {
   const uint32_t a_smem = smem;
   const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
   if (warp == kProducerWarp) {
-    producer_unit(job, &maps->a_map[0], &maps->w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr);
+    producer_unit(job, &maps->a_map[0], &maps->w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
   } else if (warp == kMmaWarp) {
     mma_unit(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr);
   } else {
@@ -566,8 +590,15 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         }
         const int first = job.S == 8 ? 0 : rank, stride = job.S == 8 ? 1 : 2;
         const int b0 = job.S == 8 ? rank * 8 : 0;
+        // the unit after this job's last one: first unit of the next job (next step's first job after the last)
+        const int nji = ji + 1 < lp.n_jobs ? ji + 1 : 0;
+        const ConvJob& njob = lp.jobs[nji];
+        const bool has_next = (ji + 1 < lp.n_jobs || k < lp.n_steps) && (njob.S == 8 || rank < njob.slices);
+        const int n_n0 = njob.S == 8 ? 0 : rank * njob.Nc;
         for (int sl = first; sl < slices; sl += stride) {
-          run_unit(job, maps, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr);
+          const bool last_unit = sl + stride >= slices;
+          run_unit(job, maps, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr,
+                   last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, n_n0);
           if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit
             tc_fence_before();
             __syncthreads();

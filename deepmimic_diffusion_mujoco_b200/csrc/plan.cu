@@ -109,6 +109,16 @@ static int find_w(const WeightMap& W, const std::string& name, std::vector<int64
   return DM_OK;
 }
 
+// Weight loads of `nx`'s first channel chunk that may be issued while `cur`'s epilogue runs: ring slots of nx
+// that lie beyond cur's staged output tile (cur's operand stages are dead by then).
+static int prefetchable_w_loads(const ConvJob& cur, const ConvJob& nx) {
+  if (getenv("DM_B200_NO_WPREFETCH")) return 0;
+  const int cur_st = cur.st_cw ? 2 * cur.st_nq * cur.st_blk_stride : 0;
+  const int w_off = nx.a_res ? nx.w_off_res : nx.n_a_stages * nx.a_stage_bytes;
+  const int lim = nx.ntaps < nx.n_w_stages ? nx.ntaps : nx.n_w_stages;
+  return w_off >= cur_st ? lim : 0;   // slots 0..lim-1 start at w_off: all of them or none
+}
+
 enum ConvKind { CONV_K5 = 0, CONV_DOWN = 1, CONV_K1 = 2, CONV_T4 = 3 };
 
 struct ConvSpec {
@@ -390,6 +400,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
       }
     }
   }
+  if (!P->layers.empty()) P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, j);
   P->layers.push_back(ly);
   return DM_OK;
 }
@@ -564,6 +575,7 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     int o2;
     if ((rc = add_conv(P, W, f1, &o2))) return rc;
   }
+  P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, P->layers.front().job);
   if (tb != P->TB) return fail(DM_ERR_ARG, "internal: time-bias layout mismatch (%d vs %d)", tb, P->TB);
 
   // time MLP parameters
@@ -610,6 +622,7 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
     if (j.out_f32) j.out_f32 = out_f32;
     j.a_res = 0;       // per-layer launches always go through global memory
     j.next_res = 0;
+    j.pre_next = 0;
     DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));
     P->last_launches++;
   }
