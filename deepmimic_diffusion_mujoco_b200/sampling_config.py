@@ -35,31 +35,45 @@ def apply_conditioning_motion_editing(x):
     return x
 
 
+_PROBES = {}
+
+
+def _probes(shape, device):
+    """Device-resident probe tensors (all-NaN, seeded normal), cached per (shape, device); callers clone them."""
+    key = (shape, str(device))
+    if key not in _PROBES:
+        if len(_PROBES) >= 4:
+            _PROBES.pop(next(iter(_PROBES)))
+        g = torch.Generator(device="cpu").manual_seed(5)
+        _PROBES[key] = (torch.full(shape, float("nan"), device=device, dtype=torch.float32),
+                        torch.randn(shape, generator=g).to(device))
+    return _PROBES[key]
+
+
 def trace_conditioning(fn, shape, device):
     """Returns (mask uint8, value fp32) with shapes [H,T] (batch-uniform) or [B,H,T], or (None, None) for the
     identity.  Raises DmError if fn is not an x-independent overwrite."""
     if fn is None or fn is apply_conditioning or fn is apply_conditioning_in_betweening \
             or fn is apply_conditioning_motion_blending:
         return None, None
-    probe = torch.full(shape, float("nan"), device=device, dtype=torch.float32)
-    out = fn(probe)
+    nan_probe, keep = _probes(tuple(shape), device)
+    out = fn(nan_probe.clone())
     if not torch.is_tensor(out) or tuple(out.shape) != tuple(shape):
         raise DmError("conditioning_fn must return a tensor of the input shape")
     mask = ~torch.isnan(out)
     value = torch.where(mask, out, torch.zeros_like(out))
-    g = torch.Generator(device="cpu").manual_seed(5)
-    probe2 = torch.randn(shape, generator=g).to(device)
-    keep = probe2.clone()
-    out2 = fn(probe2)
-    ok = torch.equal(out2[mask], value[mask]) and torch.equal(out2[~mask], keep[~mask])
-    if not ok:
+    out2 = fn(keep.clone())
+    # one device->host read for every property the host needs
+    flags = torch.stack([(out2 == torch.where(mask, value, keep)).all(), mask.any(), (mask == mask[:1]).all(),
+                         (value == value[:1]).all()]).cpu().tolist()
+    if not flags[0]:
         raise DmError("conditioning_fn is not an x-independent overwrite x = where(mask, value, x); it cannot be "
                       "fused into the sampling kernels (no fallback)")
-    if not bool(mask.any()):
+    if not flags[1]:
         return None, None
-    if bool((mask == mask[:1]).all()):
+    if flags[2]:
         mask = mask[0]
-    if bool((value == value[:1]).all()) and mask.dim() == 2:
+    if flags[3] and mask.dim() == 2:
         value = value[0]
     elif mask.dim() == 2:
         mask = mask.unsqueeze(0).expand(shape).contiguous()
