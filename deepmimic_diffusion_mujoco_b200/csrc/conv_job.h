@@ -67,6 +67,7 @@ struct ConvJob {
   int epi;
   int Cout;               // real output channels
   int cg;                 // channels per GroupNorm group
+  int cg_pow2;            // cg is a power of two (lets the epilogue fold partial sums by shifts)
   int B;                  // real batch (masks the fp32 output)
   const float* bias;      // [CoutPad]
   const float* gamma;     // [CoutPad]

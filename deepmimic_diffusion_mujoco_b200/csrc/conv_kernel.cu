@@ -42,7 +42,9 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kPollWarp = 2;   // epilogue warp that waits on the accumulator mbarrier (SMSP 2: neither TMA nor MMA warp)
 
-// Optional phase trace (debug): tr points at 16 slots of this (job, unit); null in production.
+// Optional phase trace (debug): tr points at kTraceSlots slots of this (job, unit); null in production.
+// Slots 0-15: phases; 16 + 2i / 17 + 2i: issue of weight load i by the producer / its arrival seen by the MMA warp.
+constexpr int kTraceSlots = 64;
 __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
   if (tr) {
     unsigned long long t;
@@ -84,7 +86,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
                                               RoleState& rs, unsigned long long* tr, uint32_t smem_base,
                                               const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0) {
   const bool leader = elect_one_sync();
-  int as = 0, ws = 0;
+  int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
@@ -109,10 +111,14 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
               mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
               tma_load_4d(w_smem + ws * job.w_stage_bytes, w_map, &sh.w_full[ws], cin_off + ch * job.Cc, n0,
                           job.taps[t].wtap, 0);
+#ifdef DM_TRACE_WLOADS
+              if (tr && wi < 24) trace_mark(tr, 16 + 2 * wi);
+#endif
             }
             rs.w_bits ^= 1u << ws;
           }
           if (++ws == job.n_w_stages) ws = 0;
+          ++wi;
         }
         if (!job.a_res && ++as == job.n_a_stages) as = 0;
       }
@@ -155,7 +161,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const uint32_t a_plane16 = (uint32_t)(job.a_res ? job.a_res_plane : job.a_plane_bytes) >> 4;
   const uint32_t w_plane16 = job.w_plane_bytes >> 4;
   const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
-  int as = 0, ws = 0;
+  int as = 0, ws = 0, wi = 0;
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     int cidx = 0;
     for (int src = 0; src < job.nsrc; ++src) {
@@ -174,6 +180,10 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
           rs.w_bits ^= 1u << ws;
           tc_fence_after();
           if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark(tr, 6);
+#ifdef DM_TRACE_WLOADS
+          if (leader && tr && wi < 24) trace_mark(tr, 17 + 2 * wi);
+#endif
+          ++wi;
           const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
           const int shift = job.taps[t].shift, phase = job.taps[t].phase;
           const bool first = cidx == 0 && job.taps[t].first != 0;
@@ -285,22 +295,37 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
           s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
           q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
         }
-        const uint2 gq = *reinterpret_cast<const uint2*>(&sh.qgrp[cc * 8]);
+        // fold 4-channel quads that belong to the same GroupNorm group before leaving the thread
+        // (cg is a power of two here; other widths keep one partial per quad)
+        int ng = 8;
+        if (job.cg_pow2 && job.cg >= 8) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { s[i] = s[2 * i] + s[2 * i + 1]; q[i] = q[2 * i] + q[2 * i + 1]; }
+          ng = 4;
+          if (job.cg >= 16) {
+            s[0] += s[1]; q[0] += q[1]; s[1] = s[2] + s[3]; q[1] = q[2] + q[3];
+            ng = 2;
+            if (job.cg >= 32) { s[0] += s[1]; q[0] += q[1]; ng = 1; }
+          }
+        }
+        const int qstep = 8 / ng;
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
-          s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
-          q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
-          if (S == 8) {
-            s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
-            q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
-          }
-          if (lane < S) {
-            const int gi = (int)(((r < 4 ? gq.x : gq.y) >> ((r & 3) * 8)) & 0xff);   // fixed (u, r) order: deterministic
-            float2* pp = reinterpret_cast<float2*>(&sh.part[((warp * 16 + lane) * 8 + gi) * 2]);
-            float2 acc = *pp;
-            acc.x += s[r];
-            acc.y += q[r];
-            *pp = acc;
+          if (r < ng) {
+            s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
+            q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
+            if (S == 8) {
+              s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
+              q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
+            }
+            if (lane < S) {
+              const int gi = sh.qgrp[cc * 8 + r * qstep];   // fixed (unit, r) order: deterministic
+              float2* pp = reinterpret_cast<float2*>(&sh.part[((warp * 16 + lane) * 8 + gi) * 2]);
+              float2 acc = *pp;
+              acc.x += s[r];
+              acc.y += q[r];
+              *pp = acc;
+            }
           }
         }
       }
@@ -323,15 +348,29 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     named_bar_sync(1, kEpiThreads);
     // scale/shift table: y = x * sc + sf with sc = rstd * gamma, sf = (bias - mean) * sc + beta
     const int tab_stride = 2 * Nc + 4;
-    for (int e = tid; e < S * Nc; e += kEpiThreads) {
-      const int bb = e / Nc, c = e - bb * Nc;
-      const int gi = c / job.cg;
-      const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
-      const float sc = st.y * sh.par[1][c];
-      float2 o;
-      o.x = sc;
-      o.y = fmaf(sh.par[0][c] - st.x, sc, sh.par[2][c]);
-      *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
+    if (kEpiThreads % Nc == 0) {           // Nc in {32, 64, 128, ...}: no integer division in the loop
+      const int c = tid % Nc;
+      const int gi = sh.qgrp[c >> 2];
+      const float ga = sh.par[1][c], be = sh.par[2][c], bi = sh.par[0][c];
+      for (int bb = tid / Nc; bb < S; bb += kEpiThreads / Nc) {
+        const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
+        const float sc = st.y * ga;
+        float2 o;
+        o.x = sc;
+        o.y = fmaf(bi - st.x, sc, be);
+        *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
+      }
+    } else {
+      for (int e = tid; e < S * Nc; e += kEpiThreads) {
+        const int bb = e / Nc, c = e - bb * Nc;
+        const int gi = sh.qgrp[c >> 2];
+        const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
+        const float sc = st.y * sh.par[1][c];
+        float2 o;
+        o.x = sc;
+        o.y = fmaf(sh.par[0][c] - st.x, sc, sh.par[2][c]);
+        *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
+      }
     }
     named_bar_sync(1, kEpiThreads);
   }
@@ -578,7 +617,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
       for (int ji = 0; ji < lp.n_jobs; ++ji) {
         const ConvJob& job = lp.jobs[ji];   // kernel-parameter (constant) space: warp-uniform
         unsigned long long* tr = (lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
-                                     ? lp.trace + (size_t)ji * 16 : nullptr;
+                                     ? lp.trace + (size_t)ji * kTraceSlots : nullptr;
         if (threadIdx.x == 0) trace_mark(tr, 0);
         const int slices = job.slices;
         const int off = job.tb_off;

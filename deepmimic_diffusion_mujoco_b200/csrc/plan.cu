@@ -310,6 +310,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   j.epi = gn ? EPI_GN_MISH : EPI_BIAS;
   j.Cout = sp.Cout;
   j.cg = cg;
+  j.cg_pow2 = (cg & (cg - 1)) == 0;
   j.B = P->B;
   j.bias = db;
   j.gamma = dg;

@@ -14,7 +14,7 @@ net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
 diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=steps, predict_epsilon=False).cuda()
 plan = net.plan_for(B, H)
 names = plan.layer_names()
-tr = torch.zeros(len(names), 16, dtype=torch.int64, device="cuda")
+tr = torch.zeros(len(names), 64, dtype=torch.int64, device="cuda")
 _lib.check(_lib.lib().dm_plan_set_trace(plan.handle, tr.data_ptr(), 3, 4))
 for _ in range(2):
     diff.p_sample_loop((B, H, 35), {}, verbose=False, seed=1)
@@ -30,4 +30,11 @@ for i, (n, C, L) in enumerate(names):
     vals = [(r[k] - base) / 1e3 if r[k] > 0 else float("nan") for k in range(16)]
     print(f"{n[:27]:28s}", " ".join(f"{v:6.1f}" for v in vals), f"  {(r[13]-r[0])/1e3:7.1f}")
     tot += r[13] - r[0]
+detail = os.environ.get("TRACE_DETAIL")
+if detail:
+    for i, (n, C, L) in enumerate(names):
+        if detail in n:
+            r = t[i]
+            print(n, "W loads: (issue, seen by MMA warp) us from layer start")
+            print("  " + "  ".join(f"{(r[16+2*w]-r[0])/1e3:.2f}/{(r[17+2*w]-r[0])/1e3:.2f}" for w in range(24) if r[17+2*w] > 0))
 print("sum of layers us", tot / 1e3, " step span us", (t[-1, 13] - t[0, 0]) / 1e3)
