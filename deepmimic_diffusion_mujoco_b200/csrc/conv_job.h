@@ -97,6 +97,7 @@ struct ConvJob {
   int a_res_chunk;        // bytes between channel chunks of the resident tile
   int a_res_plane;        // bytes between the hi and lo planes of the resident tile
   int w_off_res;          // weight ring offset when a_res (beyond every staged tile)
+  int sync_local;         // the next layer only reads what THIS CTA wrote (both layers S = 8): block barrier, no cluster barrier
   int pre_next;           // weight loads of the NEXT layer's first chunk the producer may issue during this epilogue
   int next_res;           // the next layer reads this layer's staged tile in place (zero the gaps, defer the store wait)
   // fused-loop bookkeeping

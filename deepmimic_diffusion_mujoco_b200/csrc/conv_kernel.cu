@@ -591,6 +591,16 @@ __device__ __forceinline__ void job_sync(bool wrote_global, bool issues_tma) {
   if (issues_tma) fence_proxy_async_global();
 }
 
+// Same hand-over when producer and consumer are the SAME CTA (S = 8 layers: each CTA owns its 8 samples end to
+// end): a block barrier is enough, the peer CTA is not involved.
+__device__ __forceinline__ void local_sync(bool wrote_global, bool issues_tma) {
+  if (wrote_global) fence_proxy_async_global();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (issues_tma) fence_proxy_async_global();
+}
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   const uint32_t smem = aligned_dyn_smem();
@@ -649,6 +659,8 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
           tc_fence_before();
           __syncthreads();
           tc_fence_after();
+        } else if (job.sync_local) {
+          local_sync(warp < kEpiWarps && job.st_cw == 0, warp == kProducerWarp);
         } else {
           job_sync(warp < kEpiWarps && job.st_cw == 0, warp == kProducerWarp);
         }
@@ -664,7 +676,8 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
     __syncthreads();
     if (warp < kEpiWarps && s_hi > s_lo)
       ddpm_step_range<true>(sstep, s_lo * ht4, s_hi * ht4, threadIdx.x, kEpiThreads);
-    job_sync(warp < kEpiWarps, warp == kProducerWarp);
+    if (lp.k4_local) local_sync(warp < kEpiWarps, warp == kProducerWarp);
+    else job_sync(warp < kEpiWarps, warp == kProducerWarp);
   }
   if (threadIdx.x == 0) tma_store_wait_all();
   tc_fence_before();

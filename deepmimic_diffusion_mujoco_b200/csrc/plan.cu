@@ -577,6 +577,9 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if ((rc = add_conv(P, W, f1, &o2))) return rc;
   }
   P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, P->layers.front().job);
+  if (!getenv("DM_B200_NO_LOCALSYNC"))
+    for (size_t i = 0; i + 1 < P->layers.size(); ++i)
+      P->layers[i].job.sync_local = P->layers[i].job.S == 8 && P->layers[i + 1].job.S == 8;
   if (tb != P->TB) return fail(DM_ERR_ARG, "internal: time-bias layout mismatch (%d vs %d)", tb, P->TB);
 
   // time MLP parameters
@@ -624,6 +627,7 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
     j.a_res = 0;       // per-layer launches always go through global memory
     j.next_res = 0;
     j.pre_next = 0;
+    j.sync_local = 0;
     DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));
     P->last_launches++;
   }
@@ -840,6 +844,7 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   lp.maps = P->maps_dev;
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
+  lp.k4_local = P->layers.front().job.S == 8 && P->layers.back().job.S == 8 && !getenv("DM_B200_NO_LOCALSYNC");
   lp.trace = P->trace_dev; lp.trace_cluster = P->trace_cluster; lp.trace_step = P->trace_step;
   DM_CUDA(launch_sample_loop(lp, P->loop_smem, s));
   // the pinned step table is reused by the next call: wait until the copy engine has consumed it

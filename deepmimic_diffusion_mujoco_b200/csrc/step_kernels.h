@@ -55,6 +55,7 @@ struct LoopParams {
   const float* tb_table;      // [n_timesteps, TB]
   int TB;
   int G, B, H, T;
+  int k4_local;               // first and last layer are S = 8: the DDPM update hands over inside the CTA
   unsigned long long* trace;  // debug: [n_jobs][16] globaltimer stamps of one (cluster, step); null in production
   int trace_cluster, trace_step;
 };
