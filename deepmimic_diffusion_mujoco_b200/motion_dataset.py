@@ -1,0 +1,110 @@
+"""Drop-in for data_loaders/motion_dataset.py:9-56 (`MotionDataset`, `Batch`) and the `.npy` motion writer.
+
+Host-side boundary code, like the reference's: DeepMimic mocap JSON ("Frames": [duration, root pos 3, root quat 4,
+12 joints as quaternions / hinge angles in DeepMimic order]) -> qpos rows [F, 35] in the MuJoCo humanoid's joint
+order (root pos, root quat, then Euler xyz per 3-dof joint / angle per hinge), as utils/mocap_v2.py:105-291 does.
+The arithmetic is vectorised over frames (no pyquaternion / transformations dependency):
+  align_rotation  (utils/mocap_util.py:31-40)  q' = qL * q * qR with qL/qR = +/-90 deg about x
+  align_position  (utils/mocap_util.py:42-48)  (x, y, z) -> (x, -z, y)
+  euler 'rxyz'    (utils/transformations.py:1031-1097) from the rotation matrix of the aligned quaternion
+"""
+import json
+from collections import namedtuple
+
+import numpy as np
+import torch
+
+Batch = namedtuple("Batch", "trajectories conditions")
+
+_BODY_JOINTS = ["chest", "neck", "right_shoulder", "right_elbow", "left_shoulder", "left_elbow", "right_hip",
+                "right_knee", "right_ankle", "left_hip", "left_knee", "left_ankle"]
+_DP_ORDER = ["chest", "neck", "right_hip", "right_knee", "right_ankle", "right_shoulder", "right_elbow", "left_hip",
+             "left_knee", "left_ankle", "left_shoulder", "left_elbow"]
+_HINGES = {"right_elbow", "left_elbow", "right_knee", "left_knee"}
+_R = np.sqrt(0.5)
+
+
+def _qmul(a, b):
+    aw, ax, ay, az = (a[..., i] for i in range(4))
+    bw, bx, by, bz = (b[..., i] for i in range(4))
+    return np.stack([aw * bw - ax * bx - ay * by - az * bz, aw * bx + ax * bw + ay * bz - az * by,
+                     aw * by - ax * bz + ay * bw + az * bx, aw * bz + ax * by - ay * bx + az * bw], axis=-1)
+
+
+def _align_rotation(q):
+    left = np.array([_R, _R, 0.0, 0.0])      # +90 deg about x
+    right = np.array([_R, -_R, 0.0, 0.0])    # -90 deg about x
+    return _qmul(_qmul(np.broadcast_to(left, q.shape), q), np.broadcast_to(right, q.shape))
+
+
+def _euler_rxyz(q):
+    """q: [..., 4] (w, x, y, z) -> intrinsic x-y-z Euler angles [..., 3]."""
+    n = np.sum(q * q, axis=-1, keepdims=True)
+    w, x, y, z = ((q * np.sqrt(2.0 / n))[..., i] for i in range(4))
+    m00 = 1.0 - y * y - z * z
+    m01, m02 = x * y - z * w, x * z + y * w
+    m12, m22 = y * z - x * w, 1.0 - x * x - y * y
+    m11 = 1.0 - x * x - z * z
+    m10 = x * y + z * w
+    cy = np.sqrt(m22 * m22 + m12 * m12)
+    ok = cy > np.finfo(float).eps * 4.0
+    ax = np.where(ok, np.arctan2(m01, m00), np.arctan2(-m10, m11))
+    ay = np.arctan2(-m02, cy)
+    az = np.where(ok, np.arctan2(m12, m22), 0.0)
+    return np.stack([-az, -ay, -ax], axis=-1)
+
+
+def mocap_to_qpos(frames):
+    """[F, 44] DeepMimic frames -> [F, 35] float64 qpos rows (`MocapDM.data_config`)."""
+    fr = np.asarray(frames, dtype=np.float64)
+    cols = [np.stack([fr[:, 1], -fr[:, 3], fr[:, 2]], axis=-1), _align_rotation(fr[:, 4:8])]
+    joint, off = {}, 8
+    for name in _DP_ORDER:
+        width = 1 if name in _HINGES else 4
+        joint[name] = fr[:, off:off + width]
+        off += width
+    for name in _BODY_JOINTS:
+        cols.append(joint[name] if name in _HINGES else _euler_rxyz(_align_rotation(joint[name])))
+    return np.concatenate(cols, axis=-1)
+
+
+def load_mocap_frames(path):
+    with open(path, "r") as f:
+        return np.array(json.load(f)["Frames"], dtype=np.float64)
+
+
+class MotionDataset(torch.utils.data.Dataset):
+    """motion_dataset.py:12-56: every cyclic shift of the clip (truncated to a multiple of 8 frames)."""
+
+    def __init__(self, motion_src_path):
+        cfg = mocap_to_qpos(load_mocap_frames(motion_src_path))
+        self.dt = float(load_mocap_frames(motion_src_path)[0, 0])
+        n = cfg.shape[0] - cfg.shape[0] % 8            # temporal unet needs a multiple of 8 (motion_dataset.py:26-28)
+        cfg = torch.from_numpy(cfg[:n]).float()
+        idx = (torch.arange(n)[:, None] + torch.arange(n)[None, :]) % n
+        self.motion_data = cfg[idx]                    # [n, n, 35]: row i = cat(cfg[i:], cfg[:i])
+
+    def __len__(self):
+        return len(self.motion_data)
+
+    def __getitem__(self, idx):
+        motion = self.motion_data[idx]
+        return Batch(trajectories=motion, conditions=self.get_conditions(motion))
+
+    def get_conditions(self, data_configs):
+        return {0: data_configs[0]}
+
+
+def tile_clip(clip, horizon):
+    """[F, 35] -> [horizon, 35] by cycling the clip, the way the dataset's shifted rows continue it."""
+    clip = torch.as_tensor(clip)
+    reps = -(-horizon // clip.shape[0])
+    return clip.repeat(reps, 1)[:horizon].contiguous()
+
+
+def save_motion_npy(path, trajectory):
+    """The `.npy` contract of the notebooks (float32 [H, 35]) that mocap_player.play_mocap_np_file (:51) loads."""
+    t = torch.as_tensor(trajectory).detach().float().cpu().numpy()
+    if t.ndim != 2 or t.shape[1] != 35:
+        raise ValueError("expected one trajectory [H, 35]")
+    np.save(path, t.astype(np.float32))

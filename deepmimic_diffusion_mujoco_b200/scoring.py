@@ -51,6 +51,13 @@ def fid_moments(data, sum_out=None, sxx_out=None):
     return sum_out, sxx_out
 
 
+def shard_range(n, rank, world):
+    """Contiguous split of n independent samples over `world` ranks (sizes differ by at most one)."""
+    base, rem = divmod(int(n), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
 def allreduce_statistics(count, *tensors):
     """The path's only exchange step: sum the packed statistics over ranks (NCCL over NVLink; gloo in CPU tests).
     count: python int or 0-d tensor; tensors: fp64 tensors reduced in place.  Returns the global count."""
