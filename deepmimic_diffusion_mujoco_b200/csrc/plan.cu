@@ -184,9 +184,10 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   int Mt = mt_total;
   const int a_budget = 80 * 1024;
   while (Mt > 1 && (stage_for(Mt) > a_budget || box_for(Mt) > 256)) --Mt;
+  j.n_ltiles = (mt_total + Mt - 1) / Mt;
+  Mt = (mt_total + j.n_ltiles - 1) / j.n_ltiles;   // even split: no padding tiles beyond mt_total (TMEM budget)
   j.Mt = Mt;
   j.Lt = Mt * pos_per_mt;
-  j.n_ltiles = (mt_total + Mt - 1) / Mt;
   j.box_l = box_for(Mt);
   j.Lj = Lj;
   j.Lout = Lout;

@@ -247,3 +247,103 @@ def test_errors_are_loud(dm):
         diff.p_sample_loop((1, 64, 35), {}, verbose=False, conditioning_fn=lambda x: x * 0.5)
     with pytest.raises(dm.DmError):
         diff.p_sample_loop((1, 64, 35), {}, verbose=False, sample_fn=lambda *a: None)
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE.json configs[2..4] at test sizes, and size-independent properties at the full configs[1] size
+# ---------------------------------------------------------------------------------------------------
+def _clip(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, "mocap_clips.npz"))
+    return torch.from_numpy(z[name + "_config"]).float()
+
+
+def test_config3_long_horizon_arm_limit(dm):
+    """configs[2]: H=256 with the hand/arm joint limit inpaint (tiles that exceed the staged epilogue's budget)."""
+    B, H, n = 3, 256, 4
+    sd = O.seeded_state_dict(H=H, seed=2)
+    g = torch.Generator().manual_seed(5)
+    noise = torch.randn(n + 1, B, H, 35, generator=g)
+    mask, value = box_cond(H)
+    ref = O.p_sample_loop(sd, O.make_schedule(n), noise, mask=mask, value=value)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    for fused in (True, False):
+        out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=dm.InjectedNoise(noise),
+                                 conditioning_fn=box_holding, fused=fused)
+        chain = out.chains.cpu()
+        for k in range(n + 1):
+            assert rel(chain[:, k], ref[:, k]) < REL_STEP, (fused, k)
+        m = mask.expand(B, H, 35)
+        assert torch.equal(chain[:, -1][m], ref[:, -1][m])
+
+
+def test_config4_inbetweening_blend_of_two_clips(dm, golden_dir):
+    """configs[3]: H=128, frames [0,32) from walk and [96,128) from spinkick kept fixed, the middle sampled."""
+    B, H, n = 5, 128, 4
+    walk, kick = _clip(golden_dir, "walk")[:32], _clip(golden_dir, "spinkick")[:32]
+    start = torch.randn(B, H, 35, generator=torch.Generator().manual_seed(8))
+    start[:, :32] = walk
+    start[:, 96:] = kick
+
+    def blend(x):   # 5_motion_blending.ipynb c20-21 pattern with two clips
+        x[:, :32] = walk.to(x.device)
+        x[:, 96:] = kick.to(x.device)
+        return x
+
+    sd = O.seeded_state_dict(H=H, seed=4)
+    noise = torch.randn(n + 1, B, H, 35, generator=torch.Generator().manual_seed(6))
+    mask = torch.zeros(H, 35, dtype=torch.bool)
+    mask[:32] = True
+    mask[96:] = True
+    value = torch.zeros(H, 35)
+    value[:32] = walk
+    value[96:] = kick
+    ref = O.p_sample_loop(sd, O.make_schedule(n), noise, mask=mask, value=value, starting_motion=start)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=dm.InjectedNoise(noise),
+                             conditioning_fn=blend, starting_motion=start)
+    chain = out.chains.cpu()
+    for k in range(n + 1):
+        assert rel(chain[:, k], ref[:, k]) < REL_STEP, k
+    assert torch.equal(chain[:, -1, :32], walk.expand(B, 32, 35)) and torch.equal(chain[:, -1, 96:], kick.expand(B, 32, 35))
+
+
+def test_config5_sample_and_score(dm, golden_dir):
+    """configs[4]: sample, then FK + tracking reward against spinkick frames 0-63 and FID moments of the samples."""
+    from deepmimic_diffusion_mujoco_b200 import scoring
+    B, H = 64, 64
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=5, predict_epsilon=False).cuda()
+    x = diff.p_sample_loop((B, H, 35), {}, verbose=False, seed=21).trajectories
+    ref = _clip(golden_dir, "spinkick")[:64]
+    out = scoring.fk_reward(x, ref, 0.016666)
+    r, terms = SO.tracking_reward(x.double().cpu().numpy(), ref.double().numpy(), 0.016666)
+    assert np.abs(out["reward"].cpu().numpy() - r).max() < 2e-4
+    s, sxx = scoring.fid_moments(x)
+    X = x.double().cpu().reshape(B, -1)
+    assert torch.allclose(s.cpu(), X.sum(0), rtol=1e-6, atol=1e-4)
+    assert torch.allclose(sxx.cpu(), X.T @ X, rtol=1e-5, atol=1e-3)
+    # linearity of the moments: two half batches sum to the full batch (what the all-reduce relies on)
+    s1, q1 = scoring.fid_moments(x[:20])
+    s2, q2 = scoring.fid_moments(x[20:])
+    assert torch.allclose(s1 + s2, s, rtol=1e-6, atol=1e-4) and torch.allclose(q1 + q2, sxx, rtol=1e-5, atol=1e-3)
+
+
+def test_full_size_properties(dm):
+    """configs[1] at full size (B=1024, H=64): finite, conditioned channels exact, deterministic, and every sample is
+    independent of the batch it was drawn in (Philox keyed by global sample index) -- the sharding invariant."""
+    H, n = 64, 6
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    a = diff.p_sample_loop((1024, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=5).trajectories.clone()
+    b = diff.p_sample_loop((1024, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=5).trajectories.clone()
+    small = diff.p_sample_loop((48, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=5).trajectories.clone()
+    assert torch.isfinite(a).all() and torch.equal(a, b)
+    assert torch.equal(a[:, :, 16], torch.full((1024, H), 1.57, device="cuda"))
+    assert torch.equal(a[:, :, 17:20], torch.zeros(1024, H, 3, device="cuda"))
+    assert torch.equal(a[:48], small)
