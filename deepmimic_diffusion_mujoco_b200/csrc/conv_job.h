@@ -82,6 +82,7 @@ struct ConvJob {
   long long out_plane_stride;
   float* out_f32;         // public layout [B][Lout][out_f32_C]; null if none
   int out_f32_C;
+  int f32_stride;         // floats per sample in the smem staging of the fp32 output (0: direct global stores)
   // staged epilogue: the unit's output tile is assembled in shared memory (same swizzle as a TMA box) and
   // written with TMA stores; the residual tile is TMA-loaded into the same buffer.  st_cw == 0: direct path.
   int st_cw;              // channels per staged block (64 -> SWIZZLE_128B rows, 32 -> SWIZZLE_64B rows)

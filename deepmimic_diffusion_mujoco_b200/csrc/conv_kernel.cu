@@ -487,7 +487,14 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         }
       }
       }
-      if (job.out_f32 && bg < job.B) {
+      if (job.out_f32 && job.f32_stride) {
+        // fp32 public-layout output, staged: one sample = Lout * C contiguous floats (+4 floats of bank skew per
+        // sample: lanes are 4 positions x 8 samples, 35-float rows -> conflict-free), copied out coalesced below
+        const uint32_t so = stg + 4u * (uint32_t)(b * job.f32_stride + lrow * job.out_f32_C + n0 + cb);
+#pragma unroll
+        for (int e = 0; e < 32; ++e)
+          if (n0 + cb + e < job.Cout) sts32(so + 4u * e, v[e]);
+      } else if (job.out_f32 && bg < job.B) {
         float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
@@ -495,6 +502,17 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
           if (c < job.Cout) of[c] = v[e];
         }
       }
+    }
+  }
+  if (job.out_f32 && job.f32_stride) {
+    named_bar_sync(1, kEpiThreads);
+    const int per = (job.Lout * job.out_f32_C) >> 2;          // float4 per sample
+    for (int i = tid; i < S * per; i += kEpiThreads) {
+      const int bb = i / per, o = i - bb * per;
+      const int sg = g * kGroupSamples + b0 + bb;
+      if (sg < job.B)
+        reinterpret_cast<float4*>(job.out_f32 + (size_t)sg * job.Lout * job.out_f32_C)[o] =
+            lds128f(stg + 4u * (uint32_t)(bb * job.f32_stride) + 16u * (uint32_t)o);
     }
   }
   trace_mark(tr, 14);

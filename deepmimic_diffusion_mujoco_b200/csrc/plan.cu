@@ -113,7 +113,8 @@ static int find_w(const WeightMap& W, const std::string& name, std::vector<int64
 // that lie beyond cur's staged output tile (cur's operand stages are dead by then).
 static int prefetchable_w_loads(const ConvJob& cur, const ConvJob& nx) {
   if (getenv("DM_B200_NO_WPREFETCH")) return 0;
-  const int cur_st = cur.st_cw ? 2 * cur.st_nq * cur.st_blk_stride : 0;
+  int cur_st = cur.st_cw ? 2 * cur.st_nq * cur.st_blk_stride : 0;
+  if (cur.f32_stride && cur.S * cur.f32_stride * 4 > cur_st) cur_st = cur.S * cur.f32_stride * 4;
   const int w_off = nx.a_res ? nx.w_off_res : nx.n_a_stages * nx.a_stage_bytes;
   const int lim = nx.ntaps < nx.n_w_stages ? nx.ntaps : nx.n_w_stages;
   return w_off >= cur_st ? lim : 0;   // slots 0..lim-1 start at w_off: all of them or none
@@ -339,6 +340,13 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (sp.f32_out) {
     j.out_f32 = P->model_out;
     j.out_f32_C = sp.Cout;
+    const int per_sample = Lout * sp.Cout;
+    if (per_sample % 4 == 0 && ly.slices == 1 && (size_t)j.S * (per_sample + 4) * 4 <= (size_t)budget &&
+        !getenv("DM_B200_NO_F32STAGE")) {
+      j.f32_stride = per_sample + 4;
+      const size_t need = (size_t)j.S * j.f32_stride * 4 + 1024;
+      if (ly.smem < need) ly.smem = need;
+    }
   }
   // ---- staged epilogue (TMA store of the output tile, TMA load of the residual tile) ----
   j.st_cw = 0;
