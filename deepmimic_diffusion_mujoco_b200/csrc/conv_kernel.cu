@@ -330,7 +330,9 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         }
       }
     }
+    trace_mark(tr, 40);
     named_bar_sync(1, kEpiThreads);
+    trace_mark(tr, 41);
     if (tid < 128) {                       // one thread per (sample, group): fixed-order sum over the warps
       float a = 0.f, q2 = 0.f;
 #pragma unroll
@@ -346,6 +348,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       (&sh.stat[0][0][0])[tid * 2 + 1] = rsqrtf(var + 1e-5f);
     }
     named_bar_sync(1, kEpiThreads);
+    trace_mark(tr, 42);
     // scale/shift table: y = x * sc + sf with sc = rstd * gamma, sf = (bias - mean) * sc + beta
     const int tab_stride = 2 * Nc + 4;
     if (kEpiThreads % Nc == 0) {           // Nc in {32, 64, 128, ...}: no integer division in the loop
@@ -646,7 +649,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         const ConvJob& job = lp.jobs[ji];   // kernel-parameter (constant) space: warp-uniform
         unsigned long long* tr = (lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
                                      ? lp.trace + (size_t)ji * kTraceSlots : nullptr;
-        if (threadIdx.x == 0) trace_mark(tr, 0);
+        if (threadIdx.x == 0 && tr) { trace_mark(tr, 0); tr[1] = (unsigned long long)clock64(); }   // slot 1: SM clock (effective MHz)
         const int slices = job.slices;
         const int off = job.tb_off;
         const float* tb = off >= 0 ? lp.tb_table + (size_t)t_index * lp.TB + off : nullptr;

@@ -30,6 +30,12 @@ for i, (n, C, L) in enumerate(names):
     vals = [(r[k] - base) / 1e3 if r[k] > 0 else float("nan") for k in range(16)]
     print(f"{n[:27]:28s}", " ".join(f"{v:6.1f}" for v in vals), f"  {(r[13]-r[0])/1e3:7.1f}")
     tot += r[13] - r[0]
+if os.environ.get("TRACE_PASS1"):
+    print("pass 1 split (us after accF barrier): own partials | +barrier | combine+barrier | table+barrier")
+    for i, (n, C, L) in enumerate(names):
+        r = t[i]
+        if r[40] > 0:
+            print(f"{n[:27]:28s} {(r[40]-r[9])/1e3:5.2f} {(r[41]-r[9])/1e3:5.2f} {(r[42]-r[9])/1e3:5.2f} {(r[10]-r[9])/1e3:5.2f}")
 detail = os.environ.get("TRACE_DETAIL")
 if detail:
     for i, (n, C, L) in enumerate(names):
@@ -37,4 +43,5 @@ if detail:
             r = t[i]
             print(n, "W loads: (issue, seen by MMA warp) us from layer start")
             print("  " + "  ".join(f"{(r[16+2*w]-r[0])/1e3:.2f}/{(r[17+2*w]-r[0])/1e3:.2f}" for w in range(24) if r[17+2*w] > 0))
+print("effective SM clock MHz over the traced step:", (t[-1, 1] - t[0, 1]) / ((t[-1, 0] - t[0, 0]) / 1e3))
 print("sum of layers us", tot / 1e3, " step span us", (t[-1, 13] - t[0, 0]) / 1e3)
