@@ -36,6 +36,8 @@ struct ConvMaps {
   CUtensorMap w_map;      // 4-D (CinTot, CoutPad, ntaps, plane) fp16
   CUtensorMap o_map;      // 5-D store map of the output activation (box = one staged plane x channel block)
   CUtensorMap r_map;      // 5-D load map of the residual activation, same box as o_map
+  CUtensorMap x_map;      // 4-D weights of the fused auxiliary 1x1 conv (the block's residual_conv), box as w_map
+  CUtensorMap p_map;      // 5-D store map of the auxiliary output activation, same box as o_map
 };
 
 // Plain-data layer descriptor.  It is always read from kernel-parameter (constant-bank) space, so every field
@@ -101,6 +103,12 @@ struct ConvJob {
   int sync_local;         // the next layer only reads what THIS CTA wrote (both layers S = 8): block barrier, no cluster barrier
   int pre_next;           // weight loads of the NEXT layer's first chunk the producer may issue during this epilogue
   int next_res;           // the next layer reads this layer's staged tile in place (zero the gaps, defer the store wait)
+  // auxiliary 1x1 conv sharing this layer's A operand (ResidualTemporalBlock.residual_conv, temporal.py:34-35,46):
+  // one extra weight tile per channel chunk, accumulated into its own TMEM columns, bias-only epilogue
+  int aux;                // 1 if present
+  int aux_shift;          // l offset of the 1x1 tap inside the A box (= halo_lo)
+  int aux_col0;           // first TMEM column of the auxiliary accumulators
+  const float* aux_bias;  // [CoutPad]
   // fused-loop bookkeeping
   int slices;             // number of N slices (units per sample sub-group)
   int tb_off;             // offset of the layer's time bias inside a time-bias table row, or -1

@@ -56,7 +56,7 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full, res_full;
   uint32_t tmem_slot;
-  alignas(16) float par[4][256];        // bias, gamma, beta, time bias of this unit's Nc channels
+  alignas(16) float par[5][256];        // bias, gamma, beta, time bias, auxiliary-conv bias of this unit's Nc channels
   alignas(16) unsigned char qgrp[64];   // GroupNorm group (within the unit) of every 4-channel quad
   float stat[16][8][2];                 // per (sample, group): mean, rstd
   // per-warp partial sums [warp][sample][group][2], combined in a fixed order (deterministic); after the
@@ -82,7 +82,7 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
 
 // ================================ TMA producer (one warp, one elected lane issues) =========================
 __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
-                                              int g, int b0, int n0, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
+                                              const CUtensorMap* x_map, int g, int b0, int n0, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
                                               RoleState& rs, unsigned long long* tr, uint32_t smem_base,
                                               const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0) {
   const bool leader = elect_one_sync();
@@ -102,15 +102,15 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
           }
           rs.a_bits ^= 1u << as;
         }
-        for (int t = 0; t < job.ntaps; ++t) {
+        for (int t = 0; t < job.ntaps + job.aux; ++t) {   // the auxiliary 1x1 weights ride the same ring as one more tap
           if (rs.pre_w > 0) {
             --rs.pre_w;            // issued during the previous layer's epilogue
           } else {
             mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
             if (leader) {
               mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
-              tma_load_4d(w_smem + ws * job.w_stage_bytes, w_map, &sh.w_full[ws], cin_off + ch * job.Cc, n0,
-                          job.taps[t].wtap, 0);
+              tma_load_4d(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws],
+                          cin_off + ch * job.Cc, n0, t < job.ntaps ? job.taps[t].wtap : 0, 0);
 #ifdef DM_TRACE_WLOADS
               if (tr && wi < 24) trace_mark(tr, 16 + 2 * wi);
 #endif
@@ -175,7 +175,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
         if (leader && lt == 0 && cidx == 0) trace_mark(tr, 5);
         const uint32_t a_base16 =
             (job.a_res ? smem_base + (uint32_t)(job.a_res_off + cidx * job.a_res_chunk) : a_smem + as * job.a_stage_bytes) >> 4;
-        for (int t = 0; t < job.ntaps; ++t) {
+        for (int t = 0; t < job.ntaps + job.aux; ++t) {
           mbar_wait(&sh.w_full[ws], (rs.w_bits >> ws) & 1, 0x400 + ws);
           rs.w_bits ^= 1u << ws;
           tc_fence_after();
@@ -185,9 +185,10 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
 #endif
           ++wi;
           const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
-          const int shift = job.taps[t].shift, phase = job.taps[t].phase;
-          const bool first = cidx == 0 && job.taps[t].first != 0;
-          uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * Nc);
+          const bool is_aux = t >= job.ntaps;
+          const int shift = is_aux ? job.aux_shift : job.taps[t].shift, phase = is_aux ? 0 : job.taps[t].phase;
+          const bool first = cidx == 0 && (is_aux || job.taps[t].first != 0);
+          uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * Nc) + (is_aux ? (uint32_t)job.aux_col0 : 0u);
           uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
           for (int mt = 0; mt < job.Mt; ++mt, d += Nc, a16 += mt_step16) {
             if (leader) {
@@ -220,6 +221,42 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   __syncwarp();
 }
 
+// Writes (optionally after adding the staged residual) 32 consecutive channels [cb, cb+32) of staged row `srow` as
+// fp16 hi/lo planes: this thread's 64 B + 64 B, 16-byte slots XOR-swizzled like a TMA box (conflict-free).
+__device__ __forceinline__ void staged_write(const ConvJob& job, uint32_t stg_data, int srow, int cb, float* v,
+                                             bool add_res) {
+  const int cw_shift = job.st_cw == 64 ? 6 : 5;
+  const uint32_t row_bytes = (uint32_t)job.st_cw * 2;
+  const uint32_t blk_stride = (uint32_t)job.st_blk_stride;
+  const uint32_t plane_bytes = (uint32_t)job.st_nq * blk_stride;
+  const uint32_t xr = job.st_cw == 64 ? (uint32_t)(srow & 7) : (uint32_t)((srow >> 1) & 3);
+  const uint32_t i0 = (uint32_t)(cb & (job.st_cw - 1)) >> 3;
+  const uint32_t base = stg_data + (uint32_t)(cb >> cw_shift) * blk_stride + (uint32_t)srow * row_bytes;
+#pragma unroll
+  for (int q4 = 0; q4 < 4; ++q4) {
+    const uint32_t a_hi = base + (((i0 + q4) ^ xr) << 4);
+    const uint32_t a_lo = a_hi + plane_bytes;
+    if (add_res) {
+      const uint4 hv = lds128(a_hi), lv = lds128(a_lo);
+      const __half2* hh = reinterpret_cast<const __half2*>(&hv);
+      const __half2* ll = reinterpret_cast<const __half2*>(&lv);
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
+        v[q4 * 8 + w * 2] += fh.x + fl.x;
+        v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
+      }
+    }
+    uint4 hv, lv;
+    __half2* hh = reinterpret_cast<__half2*>(&hv);
+    __half2* ll = reinterpret_cast<__half2*>(&lv);
+#pragma unroll
+    for (int w = 0; w < 4; ++w) split_half2(v[q4 * 8 + w * 2], v[q4 * 8 + w * 2 + 1], hh[w], ll[w]);
+    sts128(a_hi, hv);
+    sts128(a_lo, lv);
+  }
+}
+
 // ================================ epilogue (warps 0..15) ===================================
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
@@ -243,6 +280,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     sh.par[1][i] = gn ? __ldg(job.gamma + n0 + i) : 1.f;
     sh.par[2][i] = gn ? __ldg(job.beta + n0 + i) : 0.f;
     sh.par[3][i] = tb_uniform ? __ldg(tbias + n0 + i) : 0.f;
+    if (job.aux) sh.par[4][i] = __ldg(job.aux_bias + n0 + i);
   }
   if (tid < (Nc >> 2)) sh.qgrp[tid] = (unsigned char)((tid * 4) / job.cg);
   if (gn) {
@@ -268,6 +306,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   const uint32_t stg_data = stg + kStageGap;
   if (res_staged) {
     if (tid == 0) {
+      tma_store_wait_all();   // the residual may be an auxiliary tile this thread stored one layer ago without waiting
       mbar_arrive_expect_tx(&sh.res_full, 2u * job.st_nq * blk_bytes);
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
@@ -279,6 +318,35 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
   const int nchunks = Nc >> 5;
   float v[32];
+
+  if (job.aux) {
+    // ---- auxiliary 1x1 conv (the block's residual_conv): bias only, staged and stored first; its TMA store
+    //      drains while pass 1 runs, and the staging buffer is reclaimed before pass 2 writes it ----
+    for (int T = 0; T < MT; ++T) {
+      const int jrow = (T * 128 + row) >> s_shift;
+      for (int cc = (slice - T * nchunks) & 3; cc < nchunks; cc += 4) {
+        tmem_ld32(trow + (uint32_t)(job.aux_col0 + T * Nc + cc * 32), v);
+        tmem_ld_wait();
+        if (jrow >= job.Lj) continue;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[4][cc * 32 + r * 4]);
+          v[r * 4] += bi.x; v[r * 4 + 1] += bi.y; v[r * 4 + 2] += bi.z; v[r * 4 + 3] += bi.w;
+        }
+        staged_write(job, stg_data, jrow * S + b, cc * 32, v, false);
+      }
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(1, kEpiThreads);
+    if (tid == 0) {
+      for (int p = 0; p < 2; ++p)
+        for (int q = 0; q < job.st_nq; ++q)
+          tma_store_5d(&maps->p_map, stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0, 0,
+                       g, p);
+      tma_store_commit();
+    }
+    __syncwarp();
+  }
 
   if (gn) {
     // ---- pass 1: GroupNorm statistics over (channels of group) x (all L positions), per sample ----
@@ -331,6 +399,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       }
     }
     trace_mark(tr, 40);
+    if (job.aux && tid == 0) tma_store_wait_read();   // the auxiliary tile has left the staging buffer
     named_bar_sync(1, kEpiThreads);
     trace_mark(tr, 41);
     if (tid < 128) {                       // one thread per (sample, group): fixed-order sum over the warps
@@ -386,9 +455,6 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     mbar_wait(&sh.res_full, rs.res_count & 1, 0x600);
     rs.res_count++;
   }
-  const int cw_shift = job.st_cw == 64 ? 6 : 5;
-  const uint32_t row_bytes = (uint32_t)job.st_cw * 2;
-  const uint32_t plane_bytes = (uint32_t)job.st_nq * blk_stride;
   for (int pt = 0; pt < PT; ++pt) {
     const int ph = pt >= MT ? 1 : 0;
     const int T = pt - ph * MT;
@@ -429,34 +495,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         }
       }
       if (staged) {
-        // this thread's 64 B (hi) + 64 B (lo) of staged row srow; 16-byte slots XOR-swizzled like a TMA box
-        const int srow = lrow * S + b;
-        const uint32_t xr = job.st_cw == 64 ? (uint32_t)(srow & 7) : (uint32_t)((srow >> 1) & 3);
-        const uint32_t i0 = (uint32_t)(cb & (job.st_cw - 1)) >> 3;
-        const uint32_t base = stg_data + (uint32_t)(cb >> cw_shift) * blk_stride + (uint32_t)srow * row_bytes;
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          const uint32_t a_hi = base + (((i0 + q4) ^ xr) << 4);
-          const uint32_t a_lo = a_hi + plane_bytes;
-          if (res_staged) {
-            const uint4 hv = lds128(a_hi), lv = lds128(a_lo);
-            const __half2* hh = reinterpret_cast<const __half2*>(&hv);
-            const __half2* ll = reinterpret_cast<const __half2*>(&lv);
-#pragma unroll
-            for (int w = 0; w < 4; ++w) {
-              const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
-              v[q4 * 8 + w * 2] += fh.x + fl.x;
-              v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
-            }
-          }
-          uint4 hv, lv;
-          __half2* hh = reinterpret_cast<__half2*>(&hv);
-          __half2* ll = reinterpret_cast<__half2*>(&lv);
-#pragma unroll
-          for (int w = 0; w < 4; ++w) split_half2(v[q4 * 8 + w * 2], v[q4 * 8 + w * 2 + 1], hh[w], ll[w]);
-          sts128(a_hi, hv);
-          sts128(a_lo, lv);
-        }
+        staged_write(job, stg_data, lrow * S + b, cb, v, res_staged);
       } else {
       if (job.res) {
         // (L2-coherent loads: inside the persistent kernel this data was written by another SM moments ago)
@@ -558,7 +597,7 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
   const uint32_t a_smem = smem;
   const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
   if (warp == kProducerWarp) {
-    producer_unit(job, &maps->a_map[0], &maps->w_map, g, b0, n0, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
+    producer_unit(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
   } else if (warp == kMmaWarp) {
     mma_unit(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr);
   } else {

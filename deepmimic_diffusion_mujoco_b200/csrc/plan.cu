@@ -135,12 +135,13 @@ struct ConvSpec {
   int res = -1;          // residual act index
   bool want_act_out = true;
   bool f32_out = false;  // write plan->model_out style fp32 [B,L,Cout]
+  std::string aux_wkey;  // fused auxiliary 1x1 conv over the same input ("<key>.weight/.bias"), or ""
 };
 
 static int round_up(int a, int b) { return (a + b - 1) / b * b; }
 
 // Adds one conv launch to the plan; returns the output act index in *out_idx (or -1).
-static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out_idx) {
+static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out_idx, int* aux_idx = nullptr) {
   Layer ly;
   ConvJob& j = ly.job;
   memset(&j, 0, sizeof(j));
@@ -221,6 +222,9 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   // 16-sample units are split over the two CTAs of a cluster by N slice: prefer an even slice count
   if (j.S == 16 && (cout_pad / Nc) % 2 == 1 && Nc % 64 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
   const int mt_all = j.n_ltiles * j.Mt;
+  const int acc_sets = j.nphase + (sp.aux_wkey.empty() ? 0 : 1);   // the auxiliary conv has its own accumulators
+  if (!sp.aux_wkey.empty() && acc_sets * mt_all * Nc > 512)
+    return fail(DM_ERR_STATE, "%s: no TMEM room for the fused residual conv", sp.name.c_str());   // caller falls back
   while (j.nphase * mt_all * Nc > 512 && Nc > 32 && (Nc / 2) % 32 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
   if (j.nphase * mt_all * Nc > 512)
     return fail(DM_ERR_ARG, "%s: horizon too long for the TMEM-resident GroupNorm design (H <= 256)", sp.name.c_str());
@@ -230,7 +234,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   j.slices = ly.slices;
   j.tb_off = sp.tb_off;
   int cols = 32;
-  while (cols < j.nphase * mt_all * Nc) cols *= 2;
+  while (cols < acc_sets * mt_all * Nc) cols *= 2;
   j.tmem_cols = cols;
   j.w_plane_bytes = Nc * j.row_bytes;
   j.w_tx_bytes = 2 * j.w_plane_bytes;
@@ -242,7 +246,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   const int budget = 200 * 1024;
   if (j.n_a_stages * j.a_stage_bytes + j.w_stage_bytes > budget) j.n_a_stages = 1;
   int nw = (budget - j.n_a_stages * j.a_stage_bytes) / j.w_stage_bytes;
-  const int w_loads = total_chunks * j.ntaps;
+  const int w_loads = total_chunks * (j.ntaps + (sp.aux_wkey.empty() ? 0 : 1));
   if (nw > w_loads) nw = w_loads;
   if (nw > 8) nw = 8;
   if (nw < 1) return fail(DM_ERR_ARG, "%s: tile does not fit in shared memory", sp.name.c_str());
@@ -384,6 +388,57 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
       st_bytes = 0;
     }
   }
+  // ---- fused auxiliary 1x1 conv (ResidualTemporalBlock.residual_conv): weights, bias, output act + store map ----
+  if (!sp.aux_wkey.empty()) {
+    if (!gn || sp.kind != CONV_K5 || sp.res >= 0 || j.st_cw == 0)
+      return fail(DM_ERR_STATE, "%s: this layer cannot carry a fused residual conv", sp.name.c_str());
+    const float *xw = nullptr, *xb = nullptr;
+    if ((rc = find_w(W, sp.aux_wkey + ".weight", {sp.Cout, cin_real, 1}, &xw))) return rc;
+    if ((rc = find_w(W, sp.aux_wkey + ".bias", {sp.Cout}, &xb))) return rc;
+    const size_t xplane = (size_t)cout_pad * cin_tot;
+    std::vector<__half> xp(2 * xplane, __float2half_rn(0.f));
+    int col0 = 0, real0 = 0;
+    for (int s = 0; s < sp.nsrc; ++s) {
+      for (int ci = 0; ci < sp.src_real_c[s]; ++ci)
+        for (int co = 0; co < sp.Cout; ++co) {
+          const float v = xw[(size_t)co * cin_real + real0 + ci];
+          const __half hi = __float2half_rn(v);
+          xp[(size_t)co * cin_tot + col0 + ci] = hi;
+          xp[xplane + (size_t)co * cin_tot + col0 + ci] = __float2half_rn(v - __half2float(hi));
+        }
+      col0 += P->acts[sp.src[s]].C;
+      real0 += sp.src_real_c[s];
+    }
+    __half* xdev = nullptr;
+    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&xdev), xp.size() * sizeof(__half), false))) return rc;
+    DM_CUDA(cudaMemcpy(xdev, xp.data(), xp.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    {
+      const uint64_t dims[4] = {(uint64_t)cin_tot, (uint64_t)cout_pad, 1, 2};
+      const uint64_t str[3] = {(uint64_t)cin_tot * 2, (uint64_t)cin_tot * cout_pad * 2, (uint64_t)xplane * 2};
+      const uint32_t box[4] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 2};
+      if ((rc = encode_map(&ly.maps.x_map, xdev, 4, dims, str, box, j.swz))) return rc;
+    }
+    std::vector<float> hxb(cout_pad, 0.f);
+    for (int c = 0; c < sp.Cout; ++c) hxb[c] = xb[c];
+    float* dxb;
+    if ((rc = upload(P, hxb, &dxb))) return rc;
+    int xi;
+    if ((rc = new_act(P, cout_pad, Lout, &xi))) return rc;
+    {
+      const Act& o = P->acts[xi];
+      const uint64_t dims[5] = {(uint64_t)o.C, kGroupSamples, (uint64_t)o.L, (uint64_t)P->G, 2};
+      const uint64_t str[4] = {(uint64_t)o.C * 2, (uint64_t)o.C * 2 * kGroupSamples,
+                               (uint64_t)o.C * 2 * kGroupSamples * o.L, (uint64_t)o.plane * 2};
+      const uint32_t box[5] = {(uint32_t)j.st_cw, (uint32_t)j.S, (uint32_t)j.st_lbox, 1, 1};
+      if ((rc = encode_map(&ly.maps.p_map, o.p, 5, dims, str, box, j.st_cw == 64 ? 2 : 4))) return rc;
+    }
+    j.aux = 1;
+    j.aux_shift = j.halo_lo;
+    j.aux_col0 = j.nphase * mt_all * Nc;
+    j.aux_bias = dxb;
+    ly.aux_act = xi;
+    if (aux_idx) *aux_idx = xi;
+  }
   // ---- resident link: read the previous layer's staged tile in place (fused loop only) ----
   if (!P->layers.empty() && !getenv("DM_B200_NO_RESIDENT")) {
     Layer& pv = P->layers.back();
@@ -428,20 +483,9 @@ struct BlockOut { int act; };
 static int add_resblock(dm_plan* P, const WeightMap& W, const std::string& key, const int* src, const int* src_real,
                         int nsrc, int cin_real, int Cout, int* tb_cursor, int* out_act) {
   int rc, mid = -1, res = -1, out = -1;
-  // job order: residual 1x1 conv first, then blocks.0 -> blocks.1 back to back, so that blocks.1 can read
-  // blocks.0's staged tile in place (resident link)
-  if (cin_real != Cout) {
-    ConvSpec cr;
-    cr.name = key + ".residual_conv";
-    cr.wkey = key + ".residual_conv";
-    cr.kind = CONV_K1;
-    cr.nsrc = nsrc;
-    for (int s = 0; s < nsrc; ++s) { cr.src[s] = src[s]; cr.src_real_c[s] = src_real[s]; }
-    cr.Cout = Cout;
-    if ((rc = add_conv(P, W, cr, &res))) return rc;
-  } else {
-    res = src[0];  // nn.Identity
-  }
+  // The 1x1 residual conv shares blocks.0's input: it rides in blocks.0's unit as an auxiliary accumulator set
+  // (one extra weight tile per channel chunk, bias-only epilogue).  When TMEM has no room for the second set
+  // (very long horizons) it stays a layer of its own, ordered first so that blocks.0 -> blocks.1 remain adjacent.
   ConvSpec c0;
   c0.name = key + ".blocks.0";
   c0.wkey = key + ".blocks.0.block.0";
@@ -451,7 +495,36 @@ static int add_resblock(dm_plan* P, const WeightMap& W, const std::string& key, 
   for (int s = 0; s < nsrc; ++s) { c0.src[s] = src[s]; c0.src_real_c[s] = src_real[s]; }
   c0.Cout = Cout;
   c0.tb_off = *tb_cursor;
-  if ((rc = add_conv(P, W, c0, &mid))) return rc;
+  bool fused_res = false;
+  if (cin_real != Cout && !getenv("DM_B200_NO_AUXFUSE")) {
+    c0.aux_wkey = key + ".residual_conv";
+    const size_t n_alloc = P->allocs.size(), n_acts = P->acts.size();
+    rc = add_conv(P, W, c0, &mid, &res);
+    if (rc == DM_OK) {
+      fused_res = true;
+    } else if (rc == DM_ERR_STATE) {     // does not fit: undo partial allocations of the attempt and fall back
+      while (P->allocs.size() > n_alloc) { cudaFree(P->allocs.back()); P->allocs.pop_back(); }
+      P->acts.resize(n_acts);
+      c0.aux_wkey.clear();
+    } else {
+      return rc;
+    }
+  }
+  if (!fused_res) {
+    if (cin_real != Cout) {
+      ConvSpec cr;
+      cr.name = key + ".residual_conv";
+      cr.wkey = key + ".residual_conv";
+      cr.kind = CONV_K1;
+      cr.nsrc = nsrc;
+      for (int s = 0; s < nsrc; ++s) { cr.src[s] = src[s]; cr.src_real_c[s] = src_real[s]; }
+      cr.Cout = Cout;
+      if ((rc = add_conv(P, W, cr, &res))) return rc;
+    } else {
+      res = src[0];  // nn.Identity
+    }
+    if ((rc = add_conv(P, W, c0, &mid))) return rc;
+  }
 
   ConvSpec c1;
   c1.name = key + ".blocks.1";

@@ -26,6 +26,7 @@ struct Layer {
   size_t smem = 0;
   int tb_off = -1;       // offset into a time-bias row, or -1
   int out_act = -1;      // index into acts (for dm_plan_read_layer), -1 if fp32-only
+  int aux_act = -1;      // output of the fused auxiliary 1x1 conv, -1 if none
   std::string name;
 };
 
