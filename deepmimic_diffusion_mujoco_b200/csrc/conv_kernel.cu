@@ -221,6 +221,66 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   __syncwarp();
 }
 
+// Cross-lane part of the GroupNorm statistics.  Each lane holds NG (sum, sum of squares) pairs, one per
+// GroupNorm group of its 32 channels; lanes with the same sample index (lane % S) must be added.  Recursive
+// halving: at every butterfly step a lane keeps half of its values and hands the other half to its partner, so
+// NG values cost NG + NG/2 shuffles per array instead of 2 * NG, and the final smem accumulation is spread over
+// all lanes.  Every (warp, sample, group) slot is touched by exactly one lane per call: the order is fixed.
+template <int NG, bool S8>
+__device__ __forceinline__ void gn_reduce_rows(float* s, float* q, int lane, float* part_warp, const unsigned char* qg) {
+  constexpr int QS = 8 / NG;   // 4-channel quads per folded value
+  auto rmw = [&](int bsample, int r, float sv, float qv) {
+    float2* pp = reinterpret_cast<float2*>(&part_warp[(bsample * 8 + qg[r * QS]) * 2]);
+    float2 acc = *pp;
+    acc.x += sv;
+    acc.y += qv;
+    *pp = acc;
+  };
+  if constexpr (NG >= 2) {
+    constexpr int H = NG / 2;
+    const bool h1 = (lane & 16) != 0;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const float ss = h1 ? s[i] : s[i + H], sk = h1 ? s[i + H] : s[i];
+      const float qs = h1 ? q[i] : q[i + H], qk = h1 ? q[i + H] : q[i];
+      s[i] = sk + __shfl_xor_sync(0xffffffffu, ss, 16);
+      q[i] = qk + __shfl_xor_sync(0xffffffffu, qs, 16);
+    }
+    const int r1 = h1 ? H : 0;
+    if constexpr (S8) {
+      const bool h0 = (lane & 8) != 0;
+      if constexpr (H >= 2) {
+        constexpr int H2 = H / 2;
+#pragma unroll
+        for (int i = 0; i < H2; ++i) {
+          const float ss = h0 ? s[i] : s[i + H2], sk = h0 ? s[i + H2] : s[i];
+          const float qs = h0 ? q[i] : q[i + H2], qk = h0 ? q[i + H2] : q[i];
+          s[i] = sk + __shfl_xor_sync(0xffffffffu, ss, 8);
+          q[i] = qk + __shfl_xor_sync(0xffffffffu, qs, 8);
+        }
+        const int r0 = r1 + (h0 ? H2 : 0);
+#pragma unroll
+        for (int i = 0; i < H2; ++i) rmw(lane & 7, r0 + i, s[i], q[i]);
+      } else {
+        s[0] += __shfl_xor_sync(0xffffffffu, s[0], 8);
+        q[0] += __shfl_xor_sync(0xffffffffu, q[0], 8);
+        if (!h0) rmw(lane & 7, r1, s[0], q[0]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < H; ++i) rmw(lane & 15, r1 + i, s[i], q[i]);
+    }
+  } else {
+    s[0] += __shfl_xor_sync(0xffffffffu, s[0], 16);
+    q[0] += __shfl_xor_sync(0xffffffffu, q[0], 16);
+    if constexpr (S8) {
+      s[0] += __shfl_xor_sync(0xffffffffu, s[0], 8);
+      q[0] += __shfl_xor_sync(0xffffffffu, q[0], 8);
+    }
+    if (lane < (S8 ? 8 : 16)) rmw(lane, 0, s[0], q[0]);
+  }
+}
+
 // Writes (optionally after adding the staged residual) 32 consecutive channels [cb, cb+32) of staged row `srow` as
 // fp16 hi/lo planes: this thread's 64 B + 64 B, 16-byte slots XOR-swizzled like a TMA box (conflict-free).
 __device__ __forceinline__ void staged_write(const ConvJob& job, uint32_t stg_data, int srow, int cb, float* v,
@@ -363,23 +423,31 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
           s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
           q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
         }
-        // fold 4-channel quads that belong to the same GroupNorm group before leaving the thread
-        // (cg is a power of two here; other widths keep one partial per quad)
-        int ng = 8;
-        if (job.cg_pow2 && job.cg >= 8) {
+        float* pw = &sh.part[warp * 256];
+        const unsigned char* qg = &sh.qgrp[cc * 8];
+        if (job.cg_pow2) {
+          // fold 4-channel quads of the same GroupNorm group inside the thread, then recursive halving across lanes
+          if (job.cg < 8) {
+            if (S == 8) gn_reduce_rows<8, true>(s, q, lane, pw, qg); else gn_reduce_rows<8, false>(s, q, lane, pw, qg);
+          } else {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { s[i] = s[2 * i] + s[2 * i + 1]; q[i] = q[2 * i] + q[2 * i + 1]; }
-          ng = 4;
-          if (job.cg >= 16) {
-            s[0] += s[1]; q[0] += q[1]; s[1] = s[2] + s[3]; q[1] = q[2] + q[3];
-            ng = 2;
-            if (job.cg >= 32) { s[0] += s[1]; q[0] += q[1]; ng = 1; }
+            for (int i = 0; i < 4; ++i) { s[i] = s[2 * i] + s[2 * i + 1]; q[i] = q[2 * i] + q[2 * i + 1]; }
+            if (job.cg < 16) {
+              if (S == 8) gn_reduce_rows<4, true>(s, q, lane, pw, qg); else gn_reduce_rows<4, false>(s, q, lane, pw, qg);
+            } else {
+              s[0] += s[1]; q[0] += q[1]; s[1] = s[2] + s[3]; q[1] = q[2] + q[3];
+              if (job.cg < 32) {
+                if (S == 8) gn_reduce_rows<2, true>(s, q, lane, pw, qg); else gn_reduce_rows<2, false>(s, q, lane, pw, qg);
+              } else {
+                s[0] += s[1]; q[0] += q[1];
+                if (S == 8) gn_reduce_rows<1, true>(s, q, lane, pw, qg); else gn_reduce_rows<1, false>(s, q, lane, pw, qg);
+              }
+            }
           }
-        }
-        const int qstep = 8 / ng;
+        } else {
+          // arbitrary group width (a multiple of 4): several quads may share a group, one lane adds them in order
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          if (r < ng) {
+          for (int r = 0; r < 8; ++r) {
             s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
             q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
             if (S == 8) {
@@ -387,8 +455,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
               q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
             }
             if (lane < S) {
-              const int gi = sh.qgrp[cc * 8 + r * qstep];   // fixed (unit, r) order: deterministic
-              float2* pp = reinterpret_cast<float2*>(&sh.part[((warp * 16 + lane) * 8 + gi) * 2]);
+              float2* pp = reinterpret_cast<float2*>(&pw[(lane * 8 + qg[r]) * 2]);
               float2 acc = *pp;
               acc.x += s[r];
               acc.y += q[r];
