@@ -47,6 +47,7 @@ struct ConvJob {
   int src_chunks[2];      // channel chunks per source
   int Cc;                 // channels per chunk (64 -> SWIZZLE_128B rows, 32 -> SWIZZLE_64B rows)
   int row_bytes;          // Cc * 2
+  int ksteps;             // k-steps (16 channels) issued per chunk: Cc / 16, less when the only chunk is zero padded
   int swz;                // UMMA layout code (2 = 128B, 4 = 64B)
   int S;                  // samples per CTA: 8 or 16
   int l_stride;           // 1, or 2 for the strided down-sampling conv

@@ -153,7 +153,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const int S = job.S, Nc = job.Nc;
   const int MT = job.n_ltiles * job.Mt;
   const uint32_t idesc = umma_idesc_f16(128, Nc);
-  const int ksteps = job.Cc >> 4;
+  const int ksteps = job.ksteps;   // 16-channel k-steps per chunk that hold real input channels (zero padding skipped)
   const int pos_per_mt = 128 / S;
   // descriptor high words are per-layer constants; only the 14-bit start address changes per MMA
   const uint64_t hi_a = umma_smem_desc(0, job.l_stride * 8 * job.row_bytes, job.swz);

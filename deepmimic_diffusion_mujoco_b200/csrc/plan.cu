@@ -170,6 +170,9 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   j.swz = all64 ? 2 : 4;
   j.nsrc = sp.nsrc;
   for (int s = 0; s < sp.nsrc; ++s) j.src_chunks[s] = P->acts[sp.src[s]].C / j.Cc;
+  j.ksteps = j.Cc / 16;
+  if (sp.nsrc == 1 && j.src_chunks[0] == 1 && sp.src_real_c[0] < j.Cc)   // e.g. the 35 qpos channels padded to 64
+    j.ksteps = (sp.src_real_c[0] + 15) / 16;
 
   // tile shape
   j.l_stride = sp.kind == CONV_DOWN ? 2 : 1;
