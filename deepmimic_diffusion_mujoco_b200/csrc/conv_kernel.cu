@@ -45,8 +45,11 @@ constexpr int kPollWarp = 2;   // epilogue warp that waits on the accumulator mb
 // Optional phase trace (debug): tr points at kTraceSlots slots of this (job, unit); null in production.
 // Slots 0-15: phases; 16 + 2i / 17 + 2i: issue of weight load i by the producer / its arrival seen by the MMA warp.
 constexpr int kTraceSlots = 64;
+// TR = false compiles every mark away: the production kernel carries no trace code (it costs ~3 % of the loop
+// time through instruction-cache footprint alone); dm_plan_set_trace selects the TR = true instantiation.
+template <bool TR>
 __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
-  if (tr) {
+  if (TR && tr) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     tr[ev] = t;
@@ -81,13 +84,14 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
 }
 
 // ================================ TMA producer (one warp, one elected lane issues) =========================
+template <bool TR>
 __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
                                               const CUtensorMap* x_map, int g, int b0, int n0, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
                                               RoleState& rs, unsigned long long* tr, uint32_t smem_base,
                                               const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0) {
   const bool leader = elect_one_sync();
   int as = 0, ws = 0, wi = 0;
-  if (leader) trace_mark(tr, 2);
+  if (leader) trace_mark<TR>(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
     int cin_off = 0;
@@ -112,7 +116,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
               tma_load_4d(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws],
                           cin_off + ch * job.Cc, n0, t < job.ntaps ? job.taps[t].wtap : 0, 0);
 #ifdef DM_TRACE_WLOADS
-              if (tr && wi < 24) trace_mark(tr, 16 + 2 * wi);
+              if (tr && wi < 24) trace_mark<TR>(tr, 16 + 2 * wi);
 #endif
             }
             rs.w_bits ^= 1u << ws;
@@ -125,7 +129,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
       cin_off += nch * job.Cc;
     }
   }
-  if (leader) trace_mark(tr, 4);
+  if (leader) trace_mark<TR>(tr, 4);
   // Weight prefetch across the layer boundary: weights do not depend on activations.  Once this unit's MMAs
   // have all completed (its operand stages are dead), the first weight tiles of the next layer are loaded into
   // that layer's ring slots that lie beyond this layer's staged output tile; they land during the epilogue.
@@ -147,6 +151,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
 }
 
 // ================================ MMA issuer (one warp, one elected lane issues) ===========================
+template <bool TR>
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
   const bool leader = elect_one_sync();
@@ -172,16 +177,16 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
           rs.a_bits ^= 1u << as;
           tc_fence_after();
         }
-        if (leader && lt == 0 && cidx == 0) trace_mark(tr, 5);
+        if (leader && lt == 0 && cidx == 0) trace_mark<TR>(tr, 5);
         const uint32_t a_base16 =
             (job.a_res ? smem_base + (uint32_t)(job.a_res_off + cidx * job.a_res_chunk) : a_smem + as * job.a_stage_bytes) >> 4;
         for (int t = 0; t < job.ntaps + job.aux; ++t) {
           mbar_wait(&sh.w_full[ws], (rs.w_bits >> ws) & 1, 0x400 + ws);
           rs.w_bits ^= 1u << ws;
           tc_fence_after();
-          if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark(tr, 6);
+          if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark<TR>(tr, 6);
 #ifdef DM_TRACE_WLOADS
-          if (leader && tr && wi < 24) trace_mark(tr, 17 + 2 * wi);
+          if (leader && tr && wi < 24) trace_mark<TR>(tr, 17 + 2 * wi);
 #endif
           ++wi;
           const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
@@ -216,7 +221,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   }
   if (leader) {
     umma_commit(&sh.acc_full);
-    trace_mark(tr, 7);
+    trace_mark<TR>(tr, 7);
   }
   __syncwarp();
 }
@@ -320,6 +325,7 @@ __device__ __forceinline__ void staged_write(const ConvJob& job, uint32_t stg_da
 // ================================ epilogue (warps 0..15) ===================================
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
+template <bool TR>
 __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps* maps, int warp, int g, int b0, int n0,
                                               const float* tbias, int tbias_stride, uint32_t stg, ConvShared& sh,
                                               uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
@@ -346,7 +352,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   if (gn) {
     for (int i = tid; i < kEpiWarps * 256; i += kEpiThreads) sh.part[i] = 0.f;
   }
-  trace_mark(tr, 8);
+  trace_mark<TR>(tr, 8);
   // The previous layer's TMA store may still be reading the staging buffer (deferred wait of a resident link).
   if (tid == 0) tma_store_wait_read();
   // one warp waits for the accumulator; everybody else parks on the hardware barrier (no issue slots burnt)
@@ -354,7 +360,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   rs.acc_count++;
   named_bar_sync(1, kEpiThreads);
   tc_fence_after();
-  trace_mark(tr, 9);
+  trace_mark<TR>(tr, 9);
   // Staged epilogue: every MMA has completed, so the operand stages are dead and the unit's output tile is
   // assembled there.  The residual tile (temporal.py:46) is TMA-loaded into the same buffer now; it lands
   // while pass 1 runs.  Block (plane p, channel block q) = kStageGap zero bytes | st_rows rows | kStageGap zero
@@ -465,10 +471,10 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         }
       }
     }
-    trace_mark(tr, 40);
+    trace_mark<TR>(tr, 40);
     if (job.aux && tid == 0) tma_store_wait_read();   // the auxiliary tile has left the staging buffer
     named_bar_sync(1, kEpiThreads);
-    trace_mark(tr, 41);
+    trace_mark<TR>(tr, 41);
     if (tid < 128) {                       // one thread per (sample, group): fixed-order sum over the warps
       float a = 0.f, q2 = 0.f;
 #pragma unroll
@@ -484,7 +490,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       (&sh.stat[0][0][0])[tid * 2 + 1] = rsqrtf(var + 1e-5f);
     }
     named_bar_sync(1, kEpiThreads);
-    trace_mark(tr, 42);
+    trace_mark<TR>(tr, 42);
     // scale/shift table: y = x * sc + sf with sc = rstd * gamma, sf = (bias - mean) * sc + beta
     const int tab_stride = 2 * Nc + 4;
     if (kEpiThreads % Nc == 0) {           // Nc in {32, 64, 128, ...}: no integer division in the loop
@@ -513,7 +519,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     }
     named_bar_sync(1, kEpiThreads);
   }
-  trace_mark(tr, 10);
+  trace_mark<TR>(tr, 10);
 
   // ---- pass 2: normalise, Mish, + time bias, + residual, split to fp16 hi/lo, store ----
   const int bg = g * kGroupSamples + b0 + b;
@@ -624,7 +630,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
             lds128f(stg + 4u * (uint32_t)(bb * job.f32_stride) + 16u * (uint32_t)o);
     }
   }
-  trace_mark(tr, 14);
+  trace_mark<TR>(tr, 14);
   if (staged) {
     if (job.next_res) {
       // zero the halo gaps of every block (other layers' operand stages alias this memory)
@@ -638,7 +644,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     }
     fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine / next MMAs
     named_bar_sync(1, kEpiThreads);
-    trace_mark(tr, 15);
+    trace_mark<TR>(tr, 15);
     if (tid == 0) {
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
@@ -652,10 +658,11 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     }
     __syncwarp();
   }
-  trace_mark(tr, 11);
+  trace_mark<TR>(tr, 11);
 }
 
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
+template <bool TR>
 __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp,
                                          int g, int b0, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
@@ -664,11 +671,11 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
   const uint32_t a_smem = smem;
   const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
   if (warp == kProducerWarp) {
-    producer_unit(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
+    producer_unit<TR>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
   } else if (warp == kMmaWarp) {
-    mma_unit(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr);
+    mma_unit<TR>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr);
   } else {
-    epilogue_unit(job, maps, warp, g, b0, n0, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
+    epilogue_unit<TR>(job, maps, warp, g, b0, n0, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
 }
 
@@ -699,7 +706,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = sh.tmem_slot;
   RoleState rs;
-  run_unit(job, &maps, warp, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
+  run_unit<false>(job, &maps, warp, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
            job.tbias, job.tbias_stride, smem, sh, tmem_base, rs);
   tc_fence_before();
   __syncthreads();
@@ -728,6 +735,7 @@ __device__ __forceinline__ void local_sync(bool wrote_global, bool issues_tma) {
   if (issues_tma) fence_proxy_async_global();
 }
 
+template <bool TR>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   const uint32_t smem = aligned_dyn_smem();
@@ -753,9 +761,9 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
       const int t_index = lp.steps[k].t_index;
       for (int ji = 0; ji < lp.n_jobs; ++ji) {
         const ConvJob& job = lp.jobs[ji];   // kernel-parameter (constant) space: warp-uniform
-        unsigned long long* tr = (lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
+        unsigned long long* tr = (TR && lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
                                      ? lp.trace + (size_t)ji * kTraceSlots : nullptr;
-        if (threadIdx.x == 0 && tr) { trace_mark(tr, 0); tr[1] = (unsigned long long)clock64(); }   // slot 1: SM clock (effective MHz)
+        if (TR && threadIdx.x == 0 && tr) { trace_mark<TR>(tr, 0); tr[1] = (unsigned long long)clock64(); }   // slot 1: SM clock (effective MHz)
         const int slices = job.slices;
         const int off = job.tb_off;
         const float* tb = off >= 0 ? lp.tb_table + (size_t)t_index * lp.TB + off : nullptr;
@@ -773,7 +781,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         const int n_n0 = njob.S == 8 ? 0 : rank * njob.Nc;
         for (int sl = first; sl < slices; sl += stride) {
           const bool last_unit = sl + stride >= slices;
-          run_unit(job, maps, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr,
+          run_unit<TR>(job, maps, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr,
                    last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, n_n0);
           if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit
             tc_fence_before();
@@ -781,7 +789,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
             tc_fence_after();
           }
         }
-        if (threadIdx.x == 0) trace_mark(tr, 12);
+        if (threadIdx.x == 0) trace_mark<TR>(tr, 12);
         if (job.next_res) {   // CTA-local hand-over of the staged tile (writers fenced the async proxy already)
           tc_fence_before();
           __syncthreads();
@@ -791,7 +799,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         } else {
           job_sync(warp < kEpiWarps && job.st_cw == 0, warp == kProducerWarp);
         }
-        if (threadIdx.x == 0) trace_mark(tr, 13);
+        if (threadIdx.x == 0) trace_mark<TR>(tr, 13);
       }
     }
     // ---- K4: init (k == 0) or fused posterior + noise + inpaint + operand re-pack for this CTA's samples ----
@@ -828,11 +836,14 @@ cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_grou
 cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(sample_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(sample_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(sample_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  sample_loop_kernel<<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+  if (lp.trace) sample_loop_kernel<true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+  else sample_loop_kernel<false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
   return cudaGetLastError();
 }
 

@@ -35,7 +35,10 @@ def apply_conditioning_motion_editing(x):
     return x
 
 
+import weakref
+
 _PROBES = {}
+_VERIFIED = weakref.WeakKeyDictionary()   # conditioning function -> {(shape, device)} verified as pure overwrites
 
 
 def _probes(shape, device):
@@ -62,10 +65,22 @@ def trace_conditioning(fn, shape, device):
         raise DmError("conditioning_fn must return a tensor of the input shape")
     mask = ~torch.isnan(out)
     value = torch.where(mask, out, torch.zeros_like(out))
-    out2 = fn(keep.clone())
+    # x-independence is a property of the function: verified with a second probe the first time this function
+    # object is seen for this shape (its mask/values are re-read on every call above)
+    key = (tuple(shape), str(device))
+    try:
+        seen = _VERIFIED.setdefault(fn, set())
+    except TypeError:          # not weak-referenceable: verify every time
+        seen = set()
+    if key in seen:
+        pure = torch.ones((), dtype=torch.bool, device=out.device)
+    else:
+        out2 = fn(keep.clone())
+        pure = (out2 == torch.where(mask, value, keep)).all()
     # one device->host read for every property the host needs
-    flags = torch.stack([(out2 == torch.where(mask, value, keep)).all(), mask.any(), (mask == mask[:1]).all(),
-                         (value == value[:1]).all()]).cpu().tolist()
+    flags = torch.stack([pure, mask.any(), (mask == mask[:1]).all(), (value == value[:1]).all()]).cpu().tolist()
+    if flags[0]:
+        seen.add(key)
     if not flags[0]:
         raise DmError("conditioning_fn is not an x-independent overwrite x = where(mask, value, x); it cannot be "
                       "fused into the sampling kernels (no fallback)")
