@@ -19,7 +19,8 @@ constexpr int kMaxTaps = 5;
 constexpr int kEpiWarps = 16;       // epilogue warps 0-15: TMEM lane quarter = warp % 4, work slice = warp / 4
 constexpr int kProducerWarp = 16;   // one elected lane issues TMA
 constexpr int kMmaWarp = 17;        // one elected lane issues tcgen05.mma; the warp owns the TMEM allocation
-constexpr int kConvThreads = (kEpiWarps + 2) * 32;
+constexpr int kMmaWarpB = 18;       // second MMA issuer: one thread alone cannot keep the tensor pipe busy (see mma_unit)
+constexpr int kConvThreads = (kEpiWarps + 3) * 32;
 
 struct ConvTap {
   int wtap;    // index into the packed weight's tap dimension
@@ -66,6 +67,10 @@ struct ConvJob {
   int a_stage_bytes, w_stage_bytes, a_plane_bytes, w_plane_bytes;
   int a_tx_bytes, w_tx_bytes;
   int tmem_cols;
+  int mma_mode;           // 0: warp A issues every tap; 1: taps alternate between the two issuer warps, each with its
+                          // own accumulator set; 2: ConvTranspose, one accumulator phase per warp (see mma_unit)
+  int acc2;               // 1: a second accumulator set (the odd taps) at TMEM column acc2_off is added by the epilogue
+  int acc2_off;
   // epilogue
   int epi;
   int Cout;               // real output channels

@@ -76,9 +76,9 @@ struct RoleState {
 };
 
 __device__ __forceinline__ void init_shared(ConvShared& sh) {
-  for (int i = 0; i < 2; ++i) { mbar_init(&sh.a_full[i], 1); mbar_init(&sh.a_empty[i], 1); }
-  for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], 1); }
-  mbar_init(&sh.acc_full, 1);
+  for (int i = 0; i < 2; ++i) { mbar_init(&sh.a_full[i], 1); mbar_init(&sh.a_empty[i], 2); }   // both MMA warps release
+  for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], 2); }
+  mbar_init(&sh.acc_full, 2);
   mbar_init(&sh.res_full, 1);
   fence_barrier_init();
 }
@@ -150,13 +150,26 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
   __syncwarp();
 }
 
-// ================================ MMA issuer (one warp, one elected lane issues) ===========================
+// ================================ MMA issuers (two warps, one elected lane each) ===========================
+// A single thread cannot keep the tensor pipe busy: every mbarrier poll or descriptor recomputation between two
+// taps shows up as a pipe bubble (measured: 86-110 cycles per N=128 MMA from one thread against the 64-cycle MAC
+// floor; two threads alternating taps reach 64.4).  So two warps issue.  job.mma_mode:
+//   0  warp A issues every tap (B only keeps the ring bookkeeping in step);
+//   1  taps alternate: A takes the even taps, B the odd ones.  Each warp accumulates into its OWN accumulator
+//      set (B's at column job.acc2_off) and the epilogue adds the two: every accumulator sees one thread's MMAs
+//      in program order, so results stay bit-reproducible.  An auxiliary tap has its own accumulators anyway;
+//   2  ConvTranspose: taps 0,1 (even outputs) on A, taps 2,3 (odd outputs) on B, disjoint accumulators.
+// Each tap's weight stage is released (w_empty) by the warp that issued its MMAs; A stages and the unit's
+// acc_full take one commit from each warp.
 template <bool TR>
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
-                                         ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
+                                         ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr,
+                                         const int which) {
   const bool leader = elect_one_sync();
+  if (which != 0) tr = nullptr;
   const int S = job.S, Nc = job.Nc;
   const int MT = job.n_ltiles * job.Mt;
+  const int mode = job.mma_mode;
   const uint32_t idesc = umma_idesc_f16(128, Nc);
   const int ksteps = job.ksteps;   // 16-channel k-steps per chunk that hold real input channels (zero padding skipped)
   const int pos_per_mt = 128 / S;
@@ -178,38 +191,52 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
           tc_fence_after();
         }
         if (leader && lt == 0 && cidx == 0) trace_mark<TR>(tr, 5);
+#ifdef DM_TRACE_WLOADS
+        if (leader && tr && lt == 0 && cidx < 8) trace_mark<TR>(tr, 48 + cidx);
+#endif
         const uint32_t a_base16 =
             (job.a_res ? smem_base + (uint32_t)(job.a_res_off + cidx * job.a_res_chunk) : a_smem + as * job.a_stage_bytes) >> 4;
         for (int t = 0; t < job.ntaps + job.aux; ++t) {
-          mbar_wait(&sh.w_full[ws], (rs.w_bits >> ws) & 1, 0x400 + ws);
-          rs.w_bits ^= 1u << ws;
-          tc_fence_after();
-          if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark<TR>(tr, 6);
-#ifdef DM_TRACE_WLOADS
-          if (leader && tr && wi < 24) trace_mark<TR>(tr, 17 + 2 * wi);
-#endif
-          ++wi;
-          const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
           const bool is_aux = t >= job.ntaps;
-          const int shift = is_aux ? job.aux_shift : job.taps[t].shift, phase = is_aux ? 0 : job.taps[t].phase;
-          const bool first = cidx == 0 && (is_aux || job.taps[t].first != 0);
-          uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * Nc) + (is_aux ? (uint32_t)job.aux_col0 : 0u);
-          uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
-          for (int mt = 0; mt < job.Mt; ++mt, d += Nc, a16 += mt_step16) {
-            if (leader) {
-              for (int k = 0; k < ksteps; ++k) {
-                const uint64_t a_hi = hi_a | ((a16 + 2 * k) & 0x3FFF);
-                const uint64_t a_lo = hi_a | ((a16 + a_plane16 + 2 * k) & 0x3FFF);
-                const uint64_t w_hi = hi_w | ((w16 + 2 * k) & 0x3FFF);
-                const uint64_t w_lo = hi_w | ((w16 + w_plane16 + 2 * k) & 0x3FFF);
-                umma_f16(d, a_lo, w_hi, idesc, !(first && k == 0));
-                umma_f16(d, a_hi, w_lo, idesc, 1);
-                umma_f16(d, a_hi, w_hi, idesc, 1);
+          const int owner = mode == 0 ? 0 : mode == 1 ? (t & 1) : job.taps[t].phase;
+          const uint32_t w_par = (rs.w_bits >> ws) & 1;
+          rs.w_bits ^= 1u << ws;
+          // Both warps observe every fill of every stage, in order, and the stage is not refilled before both have:
+          // a parity wait may only be one phase behind the barrier, so the warp that does not own a tap still
+          // waits for its fill and then releases its half of w_empty (the owner's half is the tcgen05.commit).
+          mbar_wait(&sh.w_full[ws], w_par, 0x400 + ws);
+          if (owner != which) {
+            if (leader) mbar_arrive(&sh.w_empty[ws]);
+          } else {
+            tc_fence_after();
+            if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark<TR>(tr, 6);
+#ifdef DM_TRACE_WLOADS
+            if (leader && tr && wi < 24) trace_mark<TR>(tr, 17 + 2 * wi);
+#endif
+            const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
+            const int shift = is_aux ? job.aux_shift : job.taps[t].shift, phase = is_aux ? 0 : job.taps[t].phase;
+            // mode 1: B's taps go to the second accumulator set, so its first tap of the unit overwrites too
+            const bool first = cidx == 0 && (is_aux || job.taps[t].first != 0 || (mode == 1 && t == 1));
+            uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * Nc) +
+                         (is_aux ? (uint32_t)job.aux_col0 : (mode == 1 && which != 0) ? (uint32_t)job.acc2_off : 0u);
+            uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
+            for (int mt = 0; mt < job.Mt; ++mt, d += Nc, a16 += mt_step16) {
+              if (leader) {
+                for (int k = 0; k < ksteps; ++k) {
+                  const uint64_t a_hi = hi_a | ((a16 + 2 * k) & 0x3FFF);
+                  const uint64_t a_lo = hi_a | ((a16 + a_plane16 + 2 * k) & 0x3FFF);
+                  const uint64_t w_hi = hi_w | ((w16 + 2 * k) & 0x3FFF);
+                  const uint64_t w_lo = hi_w | ((w16 + w_plane16 + 2 * k) & 0x3FFF);
+                  umma_f16(d, a_lo, w_hi, idesc, !(first && k == 0));
+                  umma_f16(d, a_hi, w_lo, idesc, 1);
+                  umma_f16(d, a_hi, w_hi, idesc, 1);
+                }
               }
             }
+            __syncwarp();
+            if (leader) umma_commit(&sh.w_empty[ws]);
           }
-          __syncwarp();
-          if (leader) umma_commit(&sh.w_empty[ws]);
+          ++wi;
           if (++ws == job.n_w_stages) ws = 0;
         }
         if (!job.a_res) {
@@ -421,6 +448,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       for (int cc = (slice - T * nchunks) & 3; cc < nchunks; cc += 4) {   // units u = T * nchunks + cc with u % 4 == slice
         tmem_ld32(trow + (uint32_t)(T * Nc + cc * 32), v);
         tmem_ld_wait();
+        if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * Nc + cc * 32), v);
         float s[8], q[8];
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
@@ -539,6 +567,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       const int cb = cc * 32;
       tmem_ld32(trow + (uint32_t)(pt * Nc + cc * 32), v);
       tmem_ld_wait();
+      if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + pt * Nc + cc * 32), v);
       if (!ok) continue;
       if (gn) {
         const float* trow_tab = &sh.part[b * (2 * Nc + 4) + 2 * cb];
@@ -672,8 +701,8 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
   const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
   if (warp == kProducerWarp) {
     producer_unit<TR>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
-  } else if (warp == kMmaWarp) {
-    mma_unit<TR>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr);
+  } else if (warp == kMmaWarp || warp == kMmaWarpB) {
+    mma_unit<TR>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);
   } else {
     epilogue_unit<TR>(job, maps, warp, g, b0, n0, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
@@ -764,6 +793,9 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         unsigned long long* tr = (TR && lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
                                      ? lp.trace + (size_t)ji * kTraceSlots : nullptr;
         if (TR && threadIdx.x == 0 && tr) { trace_mark<TR>(tr, 0); tr[1] = (unsigned long long)clock64(); }   // slot 1: SM clock (effective MHz)
+#ifdef DM_DEBUG_WAIT
+        if (threadIdx.x == 0) g_dm_dbg_pos[blockIdx.x] = (unsigned)ji | ((unsigned)k << 7);
+#endif
         const int slices = job.slices;
         const int off = job.tb_off;
         const float* tb = off >= 0 ? lp.tb_table + (size_t)t_index * lp.TB + off : nullptr;

@@ -225,7 +225,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   // 16-sample units are split over the two CTAs of a cluster by N slice: prefer an even slice count
   if (j.S == 16 && (cout_pad / Nc) % 2 == 1 && Nc % 64 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
   const int mt_all = j.n_ltiles * j.Mt;
-  const int acc_sets = j.nphase + (sp.aux_wkey.empty() ? 0 : 1);   // the auxiliary conv has its own accumulators
+  int acc_sets = j.nphase + (sp.aux_wkey.empty() ? 0 : 1);   // the auxiliary conv has its own accumulators
   if (!sp.aux_wkey.empty() && acc_sets * mt_all * Nc > 512)
     return fail(DM_ERR_STATE, "%s: no TMEM room for the fused residual conv", sp.name.c_str());   // caller falls back
   while (j.nphase * mt_all * Nc > 512 && Nc > 32 && (Nc / 2) % 32 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
@@ -233,6 +233,15 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     return fail(DM_ERR_ARG, "%s: horizon too long for the TMEM-resident GroupNorm design (H <= 256)", sp.name.c_str());
   if (gn && Nc % cg) return fail(DM_ERR_ARG, "%s: N slice does not hold whole GroupNorm groups", sp.name.c_str());
   j.Nc = Nc;
+  // two MMA issuer warps with one accumulator set each (conv_kernel.cu, mma_unit) when TMEM has room for it
+  j.acc2 = 0;
+  j.acc2_off = 0;
+  if (j.nphase == 1 && j.ntaps >= 2 && (acc_sets + 1) * mt_all * Nc <= 512 && !getenv("DM_B200_SINGLE_ISSUER") &&
+      !getenv("DM_B200_NO_MODE1")) {
+    j.acc2 = 1;
+    j.acc2_off = mt_all * Nc;
+    ++acc_sets;
+  }
   ly.slices = cout_pad / Nc;
   j.slices = ly.slices;
   j.tb_off = sp.tb_off;
@@ -437,10 +446,16 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     }
     j.aux = 1;
     j.aux_shift = j.halo_lo;
-    j.aux_col0 = j.nphase * mt_all * Nc;
+    j.aux_col0 = (j.nphase + j.acc2) * mt_all * Nc;
     j.aux_bias = dxb;
     ly.aux_act = xi;
     if (aux_idx) *aux_idx = xi;
+  }
+  // ---- MMA issue split over the two issuer warps ----
+  j.mma_mode = 0;
+  if (!getenv("DM_B200_SINGLE_ISSUER")) {
+    if (j.nphase == 2) j.mma_mode = getenv("DM_B200_NO_MODE2") ? 0 : 2;   // taps 0,1 -> phase 0, taps 2,3 -> phase 1
+    else if (j.acc2 || (j.ntaps == 1 && j.aux)) j.mma_mode = getenv("DM_B200_NO_MODE1") ? 0 : 1;
   }
   // ---- resident link: read the previous layer's staged tile in place (fused loop only) ----
   if (!P->layers.empty() && !getenv("DM_B200_NO_RESIDENT")) {
@@ -715,6 +730,13 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
     j.sync_local = 0;
     DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));
     P->last_launches++;
+    if (getenv("DM_B200_DEBUG_SYNC")) {   // debugging aid: find the layer whose kernel faults
+      const cudaError_t e = cudaStreamSynchronize(s);
+      fprintf(stderr, "[dm debug] %-28s mode %d S %d Mt %d ltiles %d Nc %d slices %d chunks %d+%d taps %d aux %d : %s\n", ly.name.c_str(),
+              j.mma_mode, j.S, j.Mt, j.n_ltiles, j.Nc, j.slices, j.src_chunks[0], j.nsrc > 1 ? j.src_chunks[1] : 0, j.ntaps, j.aux,
+              cudaGetErrorString(e));
+      if (e != cudaSuccess) return fail(DM_ERR_CUDA, "layer %s failed", ly.name.c_str());
+    }
   }
   return DM_OK;
 }
@@ -926,6 +948,16 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   static thread_local LoopParams lp;   // ~19 KB: keep it off the stack
   lp.n_jobs = (int)P->layers.size();
   for (int i = 0; i < lp.n_jobs; ++i) lp.jobs[i] = P->layers[i].job;
+  if (getenv("DM_B200_DUMP_PLAN")) {   // debugging aid: the fused loop's job list
+    for (int i = 0; i < lp.n_jobs; ++i) {
+      const ConvJob& j = lp.jobs[i];
+      fprintf(stderr, "[dm plan] %2d %-24s S %2d Mt %d lt %d Nc %3d sl %d ch %d+%d taps %d aux %d mode %d acc2 %d | A st %d x %6d  W st %d x %6d "
+              "a_res %d w_off %6d pre_next %d next_res %d local %d cols %d\n", i, P->layers[i].name.c_str(), j.S, j.Mt, j.n_ltiles, j.Nc,
+              j.slices, j.src_chunks[0], j.nsrc > 1 ? j.src_chunks[1] : 0, j.ntaps, j.aux, j.mma_mode, j.acc2, j.n_a_stages,
+              j.a_stage_bytes, j.n_w_stages, j.w_stage_bytes, j.a_res, j.a_res ? j.w_off_res : j.n_a_stages * j.a_stage_bytes, j.pre_next,
+              j.next_res, j.sync_local, j.tmem_cols);
+    }
+  }
   lp.maps = P->maps_dev;
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;

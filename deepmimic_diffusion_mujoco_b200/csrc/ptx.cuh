@@ -14,6 +14,9 @@ namespace dm {
 // traps, so that a hung pipeline becomes a loud CUDA error instead of a dead GPU box.
 // ----------------------------------------------------------------------------------------------
 __device__ unsigned int g_dm_device_error = 0;
+#ifdef DM_DEBUG_WAIT
+__device__ volatile unsigned int g_dm_dbg_pos[512];   // per CTA: job index | step << 7
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -51,11 +54,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t code) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
+#ifdef DM_DEBUG_WAIT
+    // debugging aid: record the first stuck wait and let the kernel run to its end (results are garbage)
+    if (*(volatile unsigned int*)&g_dm_device_error != 0u) return;
+    if (++spins > (1u << 20)) {
+      atomicCAS(&g_dm_device_error, 0u, (code & 0xFFFu) | ((threadIdx.x >> 5) << 12) | ((unsigned)g_dm_dbg_pos[blockIdx.x] << 17));
+      __threadfence();
+      return;
+    }
+#else
     if (++spins > (1u << 26)) {
       atomicExch(&g_dm_device_error, code);
       __threadfence_system();
       __trap();
     }
+#endif
   }
 }
 
@@ -143,6 +156,22 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                    smem_u32(bar))
                : "memory");
+}
+// v[0..31] += 32 lanes x 32 consecutive fp32 columns (two 16-column loads: keeps the live registers at 48)
+__device__ __forceinline__ void tmem_ld32_add(uint32_t taddr, float* v) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
+        "%15}, [%16];\n\ttcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr + 16u * h)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[16 * h + i] += __uint_as_float(r[i]);
+  }
 }
 // 32 lanes x 32 consecutive fp32 columns: thread i of the warp gets row (lane base + i).
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {

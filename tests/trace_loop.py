@@ -39,8 +39,9 @@ if os.environ.get("TRACE_PASS1"):
 detail = os.environ.get("TRACE_DETAIL")
 if detail:
     for i, (n, C, L) in enumerate(names):
-        if detail in n:
+        if any(d in n for d in detail.split(",")):
             r = t[i]
+            print(n, "A chunks seen by MMA warp (us):", "  ".join(f"{(r[48+c]-r[0])/1e3:.2f}" for c in range(8) if r[48+c] > 0))
             print(n, "W loads: (issue, seen by MMA warp) us from layer start")
             print("  " + "  ".join(f"{(r[16+2*w]-r[0])/1e3:.2f}/{(r[17+2*w]-r[0])/1e3:.2f}" for w in range(24) if r[17+2*w] > 0))
 print("effective SM clock MHz over the traced step:", (t[-1, 1] - t[0, 1]) / ((t[-1, 0] - t[0, 0]) / 1e3))
