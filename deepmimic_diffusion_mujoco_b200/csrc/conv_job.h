@@ -67,9 +67,9 @@ struct ConvJob {
   int a_stage_bytes, w_stage_bytes, a_plane_bytes, w_plane_bytes;
   int a_tx_bytes, w_tx_bytes;
   int tmem_cols;
-  int mma_mode;           // 0: warp A issues every tap; 1: taps alternate between the two issuer warps, each with its
-                          // own accumulator set; 2: ConvTranspose, one accumulator phase per warp (see mma_unit)
-  int acc2;               // 1: a second accumulator set (the odd taps) at TMEM column acc2_off is added by the epilogue
+  int mma_mode;           // 0: warp A issues every MMA; 1: the two issuer warps split the k-steps of every tap, each
+                          // with its own accumulator set (see mma_unit)
+  int acc2;               // 1: a second accumulator set at TMEM column acc2_off is added by the epilogue
   int acc2_off;
   // epilogue
   int epi;

@@ -153,14 +153,14 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
 // ================================ MMA issuers (two warps, one elected lane each) ===========================
 // A single thread cannot keep the tensor pipe busy: every mbarrier poll or descriptor recomputation between two
 // taps shows up as a pipe bubble (measured: 86-110 cycles per N=128 MMA from one thread against the 64-cycle MAC
-// floor; two threads alternating taps reach 64.4).  So two warps issue.  job.mma_mode:
-//   0  warp A issues every tap (B only keeps the ring bookkeeping in step);
-//   1  taps alternate: A takes the even taps, B the odd ones.  Each warp accumulates into its OWN accumulator
-//      set (B's at column job.acc2_off) and the epilogue adds the two: every accumulator sees one thread's MMAs
-//      in program order, so results stay bit-reproducible.  An auxiliary tap has its own accumulators anyway;
-//   2  ConvTranspose: taps 0,1 (even outputs) on A, taps 2,3 (odd outputs) on B, disjoint accumulators.
-// Each tap's weight stage is released (w_empty) by the warp that issued its MMAs; A stages and the unit's
-// acc_full take one commit from each warp.
+// floor; two threads reach 64.4).  So two warps issue.  job.mma_mode:
+//   0  warp A issues everything (B only keeps the ring bookkeeping in step);
+//   1  every tap is shared: A issues the first half of its k-steps, B the second half, each into its OWN
+//      accumulator set (B's at column job.acc2_off); the epilogue adds the two.  Every accumulator sees one
+//      thread's MMAs in program order, so results stay bit-reproducible.  The auxiliary tap (one accumulator
+//      set) is B's alone.
+// A weight stage is released (w_empty, two arrivals) by both warps; A stages and the unit's acc_full take one
+// commit from each warp as well.
 template <bool TR>
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr,
@@ -198,14 +198,17 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
             (job.a_res ? smem_base + (uint32_t)(job.a_res_off + cidx * job.a_res_chunk) : a_smem + as * job.a_stage_bytes) >> 4;
         for (int t = 0; t < job.ntaps + job.aux; ++t) {
           const bool is_aux = t >= job.ntaps;
-          const int owner = mode == 0 ? 0 : mode == 1 ? (t & 1) : job.taps[t].phase;
+          // mode 1: both warps work on every tap, A on the first half of its k-steps and B on the second half;
+          // the auxiliary tap (single accumulator set) is B's alone.  mode 0: everything is A's.
+          const bool both = mode == 1 && !is_aux;
+          const bool mine = both || which == mode;
           const uint32_t w_par = (rs.w_bits >> ws) & 1;
           rs.w_bits ^= 1u << ws;
           // Both warps observe every fill of every stage, in order, and the stage is not refilled before both have:
-          // a parity wait may only be one phase behind the barrier, so the warp that does not own a tap still
-          // waits for its fill and then releases its half of w_empty (the owner's half is the tcgen05.commit).
+          // a parity wait may only be one phase behind the barrier, so a warp without work on a tap still waits
+          // for its fill and then releases its half of w_empty (otherwise its half is the tcgen05.commit).
           mbar_wait(&sh.w_full[ws], w_par, 0x400 + ws);
-          if (owner != which) {
+          if (!mine) {
             if (leader) mbar_arrive(&sh.w_empty[ws]);
           } else {
             tc_fence_after();
@@ -215,19 +218,20 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
 #endif
             const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
             const int shift = is_aux ? job.aux_shift : job.taps[t].shift, phase = is_aux ? 0 : job.taps[t].phase;
-            // mode 1: B's taps go to the second accumulator set, so its first tap of the unit overwrites too
-            const bool first = cidx == 0 && (is_aux || job.taps[t].first != 0 || (mode == 1 && t == 1));
+            const bool first = cidx == 0 && (is_aux || job.taps[t].first != 0);
+            const int k_mid = (ksteps + 1) >> 1;
+            const int k0 = both && which ? k_mid : 0, k1 = both && !which ? k_mid : ksteps;
             uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * Nc) +
-                         (is_aux ? (uint32_t)job.aux_col0 : (mode == 1 && which != 0) ? (uint32_t)job.acc2_off : 0u);
+                         (is_aux ? (uint32_t)job.aux_col0 : which ? (uint32_t)job.acc2_off : 0u);
             uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
             for (int mt = 0; mt < job.Mt; ++mt, d += Nc, a16 += mt_step16) {
               if (leader) {
-                for (int k = 0; k < ksteps; ++k) {
+                for (int k = k0; k < k1; ++k) {
                   const uint64_t a_hi = hi_a | ((a16 + 2 * k) & 0x3FFF);
                   const uint64_t a_lo = hi_a | ((a16 + a_plane16 + 2 * k) & 0x3FFF);
                   const uint64_t w_hi = hi_w | ((w16 + 2 * k) & 0x3FFF);
                   const uint64_t w_lo = hi_w | ((w16 + w_plane16 + 2 * k) & 0x3FFF);
-                  umma_f16(d, a_lo, w_hi, idesc, !(first && k == 0));
+                  umma_f16(d, a_lo, w_hi, idesc, !(first && k == k0));
                   umma_f16(d, a_hi, w_lo, idesc, 1);
                   umma_f16(d, a_hi, w_hi, idesc, 1);
                 }

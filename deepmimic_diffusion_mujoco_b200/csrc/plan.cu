@@ -236,11 +236,10 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   // two MMA issuer warps with one accumulator set each (conv_kernel.cu, mma_unit) when TMEM has room for it
   j.acc2 = 0;
   j.acc2_off = 0;
-  if (j.nphase == 1 && j.ntaps >= 2 && (acc_sets + 1) * mt_all * Nc <= 512 && !getenv("DM_B200_SINGLE_ISSUER") &&
-      !getenv("DM_B200_NO_MODE1")) {
+  if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_all * Nc <= 512 && !getenv("DM_B200_SINGLE_ISSUER")) {
     j.acc2 = 1;
-    j.acc2_off = mt_all * Nc;
-    ++acc_sets;
+    j.acc2_off = j.nphase * mt_all * Nc;
+    acc_sets += j.nphase;
   }
   ly.slices = cout_pad / Nc;
   j.slices = ly.slices;
@@ -446,17 +445,12 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     }
     j.aux = 1;
     j.aux_shift = j.halo_lo;
-    j.aux_col0 = (j.nphase + j.acc2) * mt_all * Nc;
+    j.aux_col0 = j.nphase * (1 + j.acc2) * mt_all * Nc;
     j.aux_bias = dxb;
     ly.aux_act = xi;
     if (aux_idx) *aux_idx = xi;
   }
-  // ---- MMA issue split over the two issuer warps ----
-  j.mma_mode = 0;
-  if (!getenv("DM_B200_SINGLE_ISSUER")) {
-    if (j.nphase == 2) j.mma_mode = getenv("DM_B200_NO_MODE2") ? 0 : 2;   // taps 0,1 -> phase 0, taps 2,3 -> phase 1
-    else if (j.acc2 || (j.ntaps == 1 && j.aux)) j.mma_mode = getenv("DM_B200_NO_MODE1") ? 0 : 1;
-  }
+  j.mma_mode = j.acc2;   // 1: both issuer warps share every tap (conv_kernel.cu, mma_unit)
   // ---- resident link: read the previous layer's staged tile in place (fused loop only) ----
   if (!P->layers.empty() && !getenv("DM_B200_NO_RESIDENT")) {
     Layer& pv = P->layers.back();
