@@ -167,6 +167,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
                                          const int which) {
   const bool leader = elect_one_sync();
   if (which != 0) tr = nullptr;
+  if (leader) trace_mark<TR>(tr, 20);
   const int S = job.S, Nc = job.Nc;
   const int MT = job.n_ltiles * job.Mt;
   const int mode = job.mma_mode;
@@ -180,6 +181,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const uint32_t w_plane16 = job.w_plane_bytes >> 4;
   const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
   int as = 0, ws = 0, wi = 0;
+  if (leader) trace_mark<TR>(tr, 21);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     int cidx = 0;
     for (int src = 0; src < job.nsrc; ++src) {
@@ -797,6 +799,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         unsigned long long* tr = (TR && lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
                                      ? lp.trace + (size_t)ji * kTraceSlots : nullptr;
         if (TR && threadIdx.x == 0 && tr) { trace_mark<TR>(tr, 0); tr[1] = (unsigned long long)clock64(); }   // slot 1: SM clock (effective MHz)
+        if (TR && threadIdx.x == kMmaWarp * 32 && tr) trace_mark<TR>(tr, 22);
 #ifdef DM_DEBUG_WAIT
         if (threadIdx.x == 0) g_dm_dbg_pos[blockIdx.x] = (unsigned)ji | ((unsigned)k << 7);
 #endif
@@ -817,6 +820,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         const int n_n0 = njob.S == 8 ? 0 : rank * njob.Nc;
         for (int sl = first; sl < slices; sl += stride) {
           const bool last_unit = sl + stride >= slices;
+          if (TR && threadIdx.x == kMmaWarp * 32 && tr && sl == first) trace_mark<TR>(tr, 23);
           run_unit<TR>(job, maps, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr,
                    last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, n_n0);
           if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit

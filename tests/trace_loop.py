@@ -30,6 +30,11 @@ for i, (n, C, L) in enumerate(names):
     vals = [(r[k] - base) / 1e3 if r[k] > 0 else float("nan") for k in range(16)]
     print(f"{n[:27]:28s}", " ".join(f"{v:6.1f}" for v in vals), f"  {(r[13]-r[0])/1e3:7.1f}")
     tot += r[13] - r[0]
+if os.environ.get("TRACE_START"):
+    print("layer start (us): mma warp at loop top | before run_unit | mma warp enters | descriptors ready | first A seen | first W seen | epilogue params loaded")
+    for i, (n, C, L) in enumerate(names):
+        r = t[i]
+        print(f"{n[:27]:28s} " + " ".join(f"{(r[k]-r[0])/1e3:5.2f}" if r[k] > 0 else "  nan" for k in (22, 23, 20, 21, 5, 6, 8)))
 if os.environ.get("TRACE_PASS1"):
     print("pass 1 split (us after accF barrier): own partials | +barrier | combine+barrier | table+barrier")
     for i, (n, C, L) in enumerate(names):
