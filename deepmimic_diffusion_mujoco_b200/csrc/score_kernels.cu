@@ -10,254 +10,84 @@
 #include <stdint.h>
 
 #include "../../include/dm_b200.h"
+#include "fk_math.cuh"
 
 namespace dm {
 
 int fail(int code, const char* fmt, ...);
 int check_device();
 
-struct V3 { float x, y, z; };
-struct Q4 { float w, x, y, z; };
-
-__device__ __forceinline__ V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
-__device__ __forceinline__ V3 vadd(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ V3 vsub(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ Q4 qmul(Q4 a, Q4 b) {
-  Q4 r;
-  r.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
-  r.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
-  r.y = a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x;
-  r.z = a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w;
-  return r;
-}
-__device__ __forceinline__ Q4 qconj(Q4 a) { Q4 r; r.w = a.w; r.x = -a.x; r.y = -a.y; r.z = -a.z; return r; }
-__device__ __forceinline__ V3 qrot(Q4 q, V3 v) {
-  // v + 2 w (u x v) + 2 u x (u x v)
-  const float cx = q.y * v.z - q.z * v.y, cy = q.z * v.x - q.x * v.z, cz = q.x * v.y - q.y * v.x;
-  const float dx = q.y * cz - q.z * cy, dy = q.z * cx - q.x * cz, dz = q.x * cy - q.y * cx;
-  return v3(v.x + 2.f * (q.w * cx + dx), v.y + 2.f * (q.w * cy + dy), v.z + 2.f * (q.w * cz + dz));
-}
-__device__ __forceinline__ Q4 qaxis(int axis, float sign, float ang) {
-  float s, c;
-  sincosf(0.5f * ang, &s, &c);
-  Q4 r; r.w = c; r.x = 0.f; r.y = 0.f; r.z = 0.f;
-  if (axis == 0) r.x = sign * s; else if (axis == 1) r.y = sign * s; else r.z = sign * s;
-  return r;
-}
-__device__ __forceinline__ float qangle(Q4 q) {   // rotation angle in [0, pi]
-  const float vn = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z);
-  return 2.f * atan2f(vn, fabsf(q.w));
-}
-__device__ __forceinline__ V3 qlogvel(Q4 q, float inv_dt) {   // axis * angle / dt (mocap_v2.py:155-178)
-  const float vn = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z);
-  if (vn < 1e-12f) return v3(0.f, 0.f, 0.f);
-  float w = q.w, sx = 1.f;
-  if (w < 0.f) { w = -w; sx = -1.f; }
-  const float k = 2.f * atan2f(vn, w) * inv_dt * sx / vn;
-  return v3(q.x * k, q.y * k, q.z * k);
-}
-
-// rotate frame (pos, q) by a hinge about body-frame `axis` through body-frame anchor (ax, 0, 0)
-__device__ __forceinline__ void hinge(V3& pos, Q4& q, int axis, float sign, float anchor_x, float ang) {
-  if (anchor_x != 0.f) {
-    const V3 a = vadd(pos, qrot(q, v3(anchor_x, 0.f, 0.f)));
-    q = qmul(q, qaxis(axis, sign, ang));
-    pos = vsub(a, qrot(q, v3(anchor_x, 0.f, 0.f)));
-  } else {
-    q = qmul(q, qaxis(axis, sign, ang));
-  }
-}
-
-struct Feat {
-  Q4 rootq;
-  V3 rootw;
-  Q4 jq[8];      // local rotations of the eight 3-DoF joints (chest, neck, r/l shoulder, r/l hip, r/l ankle order below)
-  float ja[4];   // elbow / knee angles
-  float rate[28];
-  V3 ee[4];      // r_ankle, l_ankle, r_wrist, l_wrist relative to the root position
-  V3 com;
-};
-constexpr int kFeatFloats = sizeof(Feat) / sizeof(float);
-
-// body order of body_pos output == BODY_DEFS (utils/mocap_util.py:17-19)
-enum { B_ROOT, B_CHEST, B_NECK, B_RHIP, B_RKNEE, B_RANKLE, B_RSHO, B_RELB, B_RWRIST, B_LHIP, B_LKNEE, B_LANKLE, B_LSHO,
-       B_LELB, B_LWRIST, B_COUNT };
-
-__device__ __forceinline__ void ball(V3& pos, Q4& q, const float* a, float anchor_y_hinge_x) {
-  hinge(pos, q, 0, 1.f, 0.f, a[0]);
-  hinge(pos, q, 1, 1.f, anchor_y_hinge_x, a[1]);
-  hinge(pos, q, 2, 1.f, 0.f, a[2]);
-}
-__device__ __forceinline__ Q4 euler_q(const float* a) {
-  return qmul(qmul(qaxis(0, 1.f, a[0]), qaxis(1, 1.f, a[1])), qaxis(2, 1.f, a[2]));
-}
-
-// q: 35 qpos of this frame; qp: previous frame (== q for frame 0 -> zero velocity, mocap_v2.py:201-205)
-__device__ void frame_features(const float* q, const float* qp, float inv_dt, Feat& f, V3* bp) {
-  Q4 rq; rq.w = q[3]; rq.x = q[4]; rq.y = q[5]; rq.z = q[6];
-  float n = sqrtf(rq.w * rq.w + rq.x * rq.x + rq.y * rq.y + rq.z * rq.z);
-  if (n < 1e-10f) { rq.w = 1.f; rq.x = rq.y = rq.z = 0.f; } else { n = 1.f / n; rq.w *= n; rq.x *= n; rq.y *= n; rq.z *= n; }
-  Q4 pq; pq.w = qp[3]; pq.x = qp[4]; pq.y = qp[5]; pq.z = qp[6];
-  n = sqrtf(pq.w * pq.w + pq.x * pq.x + pq.y * pq.y + pq.z * pq.z);
-  if (n < 1e-10f) { pq.w = 1.f; pq.x = pq.y = pq.z = 0.f; } else { n = 1.f / n; pq.w *= n; pq.x *= n; pq.y *= n; pq.z *= n; }
-  f.rootq = rq;
-  f.rootw = qlogvel(qmul(qconj(pq), rq), inv_dt);
-  const V3 rp = v3(q[0], q[1], q[2]);
-  bp[B_ROOT] = rp;
-
-  V3 p; Q4 o;
-  // chest (qpos 7-9), neck (10-12)
-  p = vadd(rp, qrot(rq, v3(0.f, 0.f, 0.236151f))); o = rq;
-  ball(p, o, q + 7, 0.f);
-  const V3 chest_p = p; const Q4 chest_q = o;
-  bp[B_CHEST] = p;
-  p = vadd(chest_p, qrot(chest_q, v3(0.f, 0.f, 0.223894f))); o = chest_q;
-  ball(p, o, q + 10, 0.f);
-  bp[B_NECK] = p;
-  const V3 neck_p = p; const Q4 neck_q = o;
-  // arms: shoulder (13-15 / 17-19), elbow (16 / 20): axis (0,-1,0), anchor (0.028,0,0); wrist geom at (0,0,-0.258947)
-  V3 sh_p[2], el_p[2], wr_p[2]; Q4 sh_q[2], el_q[2];
-#pragma unroll
-  for (int s = 0; s < 2; ++s) {
-    const float ysign = s == 0 ? -1.f : 1.f;
-    const int qi = s == 0 ? 13 : 17;
-    p = vadd(chest_p, qrot(chest_q, v3(-0.02405f, ysign * 0.18311f, 0.2435f))); o = chest_q;
-    ball(p, o, q + qi, 0.f);
-    sh_p[s] = p; sh_q[s] = o;
-    p = vadd(p, qrot(o, v3(0.f, 0.f, -0.274788f)));
-    hinge(p, o, 1, -1.f, 0.028f, q[qi + 3]);
-    el_p[s] = p; el_q[s] = o;
-    wr_p[s] = vadd(p, qrot(o, v3(0.f, 0.f, -0.258947f)));
-  }
-  bp[B_RSHO] = sh_p[0]; bp[B_RELB] = el_p[0]; bp[B_RWRIST] = wr_p[0];
-  bp[B_LSHO] = sh_p[1]; bp[B_LELB] = el_p[1]; bp[B_LWRIST] = wr_p[1];
-  // legs: hip (21-23 / 28-30; y hinge anchored at (0.02,0,0)), knee (24 / 31; axis (0,-1,0), anchor (-0.035,0,0)),
-  // ankle (25-27 / 32-34; y hinge anchored at (-0.02,0,0))
-  V3 hip_p[2], kn_p[2], an_p[2]; Q4 hip_q[2], kn_q[2], an_q[2];
-#pragma unroll
-  for (int s = 0; s < 2; ++s) {
-    const float ysign = s == 0 ? -1.f : 1.f;
-    const int qi = s == 0 ? 21 : 28;
-    p = vadd(rp, qrot(rq, v3(0.f, ysign * 0.094887f, -0.05f))); o = rq;
-    ball(p, o, q + qi, 0.02f);
-    hip_p[s] = p; hip_q[s] = o;
-    p = vadd(p, qrot(o, v3(0.f, 0.f, -0.421546f)));
-    hinge(p, o, 1, -1.f, -0.035f, q[qi + 3]);
-    kn_p[s] = p; kn_q[s] = o;
-    p = vadd(p, qrot(o, v3(0.f, 0.f, -0.40987f)));
-    ball(p, o, q + qi + 4, -0.02f);
-    an_p[s] = p; an_q[s] = o;
-  }
-  bp[B_RHIP] = hip_p[0]; bp[B_RKNEE] = kn_p[0]; bp[B_RANKLE] = an_p[0];
-  bp[B_LHIP] = hip_p[1]; bp[B_LKNEE] = kn_p[1]; bp[B_LANKLE] = an_p[1];
-
-  // local joint rotations in qpos (BODY_JOINTS) order
-  f.jq[0] = euler_q(q + 7);  f.jq[1] = euler_q(q + 10); f.jq[2] = euler_q(q + 13); f.jq[3] = euler_q(q + 17);
-  f.jq[4] = euler_q(q + 21); f.jq[5] = euler_q(q + 25); f.jq[6] = euler_q(q + 28); f.jq[7] = euler_q(q + 32);
-  f.ja[0] = q[16]; f.ja[1] = q[20]; f.ja[2] = q[24]; f.ja[3] = q[31];
-#pragma unroll
-  for (int d = 0; d < 28; ++d) f.rate[d] = (q[7 + d] - qp[7 + d]) * inv_dt;
-  f.ee[0] = vsub(an_p[0], rp); f.ee[1] = vsub(an_p[1], rp);
-  f.ee[2] = vsub(wr_p[0], rp); f.ee[3] = vsub(wr_p[1], rp);
-
-  // centre of mass from the XML geoms (mass, body-local centre)
-  V3 c = v3(0.f, 0.f, 0.f);
-  auto acc = [&](float m, V3 bpz, Q4 bq, V3 local) {
-    const V3 w = vadd(bpz, qrot(bq, local));
-    c.x += m * w.x; c.y += m * w.y; c.z += m * w.z;
-  };
-  acc(2.5f, rp, rq, v3(0.f, 0.f, 0.07f));
-  acc(3.0f, chest_p, chest_q, v3(0.f, 0.f, 0.12f));
-  acc(2.0f, neck_p, neck_q, v3(0.f, 0.f, 0.175f));
-#pragma unroll
-  for (int s = 0; s < 2; ++s) {
-    acc(1.5f, sh_p[s], sh_q[s], v3(0.f, 0.f, -0.14f));
-    acc(1.0f, el_p[s], el_q[s], v3(0.f, 0.f, -0.12f));
-    acc(0.5f, el_p[s], el_q[s], v3(0.f, 0.f, -0.258947f));
-    acc(4.5f, hip_p[s], hip_q[s], v3(0.f, 0.f, -0.21f));
-    acc(3.0f, kn_p[s], kn_q[s], v3(0.f, 0.f, -0.2f));
-    acc(1.0f, an_p[s], an_q[s], v3(0.045f, 0.f, -0.0425f));
-  }
-  const float inv_m = 1.f / 30.5f;
-  f.com = v3(c.x * inv_m, c.y * inv_m, c.z * inv_m);
-}
+// ------------------------------------------------------------------------------------------------
+// K5.  One thread per frame; the arithmetic lives in fk_math.cuh.  A block walks tiles of 128 consecutive frames
+// (grid-stride, grid = a multiple of the SM count): the tile's qpos rows are staged into shared memory with
+// coalesced 16-byte loads and read back row-wise (row stride 35 words: conflict-free); the reference clip's
+// features sit in shared memory for the whole kernel (row stride 92 words).  Registers are capped at 128 so that
+// 16 warps per SM hide the latency of the dependent FK chain.
+// ------------------------------------------------------------------------------------------------
+constexpr int kFkThreads = 128;
+constexpr int kFkBlocksPerSm = 4;
 
 __global__ void ref_features_kernel(const float* __restrict__ ref, int H, float inv_dt, float* __restrict__ feat) {
   const int h = blockIdx.x * blockDim.x + threadIdx.x;
   if (h >= H) return;
-  float q[35], qp[35];
-  for (int i = 0; i < 35; ++i) { q[i] = ref[h * 35 + i]; qp[i] = ref[(h > 0 ? h - 1 : 0) * 35 + i]; }
-  Feat f;
-  V3 bp[B_COUNT];
-  frame_features(q, qp, inv_dt, f, bp);
-  const float* src = reinterpret_cast<const float*>(&f);
-  for (int i = 0; i < kFeatFloats; ++i) feat[(size_t)h * kFeatFloats + i] = src[i];
+  float fo[fk::kFeatStride];
+  for (int i = 86; i < fk::kFeatStride; ++i) fo[i] = 0.f;
+  fk::frame_pass<true, false>(ref + (size_t)h * 35, ref + (size_t)(h > 0 ? h - 1 : 0) * 35, inv_dt, nullptr, fo, nullptr, nullptr);
+  for (int i = 0; i < fk::kFeatStride; ++i) feat[(size_t)h * fk::kFeatStride + i] = fo[i];
 }
 
-constexpr int kFkThreads = 128;
-
-__global__ void __launch_bounds__(kFkThreads) fk_reward_kernel(const float* __restrict__ qpos, const float* __restrict__ feat,
-                                                               long long n_frames, int H, float inv_dt,
-                                                               float* __restrict__ body_pos, float* __restrict__ reward,
-                                                               double* __restrict__ sums) {
-  __shared__ float sq[(kFkThreads + 1) * 35];
+template <bool kBody, bool kFeatSmem>
+__global__ void __launch_bounds__(kFkThreads, kFkBlocksPerSm)
+fk_reward_kernel(const float* __restrict__ qpos, const float* __restrict__ feat, long long n_frames, int H, float inv_dt,
+                 int vec_ok, float* __restrict__ body_pos, float* __restrict__ reward, double* __restrict__ sums) {
+  extern __shared__ __align__(16) float fk_smem[];
   __shared__ float red[6][kFkThreads / 32];
-  const long long f0 = (long long)blockIdx.x * kFkThreads;
-  const long long nf = min((long long)kFkThreads, n_frames - f0);
-  // coalesced stage of frames [f0-1, f0+nf) into shared memory (row 0 = the frame before f0)
-  {
-    const long long g0 = (f0 > 0 ? f0 - 1 : 0) * 35;
-    const long long g1 = (f0 + nf) * 35;
-    const int skip = f0 > 0 ? 0 : 35;
-    for (long long i = g0 + threadIdx.x; i < g1; i += kFkThreads) sq[skip + (int)(i - g0)] = __ldg(qpos + i);
+  float* sq = fk_smem;                              // [128][35] rows of this tile
+  float* sprev = fk_smem + kFkThreads * 35;         // the frame before the tile (35 floats, padded to 36)
+  float* sfeat = fk_smem + kFkThreads * 35 + 36;    // [H][92] when kFeatSmem
+  if (kFeatSmem) {
+    const float4* src = reinterpret_cast<const float4*>(feat);
+    float4* dst = reinterpret_cast<float4*>(sfeat);
+    for (int i = threadIdx.x; i < H * (fk::kFeatStride / 4); i += kFkThreads) dst[i] = __ldg(src + i);
   }
-  __syncthreads();
-  float r = 0.f, tp = 0.f, tv = 0.f, te = 0.f, tc = 0.f;
-  const long long fi = f0 + threadIdx.x;
-  const bool active = threadIdx.x < nf;
-  if (active) {
-    const int h = (int)(fi % H);
-    float q[35], qp[35];
-#pragma unroll
-    for (int i = 0; i < 35; ++i) q[i] = sq[(threadIdx.x + 1) * 35 + i];
-#pragma unroll
-    for (int i = 0; i < 35; ++i) qp[i] = h > 0 ? sq[threadIdx.x * 35 + i] : q[i];
-    Feat f;
-    V3 bp[B_COUNT];
-    frame_features(q, qp, inv_dt, f, bp);
-    const Feat& g = *reinterpret_cast<const Feat*>(feat + (size_t)h * kFeatFloats);
-    const float w3[8] = {0.5f, 0.3f, 0.3f, 0.3f, 0.5f, 0.2f, 0.5f, 0.2f};   // chest neck rsho lsho rhip rank lhip lank
-    const float w1[4] = {0.2f, 0.2f, 0.3f, 0.3f};                           // relbow lelbow rknee lknee
-    // pose
-    float a = qangle(qmul(qconj(g.rootq), f.rootq));
-    float pose = a * a;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) { a = qangle(qmul(qconj(g.jq[k]), f.jq[k])); pose += w3[k] * a * a; }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { a = f.ja[k] - g.ja[k]; pose += w1[k] * a * a; }
-    // velocity: rate index d <-> qpos 7+d
-    V3 dw = vsub(f.rootw, g.rootw);
-    float vel = dw.x * dw.x + dw.y * dw.y + dw.z * dw.z;
-    const float wr[28] = {0.5f, 0.5f, 0.5f, 0.3f, 0.3f, 0.3f, 0.3f, 0.3f, 0.3f, 0.2f, 0.3f, 0.3f, 0.3f, 0.2f,
-                          0.5f, 0.5f, 0.5f, 0.3f, 0.2f, 0.2f, 0.2f, 0.5f, 0.5f, 0.5f, 0.3f, 0.2f, 0.2f, 0.2f};
-#pragma unroll
-    for (int d = 0; d < 28; ++d) { a = f.rate[d] - g.rate[d]; vel += wr[d] * a * a; }
-    float ee = 0.f;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { V3 d = vsub(f.ee[k], g.ee[k]); ee += d.x * d.x + d.y * d.y + d.z * d.z; }
-    V3 dc = vsub(f.com, g.com);
-    const float com = dc.x * dc.x + dc.y * dc.y + dc.z * dc.z;
-    tp = expf(-2.f * pose); tv = expf(-0.1f * vel); te = expf(-40.f * ee); tc = expf(-10.f * com);
-    r = 0.65f * tp + 0.1f * tv + 0.15f * te + 0.1f * tc;
-    reward[fi] = r;
-    if (body_pos) {
-      float* o = body_pos + (size_t)fi * B_COUNT * 3;
-#pragma unroll
-      for (int k = 0; k < B_COUNT; ++k) { o[3 * k] = bp[k].x; o[3 * k + 1] = bp[k].y; o[3 * k + 2] = bp[k].z; }
+  const long long n_tiles = (n_frames + kFkThreads - 1) / kFkThreads;
+  float s_r = 0.f, s_r2 = 0.f, s_p = 0.f, s_v = 0.f, s_e = 0.f, s_c = 0.f;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long f0 = tile * kFkThreads;
+    const int nf = (int)min((long long)kFkThreads, n_frames - f0);
+    __syncthreads();   // previous tile fully consumed (also orders the feature copy before first use)
+    {
+      const float* src = qpos + f0 * 35;
+      const int n = nf * 35;
+      int done = 0;
+      if (vec_ok) {   // f0 * 140 bytes is a multiple of 16: the tile starts 16-byte aligned when qpos does
+        const int n4 = n >> 2;
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(sq);
+        for (int i = threadIdx.x; i < n4; i += kFkThreads) d4[i] = __ldcs(s4 + i);
+        done = n4 << 2;
+      }
+      for (int i = done + threadIdx.x; i < n; i += kFkThreads) sq[i] = __ldcs(src + i);
+      if (f0 > 0 && threadIdx.x < 35) sprev[threadIdx.x] = __ldg(src - 35 + threadIdx.x);
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < nf) {
+      const long long fi = f0 + threadIdx.x;
+      const int h = (int)(fi % H);
+      const float* q = sq + threadIdx.x * 35;
+      const float* qp = h == 0 ? q : (threadIdx.x == 0 ? sprev : q - 35);
+      const float* g = (kFeatSmem ? sfeat : feat) + (size_t)h * fk::kFeatStride;
+      float acc[4];
+      fk::frame_pass<false, kBody>(q, qp, inv_dt, g, nullptr, kBody ? body_pos + (size_t)fi * (fk::kBodies * 3) : nullptr, acc);
+      const float tp = fk::fast_exp(-2.f * acc[0]), tv = fk::fast_exp(-0.1f * acc[1]);
+      const float te = fk::fast_exp(-40.f * acc[2]), tc = fk::fast_exp(-10.f * acc[3]);
+      const float r = 0.65f * tp + 0.1f * tv + 0.15f * te + 0.1f * tc;
+      __stcs(reward + fi, r);
+      s_r += r; s_r2 = fmaf(r, r, s_r2); s_p += tp; s_v += tv; s_e += te; s_c += tc;
     }
   }
   // block reduction -> one double atomic per statistic per block
-  float vals[6] = {r, r * r, tp, tv, te, tc};
+  float vals[6] = {s_r, s_r2, s_p, s_v, s_e, s_c};
 #pragma unroll
   for (int k = 0; k < 6; ++k) {
     float v = vals[k];
@@ -271,7 +101,7 @@ __global__ void __launch_bounds__(kFkThreads) fk_reward_kernel(const float* __re
     for (int w = 0; w < kFkThreads / 32; ++w) s += (double)red[threadIdx.x][w];
     atomicAdd(&sums[threadIdx.x], s);
   }
-  if (threadIdx.x == 6) atomicAdd(&sums[6], (double)nf);
+  if (threadIdx.x == 6 && blockIdx.x == 0) atomicAdd(&sums[6], (double)n_frames);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -347,13 +177,28 @@ extern "C" int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, 
   if (rc) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(st);
   float* feat = nullptr;
-  cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&feat), (size_t)H * kFeatFloats * sizeof(float), s);
+  cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&feat), (size_t)H * fk::kFeatStride * sizeof(float), s);
   if (e != cudaSuccess) return fail(DM_ERR_CUDA, "cudaMallocAsync: %s", cudaGetErrorString(e));
-  ref_features_kernel<<<(H + 63) / 64, 64, 0, s>>>(ref_dev, H, 1.f / dt, feat);
+  ref_features_kernel<<<(H + 31) / 32, 32, 0, s>>>(ref_dev, H, 1.f / dt, feat);
   const long long nfr = (long long)N * H;
-  fk_reward_kernel<<<(unsigned)((nfr + kFkThreads - 1) / kFkThreads), kFkThreads, 0, s>>>(qpos_dev, feat, nfr, H, 1.f / dt,
-                                                                                        body_pos_dev, reward_dev, sums_dev);
-  e = cudaGetLastError();
+  const long long tiles = (nfr + kFkThreads - 1) / kFkThreads;
+  const size_t base_smem = (size_t)(kFkThreads * 35 + 36) * sizeof(float);
+  const size_t feat_smem = (size_t)H * fk::kFeatStride * sizeof(float);
+  const bool feat_in_smem = base_smem + feat_smem <= 200 * 1024;
+  const size_t smem = base_smem + (feat_in_smem ? feat_smem : 0);
+  int blocks_per_sm = kFkBlocksPerSm;
+  while (blocks_per_sm > 1 && (smem + 1024) * blocks_per_sm > 227 * 1024) --blocks_per_sm;
+  const unsigned grid = (unsigned)(tiles < 148LL * blocks_per_sm ? tiles : 148LL * blocks_per_sm);
+  const int vec_ok = (reinterpret_cast<uintptr_t>(qpos_dev) & 15) == 0;
+  const bool body = body_pos_dev != nullptr;
+  auto launch = [&](auto kern) -> cudaError_t {
+    cudaError_t le = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (le != cudaSuccess) return le;
+    kern<<<grid, kFkThreads, smem, s>>>(qpos_dev, feat, nfr, H, 1.f / dt, vec_ok, body_pos_dev, reward_dev, sums_dev);
+    return cudaGetLastError();
+  };
+  if (body) e = feat_in_smem ? launch(fk_reward_kernel<true, true>) : launch(fk_reward_kernel<true, false>);
+  else e = feat_in_smem ? launch(fk_reward_kernel<false, true>) : launch(fk_reward_kernel<false, false>);
   cudaFreeAsync(feat, s);
   if (e != cudaSuccess) return fail(DM_ERR_CUDA, "fk_reward launch: %s", cudaGetErrorString(e));
   return DM_OK;
