@@ -1,0 +1,180 @@
+// Residual(PreNorm(LinearAttention)) of the TemporalUnet's attention=True variant
+// (reference: diffuser/models/helpers.py:75-131, used at diffuser/models/temporal.py:85,94,103):
+//   xn  = (x - mean_c) / sqrt(var_c + eps) * g + b                       LayerNorm over channels, per position
+//   qkv = W_qkv xn            (1x1 conv, no bias; 3 x heads x 32 rows)
+//   k   = softmax over positions;  q = q * 32^-0.5
+//   ctx[d][e] = sum_l k[d][l] v[e][l];   o[e][l] = sum_d ctx[d][e] q[d][l]
+//   y   = W_out o + b_out + x
+// One CTA owns NS samples of one 16-sample activation group and keeps everything in shared memory: the
+// activation tile is read once (fp16 hi + lo planes, value = hi + lo) and written once.  All arithmetic is fp32
+// on the CUDA cores: the contractions are 32-wide per head and the whole op is ~17 % of the U-Net's FLOPs, so this
+// first version favours exactness over tensor-core use; it runs in the per-layer launch path only (the fused
+// persistent loop kernel is used when attention=False).
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "attn_kernel.h"
+#include "conv_job.h"
+
+namespace dm {
+
+constexpr int kAttnThreads = 256;
+constexpr int kLc = 8;   // positions per register tile
+
+__device__ __forceinline__ int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+__global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const AttnParams p) {
+  extern __shared__ float sm[];
+  const int C = p.C, L = p.L, NS = p.NS;
+  const int Lp = L | 1;                       // odd row pitch: column walks are conflict-free
+  float* xs = sm;                             // [NS][C][Lp]  input, becomes the output accumulator
+  float* xn = xs + NS * C * Lp;               // [NS][C][Lp]  normalised input
+  float* qkv = xn + NS * C * Lp;              // [NS][96][Lp] q | k (later o) | v of the current head
+  float* ctx = qkv + NS * 96 * Lp;            // [NS][32][33]
+  const int tid = threadIdx.x;
+  const int per_group = kGroupSamples / NS;
+  const int g = blockIdx.x / per_group;
+  const int s0 = (blockIdx.x % per_group) * NS;
+
+  // ---- load: activation layout [plane][G][L][16][C] ----
+  for (int i = tid; i < NS * L * C; i += kAttnThreads) {
+    const int c = i % C, l = (i / C) % L, s = i / (C * L);
+    const long long off = (((long long)g * L + l) * kGroupSamples + s0 + s) * C + c;
+    xs[(s * C + c) * Lp + l] = __half2float(p.in[off]) + __half2float(p.in[p.in_plane + off]);
+  }
+  __syncthreads();
+  // ---- LayerNorm over channels (helpers.py:84-95: biased variance, eps inside the sqrt) ----
+  for (int i = tid; i < NS * L; i += kAttnThreads) {
+    const int l = i % L, s = i / L;
+    const float* col = xs + s * C * Lp + l;
+    float mean = 0.f;
+    for (int c = 0; c < C; ++c) mean += col[c * Lp];
+    mean /= (float)C;
+    float var = 0.f;
+    for (int c = 0; c < C; ++c) { const float d = col[c * Lp] - mean; var = fmaf(d, d, var); }
+    var /= (float)C;
+    const float inv = 1.f / sqrtf(var + p.eps);
+    float* dst = xn + s * C * Lp + l;
+    for (int c = 0; c < C; ++c) dst[c * Lp] = (col[c * Lp] - mean) * inv * __ldg(p.ln_g + c) + __ldg(p.ln_b + c);
+  }
+  __syncthreads();
+  const int n_lc = ceil_div(L, kLc);
+  for (int h = 0; h < p.heads; ++h) {
+    // ---- q, k, v rows of this head: W_qkv^T is [C][3*heads*32] so that a warp reads consecutive rows coalesced ----
+    for (int i = tid; i < 96 * NS * n_lc; i += kAttnThreads) {
+      const int o = i % 96, s = (i / 96) % NS, lc = i / (96 * NS);
+      const int part = o >> 5, d = o & 31;
+      const int row = part * (p.heads * 32) + h * 32 + d;
+      const int l0 = lc * kLc;
+      float acc[kLc];
+#pragma unroll
+      for (int j = 0; j < kLc; ++j) acc[j] = 0.f;
+      const float* xr = xn + s * C * Lp + l0;
+      const float* wr = p.wqkv_t + row;
+      const int OW = 3 * p.heads * 32;
+      if (l0 + kLc <= L) {
+        for (int c = 0; c < C; ++c) {
+          const float w = __ldg(wr + (size_t)c * OW);
+#pragma unroll
+          for (int j = 0; j < kLc; ++j) acc[j] = fmaf(w, xr[c * Lp + j], acc[j]);
+        }
+      } else {
+        for (int c = 0; c < C; ++c) {
+          const float w = __ldg(wr + (size_t)c * OW);
+#pragma unroll
+          for (int j = 0; j < kLc; ++j) if (l0 + j < L) acc[j] = fmaf(w, xr[c * Lp + j], acc[j]);
+        }
+      }
+      const float sc = part == 0 ? p.scale : 1.f;
+      float* dst = qkv + (s * 96 + o) * Lp + l0;
+#pragma unroll
+      for (int j = 0; j < kLc; ++j) if (l0 + j < L) dst[j] = acc[j] * sc;
+    }
+    __syncthreads();
+    // ---- softmax of every k row over the positions ----
+    for (int i = tid; i < NS * 32; i += kAttnThreads) {
+      float* row = qkv + ((i >> 5) * 96 + 32 + (i & 31)) * Lp;
+      float m = row[0];
+      for (int l = 1; l < L; ++l) m = fmaxf(m, row[l]);
+      float sum = 0.f;
+      for (int l = 0; l < L; ++l) { const float e = expf(row[l] - m); row[l] = e; sum += e; }
+      const float inv = 1.f / sum;
+      for (int l = 0; l < L; ++l) row[l] *= inv;
+    }
+    __syncthreads();
+    // ---- ctx[d][e] = sum_l k[d][l] v[e][l] ----
+    for (int i = tid; i < NS * 1024; i += kAttnThreads) {
+      const int e = i & 31, d = (i >> 5) & 31, s = i >> 10;
+      const float* kr = qkv + (s * 96 + 32 + d) * Lp;
+      const float* vr = qkv + (s * 96 + 64 + e) * Lp;
+      float a = 0.f;
+      for (int l = 0; l < L; ++l) a = fmaf(kr[l], vr[l], a);
+      ctx[(s * 32 + d) * 33 + e] = a;
+    }
+    __syncthreads();
+    // ---- o[e][l] = sum_d ctx[d][e] q[d][l]; stored over the (dead) k rows ----
+    for (int i = tid; i < NS * 32 * L; i += kAttnThreads) {
+      const int l = i % L, e = (i / L) & 31, s = i / (32 * L);
+      const float* qc = qkv + (s * 96) * Lp + l;
+      const float* cc = ctx + (s * 32) * 33 + e;
+      float a = 0.f;
+#pragma unroll 8
+      for (int d = 0; d < 32; ++d) a = fmaf(cc[d * 33], qc[d * Lp], a);
+      qkv[(s * 96 + 32 + e) * Lp + l] = a;   // k rows of this (s, e, l) are only read in the ctx pass above
+    }
+    __syncthreads();
+    // ---- xs += W_out[:, head] o  (+ bias once): W_out^T is [heads*32][C] ----
+    for (int i = tid; i < C * NS * n_lc; i += kAttnThreads) {
+      const int co = i % C, s = (i / C) % NS, lc = i / (C * NS);
+      const int l0 = lc * kLc;
+      float acc[kLc];
+      const float b0 = h == 0 ? __ldg(p.bout + co) : 0.f;
+#pragma unroll
+      for (int j = 0; j < kLc; ++j) acc[j] = b0;
+      const float* orow = qkv + (s * 96 + 32) * Lp + l0;
+      const float* wr = p.wout_t + (size_t)(h * 32) * C + co;
+      for (int e = 0; e < 32; ++e) {
+        const float w = __ldg(wr + (size_t)e * C);
+#pragma unroll
+        for (int j = 0; j < kLc; ++j) if (l0 + j < L) acc[j] = fmaf(w, orow[e * Lp + j], acc[j]);
+      }
+      float* dst = xs + (s * C + co) * Lp + l0;
+#pragma unroll
+      for (int j = 0; j < kLc; ++j) if (l0 + j < L) dst[j] += acc[j];
+    }
+    __syncthreads();
+  }
+  // ---- store: split to fp16 hi + lo planes ----
+  for (int i = tid; i < NS * L * C; i += kAttnThreads) {
+    const int c = i % C, l = (i / C) % L, s = i / (C * L);
+    const long long off = (((long long)g * L + l) * kGroupSamples + s0 + s) * C + c;
+    const float v = xs[(s * C + c) * Lp + l];
+    const __half hi = __float2half_rn(v);
+    p.out[off] = hi;
+    p.out[p.out_plane + off] = __float2half_rn(v - __half2float(hi));
+  }
+}
+
+size_t attention_smem_bytes(int C, int L, int NS) {
+  const int Lp = L | 1;
+  return sizeof(float) * ((size_t)2 * NS * C * Lp + (size_t)NS * 96 * Lp + (size_t)NS * 32 * 33);
+}
+
+int attention_pick_ns(int C, int L) {
+  for (int ns = 4; ns >= 1; ns >>= 1)
+    if (attention_smem_bytes(C, L, ns) <= 200 * 1024) return ns;
+  return 0;
+}
+
+cudaError_t launch_linear_attention(const AttnParams& p, int n_groups, cudaStream_t s) {
+  const size_t smem = attention_smem_bytes(p.C, p.L, p.NS);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(linear_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  linear_attention_kernel<<<n_groups * (kGroupSamples / p.NS), kAttnThreads, smem, s>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace dm

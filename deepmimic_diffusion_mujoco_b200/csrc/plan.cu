@@ -553,6 +553,57 @@ static int add_resblock(dm_plan* P, const WeightMap& W, const std::string& key, 
   return DM_OK;
 }
 
+// Residual(PreNorm(dim, LinearAttention(dim))) (helpers.py:75-131; temporal.py:85,94,103), present when the state dict
+// carries `<key>.fn.fn.to_qkv.weight`.  Weights are uploaded transposed (see attn_kernel.cu).
+static bool has_attention_weights(const WeightMap& W, const std::string& key) {
+  return W.find(key + ".fn.fn.to_qkv.weight") != W.end();
+}
+
+static int add_attention(dm_plan* P, const WeightMap& W, const std::string& key, int src, int C, int* out_act) {
+  const Act in = P->acts[src];
+  if (in.C != C) return fail(DM_ERR_ARG, "internal: attention input %s is channel padded", key.c_str());
+  const int heads = 4, dh = 32, hid = heads * dh;   // LinearAttention defaults (helpers.py:111); temporal.py never overrides them
+  const float *g, *b, *wqkv, *wout, *bout;
+  int rc;
+  if ((rc = find_w(W, key + ".fn.norm.g", {1, C, 1}, &g))) return rc;
+  if ((rc = find_w(W, key + ".fn.norm.b", {1, C, 1}, &b))) return rc;
+  if ((rc = find_w(W, key + ".fn.fn.to_qkv.weight", {3 * hid, C, 1}, &wqkv))) return rc;
+  if ((rc = find_w(W, key + ".fn.fn.to_out.weight", {C, hid, 1}, &wout))) return rc;
+  if ((rc = find_w(W, key + ".fn.fn.to_out.bias", {C}, &bout))) return rc;
+  std::vector<float> wq_t((size_t)C * 3 * hid), wo_t((size_t)hid * C);
+  for (int o = 0; o < 3 * hid; ++o)
+    for (int c = 0; c < C; ++c) wq_t[(size_t)c * 3 * hid + o] = wqkv[(size_t)o * C + c];
+  for (int c = 0; c < C; ++c)
+    for (int j = 0; j < hid; ++j) wo_t[(size_t)j * C + c] = wout[(size_t)c * hid + j];
+  float *dg, *db, *dwq, *dwo, *dbo;
+  if ((rc = upload(P, std::vector<float>(g, g + C), &dg))) return rc;
+  if ((rc = upload(P, std::vector<float>(b, b + C), &db))) return rc;
+  if ((rc = upload(P, wq_t, &dwq))) return rc;
+  if ((rc = upload(P, wo_t, &dwo))) return rc;
+  if ((rc = upload(P, std::vector<float>(bout, bout + C), &dbo))) return rc;
+  int out;
+  if ((rc = new_act(P, C, in.L, &out))) return rc;
+  const int ns = attention_pick_ns(C, in.L);
+  if (ns == 0) return fail(DM_ERR_ARG, "attention tile C=%d L=%d does not fit in shared memory (horizon too long)", C, in.L);
+  Layer ly;
+  ly.kind = 1;
+  ly.name = key;
+  ly.out_act = out;
+  memset(&ly.job, 0, sizeof(ly.job));
+  ly.job.Cout = C;
+  ly.job.Lout = in.L;
+  AttnParams& a = ly.attn;
+  a.in = in.p; a.in_plane = in.plane;
+  a.out = P->acts[out].p; a.out_plane = P->acts[out].plane;
+  a.C = C; a.L = in.L; a.NS = ns; a.heads = heads;
+  a.eps = 1e-5f; a.scale = 1.f / sqrtf((float)dh);
+  a.ln_g = dg; a.ln_b = db; a.wqkv_t = dwq; a.wout_t = dwo; a.bout = dbo;
+  P->layers.push_back(ly);
+  P->has_attention = true;
+  *out_act = out;
+  return DM_OK;
+}
+
 static int build_unet(dm_plan* P, const WeightMap& W) {
   const int nlev = (int)P->mults.size();
   std::vector<int> dims;
@@ -596,6 +647,10 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if ((rc = add_tb(k + ".1", cout))) return rc;
     if ((rc = add_resblock(P, W, k + ".1", &x, &x_real, 1, x_real, cout, &tb, &o))) return rc;
     x = o;
+    if (has_attention_weights(W, k + ".2")) {
+      if ((rc = add_attention(P, W, k + ".2", x, cout, &o))) return rc;
+      x = o;
+    }
     skips.push_back(x);
     skip_c.push_back(cout);
     if (i < nlev - 1) {
@@ -616,6 +671,10 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if ((rc = add_tb("mid_block1", c))) return rc;
     if ((rc = add_resblock(P, W, "mid_block1", &x, &x_real, 1, c, c, &tb, &o))) return rc;
     x = o;
+    if (has_attention_weights(W, "mid_attn")) {
+      if ((rc = add_attention(P, W, "mid_attn", x, c, &o))) return rc;
+      x = o;
+    }
     if ((rc = add_tb("mid_block2", c))) return rc;
     if ((rc = add_resblock(P, W, "mid_block2", &x, &x_real, 1, c, c, &tb, &o))) return rc;
     x = o;
@@ -637,6 +696,10 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if ((rc = add_tb(k + ".1", dim_in))) return rc;
     if ((rc = add_resblock(P, W, k + ".1", &x, &x_real, 1, dim_in, dim_in, &tb, &o))) return rc;
     x = o;
+    if (has_attention_weights(W, k + ".2")) {
+      if ((rc = add_attention(P, W, k + ".2", x, dim_in, &o))) return rc;
+      x = o;
+    }
     ConvSpec t;
     t.name = k + ".3.conv";
     t.wkey = k + ".3.conv";
@@ -712,6 +775,11 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
 // Launch every layer.  tb: time-bias rows; tb_stride 0 = one row for all samples (uniform t).
 static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, cudaStream_t s) {
   for (Layer& ly : P->layers) {
+    if (ly.kind == 1) {
+      DM_CUDA(launch_linear_attention(ly.attn, P->G, s));
+      P->last_launches++;
+      continue;
+    }
     ConvJob j = ly.job;
     if (ly.tb_off >= 0) {
       j.tbias = tb + ly.tb_off;
@@ -769,9 +837,6 @@ extern "C" int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, 
     t.shape.assign(weights[i].shape, weights[i].shape + weights[i].ndim);
     W[weights[i].name] = t;
   }
-  for (auto& kv : W)
-    if (kv.first.find("to_qkv") != std::string::npos)
-      return fail(DM_ERR_ARG, "attention=True (LinearAttention, helpers.py:110-131) is not supported");
   dm_plan* P = new dm_plan();
   P->B = B; P->H = H; P->T = T; P->dim = dim;
   P->G = (B + kGroupSamples - 1) / kGroupSamples;
@@ -918,6 +983,7 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
     unsigned long long sd = seed;
     DM_CUDA(cudaMemcpyAsync(P->seed_dev, &sd, sizeof(sd), cudaMemcpyHostToDevice, s));
   }
+  if (P->has_attention) fused = 0;   // LinearAttention runs as its own launch between the conv layers
   if (!fused) return enqueue_loop(P, x_dev, have_start, noise_stack_dev, seed, timesteps, predict_epsilon, clip_denoised,
                                   cond, chain_dev, s);
   // ---- persistent cluster kernel: the whole loop is ONE launch ----

@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 
+#include "attn_kernel.h"
 #include "conv_job.h"
 #include "step_kernels.h"
 
@@ -20,6 +21,8 @@ struct Act {
 };
 
 struct Layer {
+  int kind = 0;          // 0: conv launch (job, maps); 1: Residual(PreNorm(LinearAttention)) launch (attn)
+  AttnParams attn{};
   ConvJob job;
   ConvMaps maps;
   int slices = 1;
@@ -44,6 +47,7 @@ struct dm_plan {
   std::vector<dm::Act> acts;
   std::vector<dm::Layer> layers;
   int xs_act = -1;
+  bool has_attention = false;      // attention=True: per-layer launches only (the fused loop kernel has no attention stage)
   float* model_out = nullptr;      // fp32 [B,H,T] scratch for the sampling loop
   dm::TimeMlpParams tmlp{};
   int TB = 0;

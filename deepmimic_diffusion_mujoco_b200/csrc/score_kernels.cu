@@ -30,21 +30,21 @@ constexpr int kFkBlocksPerSm = 4;
 __global__ void ref_features_kernel(const float* __restrict__ ref, int H, float inv_dt, float* __restrict__ feat) {
   const int h = blockIdx.x * blockDim.x + threadIdx.x;
   if (h >= H) return;
-  float fo[fk::kFeatStride];
+  float* fo = feat + (size_t)h * fk::kFeatStride;
   for (int i = 86; i < fk::kFeatStride; ++i) fo[i] = 0.f;
   fk::frame_pass<true, false>(ref + (size_t)h * 35, ref + (size_t)(h > 0 ? h - 1 : 0) * 35, inv_dt, nullptr, fo, nullptr, nullptr);
-  for (int i = 0; i < fk::kFeatStride; ++i) feat[(size_t)h * fk::kFeatStride + i] = fo[i];
 }
 
 template <bool kBody, bool kFeatSmem>
 __global__ void __launch_bounds__(kFkThreads, kFkBlocksPerSm)
 fk_reward_kernel(const float* __restrict__ qpos, const float* __restrict__ feat, long long n_frames, int H, float inv_dt,
-                 int vec_ok, float* __restrict__ body_pos, float* __restrict__ reward, double* __restrict__ sums) {
+                 int vec_ok, int body_vec_ok, float* __restrict__ body_pos, float* __restrict__ reward, double* __restrict__ sums) {
   extern __shared__ __align__(16) float fk_smem[];
   __shared__ float red[6][kFkThreads / 32];
   float* sq = fk_smem;                              // [128][35] rows of this tile
   float* sprev = fk_smem + kFkThreads * 35;         // the frame before the tile (35 floats, padded to 36)
-  float* sfeat = fk_smem + kFkThreads * 35 + 36;    // [H][92] when kFeatSmem
+  float* sbody = fk_smem + kFkThreads * 35 + 36;    // [128][45] when kBody: positions leave through coalesced stores
+  float* sfeat = sbody + (kBody ? kFkThreads * fk::kBodies * 3 : 0);   // [H][92] when kFeatSmem
   if (kFeatSmem) {
     const float4* src = reinterpret_cast<const float4*>(feat);
     float4* dst = reinterpret_cast<float4*>(sfeat);
@@ -78,12 +78,24 @@ fk_reward_kernel(const float* __restrict__ qpos, const float* __restrict__ feat,
       const float* qp = h == 0 ? q : (threadIdx.x == 0 ? sprev : q - 35);
       const float* g = (kFeatSmem ? sfeat : feat) + (size_t)h * fk::kFeatStride;
       float acc[4];
-      fk::frame_pass<false, kBody>(q, qp, inv_dt, g, nullptr, kBody ? body_pos + (size_t)fi * (fk::kBodies * 3) : nullptr, acc);
+      fk::frame_pass<false, kBody>(q, qp, inv_dt, g, nullptr, kBody ? sbody + threadIdx.x * (fk::kBodies * 3) : nullptr, acc);
       const float tp = fk::fast_exp(-2.f * acc[0]), tv = fk::fast_exp(-0.1f * acc[1]);
       const float te = fk::fast_exp(-40.f * acc[2]), tc = fk::fast_exp(-10.f * acc[3]);
       const float r = 0.65f * tp + 0.1f * tv + 0.15f * te + 0.1f * tc;
       __stcs(reward + fi, r);
       s_r += r; s_r2 = fmaf(r, r, s_r2); s_p += tp; s_v += tv; s_e += te; s_c += tc;
+    }
+    if (kBody) {
+      __syncthreads();
+      float* dst = body_pos + (size_t)f0 * (fk::kBodies * 3);
+      const int n = nf * fk::kBodies * 3;
+      int done = 0;
+      if (body_vec_ok) {   // f0 * 180 bytes is a multiple of 16
+        const int n4 = n >> 2;
+        for (int i = threadIdx.x; i < n4; i += kFkThreads) __stcs(reinterpret_cast<float4*>(dst) + i, reinterpret_cast<const float4*>(sbody)[i]);
+        done = n4 << 2;
+      }
+      for (int i = done + threadIdx.x; i < n; i += kFkThreads) __stcs(dst + i, sbody[i]);
     }
   }
   // block reduction -> one double atomic per statistic per block
@@ -176,13 +188,31 @@ extern "C" int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, 
   int rc = check_device();
   if (rc) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(st);
+  // Scratch for the reference clip's features comes from a library-owned stream-ordered pool that never trims:
+  // the default pool returns its memory to the driver at every synchronisation, which made each call pay a real
+  // allocation (~240 us measured on B200, 6x the kernel itself at 8192 samples).
+  static cudaMemPool_t pools[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return fail(DM_ERR_ARG, "device ordinal %d out of range", dev);
+  if (!pools[dev]) {
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = dev;
+    cudaError_t pe = cudaMemPoolCreate(&pools[dev], &props);
+    if (pe != cudaSuccess) { pools[dev] = nullptr; return fail(DM_ERR_CUDA, "cudaMemPoolCreate: %s", cudaGetErrorString(pe)); }
+    unsigned long long keep = ~0ull;
+    cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
+  }
   float* feat = nullptr;
-  cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&feat), (size_t)H * fk::kFeatStride * sizeof(float), s);
-  if (e != cudaSuccess) return fail(DM_ERR_CUDA, "cudaMallocAsync: %s", cudaGetErrorString(e));
+  cudaError_t e = cudaMallocFromPoolAsync(reinterpret_cast<void**>(&feat), (size_t)H * fk::kFeatStride * sizeof(float), pools[dev], s);
+  if (e != cudaSuccess) return fail(DM_ERR_CUDA, "cudaMallocFromPoolAsync: %s", cudaGetErrorString(e));
   ref_features_kernel<<<(H + 31) / 32, 32, 0, s>>>(ref_dev, H, 1.f / dt, feat);
   const long long nfr = (long long)N * H;
   const long long tiles = (nfr + kFkThreads - 1) / kFkThreads;
-  const size_t base_smem = (size_t)(kFkThreads * 35 + 36) * sizeof(float);
+  const bool body = body_pos_dev != nullptr;
+  const size_t base_smem = (size_t)(kFkThreads * 35 + 36 + (body ? kFkThreads * fk::kBodies * 3 : 0)) * sizeof(float);
   const size_t feat_smem = (size_t)H * fk::kFeatStride * sizeof(float);
   const bool feat_in_smem = base_smem + feat_smem <= 200 * 1024;
   const size_t smem = base_smem + (feat_in_smem ? feat_smem : 0);
@@ -190,11 +220,13 @@ extern "C" int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, 
   while (blocks_per_sm > 1 && (smem + 1024) * blocks_per_sm > 227 * 1024) --blocks_per_sm;
   const unsigned grid = (unsigned)(tiles < 148LL * blocks_per_sm ? tiles : 148LL * blocks_per_sm);
   const int vec_ok = (reinterpret_cast<uintptr_t>(qpos_dev) & 15) == 0;
-  const bool body = body_pos_dev != nullptr;
+  const int body_vec_ok = (reinterpret_cast<uintptr_t>(body_pos_dev) & 15) == 0;
   auto launch = [&](auto kern) -> cudaError_t {
-    cudaError_t le = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (le != cudaSuccess) return le;
-    kern<<<grid, kFkThreads, smem, s>>>(qpos_dev, feat, nfr, H, 1.f / dt, vec_ok, body_pos_dev, reward_dev, sums_dev);
+    if (smem > 48 * 1024) {
+      cudaError_t le = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (le != cudaSuccess) return le;
+    }
+    kern<<<grid, kFkThreads, smem, s>>>(qpos_dev, feat, nfr, H, 1.f / dt, vec_ok, body_vec_ok, body_pos_dev, reward_dev, sums_dev);
     return cudaGetLastError();
   };
   if (body) e = feat_in_smem ? launch(fk_reward_kernel<true, true>) : launch(fk_reward_kernel<true, false>);

@@ -3,7 +3,8 @@
 Same constructor signature, same parameter construction order (so a seeded default init gives the reference's
 weights) and the same state_dict keys/shapes (so reference checkpoints load); forward() runs the hand-written
 sm_100a kernels through libdm_b200.so.  The nn modules below only HOLD parameters -- none of them is ever
-called.  attention=True and a non-CUDA device are hard errors (no fallback).
+called.  attention=True adds the Residual(PreNorm(LinearAttention)) stages (helpers.py:75-131) as their own CUDA
+launches between the conv layers; a non-CUDA device is a hard error (no fallback).
 """
 import ctypes
 
@@ -39,6 +40,42 @@ class _ResBlockParams(nn.Module):
                                      _ConvBlockParams(cout, cout, kernel_size)])
         self.time_mlp = nn.Sequential(nn.Mish(), nn.Linear(embed_dim, cout), nn.Identity())
         self.residual_conv = nn.Conv1d(cin, cout, 1) if cin != cout else nn.Identity()
+
+
+class _LayerNormParams(nn.Module):
+    """helpers.py:84-95: per-position LayerNorm over channels, g/b of shape [1, dim, 1]."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.g = nn.Parameter(torch.ones(1, dim, 1))
+        self.b = nn.Parameter(torch.zeros(1, dim, 1))
+
+
+class _LinearAttentionParams(nn.Module):
+    """helpers.py:110-117: to_qkv (1x1, no bias) then to_out (1x1), constructed in that order."""
+
+    def __init__(self, dim, heads=4, dim_head=32):
+        super().__init__()
+        hidden = heads * dim_head
+        self.to_qkv = nn.Conv1d(dim, hidden * 3, 1, bias=False)
+        self.to_out = nn.Conv1d(hidden, dim, 1)
+
+
+class _PreNormParams(nn.Module):
+    def __init__(self, dim, fn):
+        super().__init__()
+        self.fn = fn
+        self.norm = _LayerNormParams(dim)
+
+
+class _ResidualParams(nn.Module):
+    def __init__(self, fn):
+        super().__init__()
+        self.fn = fn
+
+
+def _attention(dim, on):
+    return _ResidualParams(_PreNormParams(dim, _LinearAttentionParams(dim))) if on else nn.Identity()
 
 
 class _Resample(nn.Module):
@@ -116,9 +153,7 @@ class UnetPlan:
 class TemporalUnet(nn.Module):
     def __init__(self, horizon, transition_dim, cond_dim, dim=32, dim_mults=(1, 2, 4, 8), attention=False):
         super().__init__()
-        if attention:
-            raise NotImplementedError("attention=True (LinearAttention, helpers.py:110-131) is outside the hot path "
-                                      "(SURVEY.md 8(f) item 3); no fallback is provided")
+        self.attention = bool(attention)
         dims = [transition_dim, *map(lambda m: dim * m, dim_mults)]
         in_out = list(zip(dims[:-1], dims[1:]))
         self.horizon, self.transition_dim, self.dim, self.dim_mults = horizon, transition_dim, dim, tuple(dim_mults)
@@ -130,15 +165,15 @@ class TemporalUnet(nn.Module):
         for ind, (cin, cout) in enumerate(in_out):
             last = ind >= n - 1
             self.downs.append(nn.ModuleList([
-                _ResBlockParams(cin, cout, dim), _ResBlockParams(cout, cout, dim), nn.Identity(),
+                _ResBlockParams(cin, cout, dim), _ResBlockParams(cout, cout, dim), _attention(cout, attention),
                 _Resample(nn.Conv1d(cout, cout, 3, 2, 1)) if not last else nn.Identity()]))
         mid = dims[-1]
         self.mid_block1 = _ResBlockParams(mid, mid, dim)
-        self.mid_attn = nn.Identity()
+        self.mid_attn = _attention(mid, attention)
         self.mid_block2 = _ResBlockParams(mid, mid, dim)
         for ind, (cin, cout) in enumerate(reversed(in_out[1:])):
             self.ups.append(nn.ModuleList([
-                _ResBlockParams(cout * 2, cin, dim), _ResBlockParams(cin, cin, dim), nn.Identity(),
+                _ResBlockParams(cout * 2, cin, dim), _ResBlockParams(cin, cin, dim), _attention(cin, attention),
                 _Resample(nn.ConvTranspose1d(cin, cin, 4, 2, 1))]))
         self.final_conv = nn.Sequential(_ConvBlockParams(dim, dim, 5), nn.Conv1d(dim, transition_dim, 1))
         self._plans = {}

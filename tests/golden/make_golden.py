@@ -46,10 +46,10 @@ def box_holding(x):  # sampling_config.py:23-32
     return x
 
 
-def run(name, B, H, n_steps, pe, clip, cond=None, start=False, max_t=None, seed=0):
+def run(name, B, H, n_steps, pe, clip, cond=None, start=False, max_t=None, seed=0, attention=False):
     with contextlib.redirect_stdout(io.StringIO()):
-        net = TemporalUnet(H, 35, 35)
-    sd = seeded_state_dict(H=H, seed=seed)
+        net = TemporalUnet(H, 35, 35, attention=attention)
+    sd = seeded_state_dict(H=H, seed=seed, attention=attention)
     net.load_state_dict(sd)
     diff = GaussianDiffusion(net, H, 35, n_timesteps=n_steps, predict_epsilon=pe, clip_denoised=clip).eval()
     g = torch.Generator().manual_seed(1234 + seed)
@@ -77,11 +77,29 @@ def run(name, B, H, n_steps, pe, clip, cond=None, start=False, max_t=None, seed=
         yf = net(xf, {}, tf)
     ck = float(sum(v.double().sum() for v in sd.values()))
     np.savez_compressed(os.path.join(HERE, name + ".npz"), chain=chain, noise=stack.numpy(), fwd_x=xf.numpy(),
-                        fwd_t=tf.numpy(), fwd_y=yf.numpy(), weight_checksum=ck,
+                        fwd_t=tf.numpy(), fwd_y=yf.numpy(), weight_checksum=ck, attention=np.array(int(attention)),
                         start=(kw["starting_motion"].numpy() if start else np.zeros(0, np.float32)),
                         meta=np.array([B, H, n_steps, int(pe), int(clip), int(cond is not None), int(start),
                                        -1 if max_t is None else max_t, seed]))
     print(name, chain.shape, "checksum", ck)
+
+
+def fid_fixture():
+    """metrics/fid_score.py:24-81 run unmodified on CPU: statistics of two seeded sample sets and their FID."""
+    with contextlib.redirect_stdout(io.StringIO()):
+        from metrics.fid_score import MotionFID
+    g = torch.Generator().manual_seed(77)
+    N, H = 600, 6
+    a = torch.randn(N, H, 35, generator=g) * 0.3 + torch.randn(1, H, 35, generator=g)
+    b = a[: N // 2] * 1.1 + 0.05 + 0.02 * torch.randn(N // 2, H, 35, generator=g)
+    fid = MotionFID(None, None, device="cpu")
+    mu1, s1 = fid.calculate_activation_statistics(a)
+    mu2, s2 = fid.calculate_activation_statistics(b)
+    val = fid.calculate_fid(mu1, s1, mu2, s2)
+    half = fid.calculate_fid(*fid.calculate_activation_statistics(a[::2]), *fid.calculate_activation_statistics(a[1::2]))
+    np.savez_compressed(os.path.join(HERE, "fid_reference.npz"), a=a.numpy(), b=b.numpy(), mu1=mu1, sigma1=s1, mu2=mu2,
+                        sigma2=s2, fid=np.array(val), fid_halves=np.array(half))
+    print("fid_reference", val, half)
 
 
 if __name__ == "__main__":
@@ -89,6 +107,9 @@ if __name__ == "__main__":
     run("unet_chain_box_eps_clip", B=3, H=16, n_steps=12, pe=True, clip=True, cond=box_holding, seed=1)
     run("unet_chain_start_maxt", B=2, H=24, n_steps=10, pe=False, clip=False, cond=box_holding, start=True, max_t=4,
         seed=2)
+    # attention=True variant (LinearAttention, helpers.py:75-131); H=24 exercises L=3 at the deepest level
+    run("unet_chain_attention", B=2, H=24, n_steps=5, pe=False, clip=False, cond=box_holding, seed=3, attention=True)
+    fid_fixture()
     # schedule buffers straight from the reference module
     with contextlib.redirect_stdout(io.StringIO()):
         net = TemporalUnet(8, 35, 35)

@@ -113,6 +113,15 @@ def test_no_cpu_fallback():
         assert rc == -2 and b"no CPU fallback" in _lib.lib().dm_last_error()
 
 
-def test_attention_rejected():
-    with pytest.raises(NotImplementedError):
-        dm.TemporalUnet(64, 35, 35, attention=True)
+def test_attention_state_dict_matches_reference_keys():
+    """attention=True keeps the reference's parameter names/shapes (helpers.py:75-131, temporal.py:85,94,103)."""
+    from oracle import diffusion_oracle as O
+    net = dm.TemporalUnet(64, 35, 35, attention=True)
+    sd = O.seeded_state_dict(H=64, attention=True)
+    mine = net.state_dict()
+    assert set(mine) == set(sd)
+    assert all(tuple(mine[k].shape) == tuple(sd[k].shape) for k in sd)
+    assert tuple(mine["mid_attn.fn.fn.to_qkv.weight"].shape) == (384, 256, 1)
+    assert tuple(mine["downs.0.2.fn.norm.g"].shape) == (1, 32, 1)
+    with pytest.raises(dm.DmError):                      # still no CPU path
+        net(torch.zeros(1, 64, 35), {}, torch.zeros(1))

@@ -104,6 +104,49 @@ def test_chain_matches_reference_fixture(dm, golden_dir, name, fused):
             assert torch.equal(chain[:, k][m], ref[:, k][m]), "conditioned channels must be bit-exact"
 
 
+@pytest.mark.parametrize("B,H", [(3, 64), (17, 16), (2, 24), (5, 128)])
+def test_attention_unet_layers_match_oracle(dm, B, H):
+    """attention=True (Residual(PreNorm(LinearAttention)), helpers.py:75-131): every layer, attention stages included."""
+    sd = O.seeded_state_dict(H=H, seed=B + 40, attention=True)
+    net = dm.TemporalUnet(H, 35, 35, attention=True)
+    net.load_state_dict(sd)
+    g = torch.Generator().manual_seed(B * 100 + H + 7)
+    x = torch.randn(B, H, 35, generator=g)
+    t = torch.randint(0, 100, (B,), generator=g)
+    rec = {}
+    y_ref = O.unet_forward(sd, x, t, record=rec)
+    y = net(x.cuda(), {}, t.cuda()).cpu()
+    plan = net.plan_for(B, H)
+    names = plan.layer_names()
+    assert sum(1 for n, _, _ in names if n.endswith(".2") or n == "mid_attn") == 8
+    for i, (name, C, L) in enumerate(names):
+        if C == 0:
+            continue
+        got = plan.read_layer(i, C, L).cpu()
+        assert rel(got, rec[name]) < 1e-4, (name, rel(got, rec[name]))
+    assert rel(y, y_ref) < 1e-4
+
+
+def test_attention_chain_matches_reference_fixture(dm, golden_dir):
+    """p_sample_loop of the attention=True model against the chain recorded from the UNMODIFIED reference."""
+    z = np.load(os.path.join(golden_dir, "unet_chain_attention.npz"))
+    B, H, n_steps, pe, clip, cond, start, max_t, seed = [int(v) for v in z["meta"]]
+    net = dm.TemporalUnet(H, 35, 35, attention=True)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=seed, attention=True))
+    y = net(torch.from_numpy(z["fwd_x"]).cuda(), {}, torch.from_numpy(z["fwd_t"]).cuda()).cpu()
+    assert rel(y, torch.from_numpy(z["fwd_y"])) < 1e-4
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n_steps, predict_epsilon=bool(pe), clip_denoised=bool(clip)).cuda()
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, conditioning_fn=box_holding,
+                             sample_fn=dm.InjectedNoise(torch.from_numpy(z["noise"])))
+    ref = torch.from_numpy(z["chain"])
+    chain = out.chains.cpu()
+    for k in range(ref.shape[1]):
+        assert rel(chain[:, k], ref[:, k]) < REL_STEP, (k, rel(chain[:, k], ref[:, k]))
+    m = box_cond(H)[0].expand(B, H, 35)
+    assert torch.equal(chain[:, -1][m], ref[:, -1][m])
+    assert diff.last_launch_count > n_steps * 40          # per-layer launches: the fused loop has no attention stage
+
+
 def test_hundred_step_chain_vs_oracle(dm):
     """100 steps, H=64, box-holding conditioning: free-running chain stays within 1e-3 of the fp32 oracle."""
     B, H, n = 2, 64, 100
@@ -240,8 +283,9 @@ def test_errors_are_loud(dm):
         net(torch.zeros(1, 64, 35), {}, torch.zeros(1))          # CPU tensor: no fallback
     with pytest.raises(dm.DmError):
         net(torch.zeros(1, 60, 35).cuda(), {}, torch.zeros(1).cuda())   # H % 8 != 0
-    with pytest.raises(NotImplementedError):
-        dm.TemporalUnet(64, 35, 35, attention=True)
+    with pytest.raises(dm.DmError):                               # attention tile beyond shared memory
+        net_a = dm.TemporalUnet(512, 35, 35, attention=True)
+        net_a(torch.zeros(1, 512, 35).cuda(), {}, torch.zeros(1).cuda())
     diff = dm.GaussianDiffusion(net, 64, 35, n_timesteps=10).cuda()
     with pytest.raises(dm.DmError):
         diff.p_sample_loop((1, 64, 35), {}, verbose=False, conditioning_fn=lambda x: x * 0.5)
