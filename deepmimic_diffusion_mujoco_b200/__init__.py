@@ -6,6 +6,7 @@ Public names mirror the reference modules they replace:
   diffuser.models.sampling_config.apply_conditioning* -> sampling_config
   data_loaders.motion_dataset.MotionDataset        -> MotionDataset
   metrics.fid_score.MotionFID                      -> MotionFID
+  diffuser.models.diffusion_v4.DiffusionV4 (sample) -> DiffusionV4
 """
 from ._lib import DmError, build, lib  # noqa: F401
 from .diffusion import GaussianDiffusion, InjectedNoise, Sample, default_sample_fn  # noqa: F401
@@ -14,3 +15,4 @@ from .sampling_config import (apply_conditioning, apply_conditioning_motion_edit
 from .temporal import TemporalUnet  # noqa: F401
 from .motion_dataset import Batch, MotionDataset, save_motion_npy  # noqa: F401
 from .scoring import MotionFID  # noqa: F401
+from .diffusion_v4 import DiffusionV4  # noqa: F401

@@ -30,7 +30,8 @@ class DmTensor(ctypes.Structure):
 class DmSchedule(ctypes.Structure):
     _fields_ = [("n_timesteps", ctypes.c_int), ("sqrt_recip_alphas_cumprod", ctypes.c_void_p),
                 ("sqrt_recipm1_alphas_cumprod", ctypes.c_void_p), ("posterior_mean_coef1", ctypes.c_void_p),
-                ("posterior_mean_coef2", ctypes.c_void_p), ("posterior_log_variance_clipped", ctypes.c_void_p)]
+                ("posterior_mean_coef2", ctypes.c_void_p), ("posterior_log_variance_clipped", ctypes.c_void_p),
+                ("time_values", ctypes.c_void_p)]
 
 
 class DmCond(ctypes.Structure):

@@ -869,7 +869,7 @@ extern "C" int dm_plan_set_schedule(dm_plan_t* P, const dm_schedule_t* s) {
   P->logvar.assign(s->posterior_log_variance_clipped, s->posterior_log_variance_clipped + n);
   P->n_timesteps = n;
   std::vector<float> tv(n);
-  for (int i = 0; i < n; ++i) tv[i] = (float)i;
+  for (int i = 0; i < n; ++i) tv[i] = s->time_values ? s->time_values[i] : (float)i;
   int rc;
   if ((rc = upload(P, tv, &P->t_table))) return rc;
   if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tb_table), (size_t)n * P->TB * sizeof(float)))) return rc;

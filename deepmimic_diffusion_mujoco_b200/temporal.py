@@ -120,6 +120,10 @@ class UnetPlan:
         s.n_timesteps = len(keep["posterior_mean_coef1"])
         for k, v in keep.items():
             setattr(s, k, v.data_ptr())
+        if bufs.get("time_values") is not None:
+            tv = bufs["time_values"].detach().to("cpu", torch.float32).contiguous()
+            keep["time_values"] = tv
+            s.time_values = tv.data_ptr()
         _lib.check(_lib.lib().dm_plan_set_schedule(self.handle, ctypes.byref(s)))
         self.schedule_id = sched_id
 

@@ -46,6 +46,9 @@ typedef struct {
   const float* posterior_mean_coef1;
   const float* posterior_mean_coef2;
   const float* posterior_log_variance_clipped;
+  /* Optional: the timestep value fed to the time embedding at each schedule index (NULL: index i embeds t = i).
+   * DiffusionV4.sample (diffuser/models/diffusion_v4.py:100-147) walks t = T-1..1, i.e. index i embeds t = i + 1. */
+  const float* time_values;
 } dm_schedule_t;
 
 /* Conditioning ("inpaint") spec: x = mask ? value : x, applied before the first step and after every step.
@@ -62,7 +65,8 @@ const char* dm_last_error(void);
 
 /* TemporalUnet.__init__ + load_state_dict (diffuser/models/temporal.py:51-113).  Packs the weights into fp16
  * hi/lo UMMA operand tiles, builds TMA descriptors and the per-layer launch list for batch B, horizon H,
- * transition_dim T.  attention=True is not supported (DM_ERR_ARG). */
+ * transition_dim T.  attention=True state dicts (helpers.py:75-131) add one launch per attention stage and switch
+ * dm_sample_loop to per-layer launches. */
 int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, int H, int T, int dim, const int* dim_mults,
                    int n_mults, dm_plan_t** plan);
 void dm_plan_free(dm_plan_t* plan);

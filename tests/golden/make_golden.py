@@ -84,6 +84,38 @@ def run(name, B, H, n_steps, pe, clip, cond=None, start=False, max_t=None, seed=
     print(name, chain.shape, "checksum", ck)
 
 
+def v4_fixture():
+    """DiffusionV4.sample (diffuser/models/diffusion_v4.py:82-149) run unmodified on CPU around the reference
+    TemporalUnet (an adaptor maps the sampler's model(x, t, y) call onto forward(x, cond, time)); the noise it drew
+    is recovered by re-seeding."""
+    with contextlib.redirect_stdout(io.StringIO()):
+        from diffuser.models.diffusion_v4 import DiffusionV4
+    out = {}
+    for tag, px0, sched, seed in (("x0_cosine", True, "cosine", 11), ("eps_linear", False, "linear", 12)):
+        B, H, T = 2, 16, 10
+        with contextlib.redirect_stdout(io.StringIO()):
+            net = TemporalUnet(H, 35, 35)
+        net.load_state_dict(seeded_state_dict(H=H, seed=seed))
+
+        class Adaptor(torch.nn.Module):
+            def forward(self, x, t, y):
+                return net(x, {}, t)
+
+        d = DiffusionV4(T, 1e-4, 0.02, 35, H, device="cpu", predict_x0=px0, schedule_type=sched)
+        torch.manual_seed(555 + seed)
+        x = d.sample(Adaptor(), B)
+        torch.manual_seed(555 + seed)
+        stack = [torch.randn(B, H, 35)]
+        for i in reversed(range(1, T)):
+            stack.append(torch.randn(B, H, 35) if i > 1 else torch.zeros(B, H, 35))
+        out[tag + "_x"] = x.numpy()
+        out[tag + "_noise"] = torch.stack(stack).numpy()
+        out[tag + "_beta"] = d.beta.numpy()
+        out[tag + "_meta"] = np.array([B, H, T, int(px0), seed])
+    np.savez_compressed(os.path.join(HERE, "v4_reference.npz"), **out)
+    print("v4_reference", {k: v.shape for k, v in out.items()})
+
+
 def fid_fixture():
     """metrics/fid_score.py:24-81 run unmodified on CPU: statistics of two seeded sample sets and their FID."""
     with contextlib.redirect_stdout(io.StringIO()):
@@ -110,6 +142,7 @@ if __name__ == "__main__":
     # attention=True variant (LinearAttention, helpers.py:75-131); H=24 exercises L=3 at the deepest level
     run("unet_chain_attention", B=2, H=24, n_steps=5, pe=False, clip=False, cond=box_holding, seed=3, attention=True)
     fid_fixture()
+    v4_fixture()
     # schedule buffers straight from the reference module
     with contextlib.redirect_stdout(io.StringIO()):
         net = TemporalUnet(8, 35, 35)

@@ -64,6 +64,27 @@ def test_unet_layers_match_oracle(dm, B, H):
     assert rel(y, y_ref) < 1e-4
 
 
+@pytest.mark.parametrize("B,H,T,dim", [(3, 32, 69, 128), (2, 32, 35, 64)])
+def test_wide_unet_matches_oracle(dm, B, H, T, dim):
+    """The later-generation configuration (temporal_v2.py dim=128, eval.py:189-197 horizon 32; T=69 features)."""
+    sd = O.seeded_state_dict(H=H, T=T, dim=dim, seed=B)
+    net = dm.TemporalUnet(H, T, T, dim=dim)
+    net.load_state_dict(sd)
+    g = torch.Generator().manual_seed(dim + T)
+    x = torch.randn(B, H, T, generator=g)
+    t = torch.randint(0, 100, (B,), generator=g)
+    rec = {}
+    y_ref = O.unet_forward(sd, x, t, dim=dim, record=rec)
+    y = net(x.cuda(), {}, t.cuda()).cpu()
+    plan = net.plan_for(B, H)
+    for i, (name, C, L) in enumerate(plan.layer_names()):
+        if C == 0:
+            continue
+        got = plan.read_layer(i, C, L).cpu()
+        assert rel(got, rec[name]) < 1e-4, (name, rel(got, rec[name]))
+    assert rel(y, y_ref) < 1e-4
+
+
 @pytest.mark.parametrize("name", ["unet_chain_plain", "unet_chain_box_eps_clip", "unet_chain_start_maxt"])
 def test_forward_matches_reference_fixture(dm, golden_dir, name):
     z = np.load(os.path.join(golden_dir, name + ".npz"))
@@ -145,6 +166,35 @@ def test_attention_chain_matches_reference_fixture(dm, golden_dir):
     m = box_cond(H)[0].expand(B, H, 35)
     assert torch.equal(chain[:, -1][m], ref[:, -1][m])
     assert diff.last_launch_count > n_steps * 40          # per-layer launches: the fused loop has no attention stage
+
+
+@pytest.mark.parametrize("tag,sched", [("x0_cosine", "cosine"), ("eps_linear", "linear")])
+@pytest.mark.parametrize("fused", [True, False])
+def test_v4_sampler_matches_reference_fixture(dm, golden_dir, tag, sched, fused):
+    """DiffusionV4.sample (diffusion_v4.py:82-149) on the CUDA loop vs the unmodified reference's output."""
+    z = np.load(os.path.join(golden_dir, "v4_reference.npz"))
+    B, H, T, px0, seed = [int(v) for v in z[tag + "_meta"]]
+    sd = O.seeded_state_dict(H=H, seed=seed)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    d = dm.DiffusionV4(T, 1e-4, 0.02, 35, H, device="cuda", predict_x0=bool(px0), schedule_type=sched)
+    noise = torch.from_numpy(z[tag + "_noise"])
+    if not fused:
+        os.environ["DM_B200_V4_UNFUSED"] = "1"
+    try:
+        x, chain = d.sample(net.cuda(), B, noise=noise, return_chain=True)
+    finally:
+        os.environ.pop("DM_B200_V4_UNFUSED", None)
+    ref = torch.from_numpy(z[tag + "_x"])
+    assert rel(x.cpu(), ref) < REL_STEP
+    oc = O.v4_sample(sd, O.v4_betas(T, 1e-4, 0.02, sched), noise, bool(px0))
+    for k in range(oc.shape[1]):
+        assert rel(chain[:, k].cpu(), oc[:, k]) < REL_STEP, k
+    assert d.last_launch_count == (1 if fused else (T - 1) * 41 + 1)
+    # Philox path: finite, seeded, reproducible
+    a = d.sample(net, 4, seed=9)
+    b = d.sample(net, 4, seed=9)
+    assert torch.isfinite(a).all() and torch.equal(a, b)
 
 
 def test_hundred_step_chain_vs_oracle(dm):
