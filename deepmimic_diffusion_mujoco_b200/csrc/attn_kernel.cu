@@ -19,15 +19,20 @@
 
 namespace dm {
 
-constexpr int kAttnThreads = 256;
+constexpr int kAttnThreads = 512;
 constexpr int kLc = 8;   // positions per register tile
 
 __device__ __forceinline__ int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+__host__ __device__ __forceinline__ int row_pitch(int L) { return (L & 3) ? (L | 1) : L + 4; }
+
+// kVec: L is a multiple of 4 -> rows are 16-byte aligned (pitch L + 4) and the two 1x1 convs run on 4 x 4 register
+// tiles fed by one 16-byte weight load and one 16-byte activation load per 16 FMAs.
+template <bool kVec>
 __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const AttnParams p) {
-  extern __shared__ float sm[];
+  extern __shared__ __align__(16) float sm[];
   const int C = p.C, L = p.L, NS = p.NS;
-  const int Lp = L | 1;                       // odd row pitch: column walks are conflict-free
+  const int Lp = row_pitch(L);
   float* xs = sm;                             // [NS][C][Lp]  input, becomes the output accumulator
   float* xn = xs + NS * C * Lp;               // [NS][C][Lp]  normalised input
   float* qkv = xn + NS * C * Lp;              // [NS][96][Lp] q | k (later o) | v of the current head
@@ -62,6 +67,36 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
   const int n_lc = ceil_div(L, kLc);
   for (int h = 0; h < p.heads; ++h) {
     // ---- q, k, v rows of this head: W_qkv^T is [C][3*heads*32] so that a warp reads consecutive rows coalesced ----
+    if (kVec) {
+      const int n_l4 = L >> 2;
+      const int OW = 3 * p.heads * 32;
+      for (int i = tid; i < 24 * NS * n_l4; i += kAttnThreads) {
+        const int oq = i % 24, s = (i / 24) % NS, l0 = (i / (24 * NS)) << 2;
+        const int o = oq << 2, part = o >> 5, d = o & 31;
+        const float* wr = p.wqkv_t + part * (p.heads * 32) + h * 32 + d;
+        const float* xr = xn + s * C * Lp + l0;
+        float acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+        for (int c = 0; c < C; ++c) {
+          const float4 w = __ldg(reinterpret_cast<const float4*>(wr + (size_t)c * OW));
+          const float4 x = *reinterpret_cast<const float4*>(xr + c * Lp);
+          const float wv[4] = {w.x, w.y, w.z, w.w}, xv[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(wv[a], xv[b], acc[a][b]);
+        }
+        const float sc = part == 0 ? p.scale : 1.f;
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+          *reinterpret_cast<float4*>(qkv + (s * 96 + o + a) * Lp + l0) =
+              make_float4(acc[a][0] * sc, acc[a][1] * sc, acc[a][2] * sc, acc[a][3] * sc);
+      }
+    } else
     for (int i = tid; i < 96 * NS * n_lc; i += kAttnThreads) {
       const int o = i % 96, s = (i / 96) % NS, lc = i / (96 * NS);
       const int part = o >> 5, d = o & 31;
@@ -125,6 +160,38 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
     }
     __syncthreads();
     // ---- xs += W_out[:, head] o  (+ bias once): W_out^T is [heads*32][C] ----
+    if (kVec) {
+      const int n_l4 = L >> 2, n_c4 = C >> 2;
+      for (int i = tid; i < n_c4 * NS * n_l4; i += kAttnThreads) {
+        const int co = (i % n_c4) << 2, s = (i / n_c4) % NS, l0 = (i / (n_c4 * NS)) << 2;
+        float acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          const float b0 = h == 0 ? __ldg(p.bout + co + a) : 0.f;
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = b0;
+        }
+        const float* orow = qkv + (s * 96 + 32) * Lp + l0;
+        const float* wr = p.wout_t + (size_t)(h * 32) * C + co;
+#pragma unroll 4
+        for (int e = 0; e < 32; ++e) {
+          const float4 w = __ldg(reinterpret_cast<const float4*>(wr + (size_t)e * C));
+          const float4 x = *reinterpret_cast<const float4*>(orow + e * Lp);
+          const float wv[4] = {w.x, w.y, w.z, w.w}, xv[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(wv[a], xv[b], acc[a][b]);
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          float4* dst = reinterpret_cast<float4*>(xs + (s * C + co + a) * Lp + l0);
+          float4 v = *dst;
+          v.x += acc[a][0]; v.y += acc[a][1]; v.z += acc[a][2]; v.w += acc[a][3];
+          *dst = v;
+        }
+      }
+    } else
     for (int i = tid; i < C * NS * n_lc; i += kAttnThreads) {
       const int co = i % C, s = (i / C) % NS, lc = i / (C * NS);
       const int l0 = lc * kLc;
@@ -157,7 +224,7 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
 }
 
 size_t attention_smem_bytes(int C, int L, int NS) {
-  const int Lp = L | 1;
+  const int Lp = row_pitch(L);
   return sizeof(float) * ((size_t)2 * NS * C * Lp + (size_t)NS * 96 * Lp + (size_t)NS * 32 * 33);
 }
 
@@ -169,11 +236,12 @@ int attention_pick_ns(int C, int L) {
 
 cudaError_t launch_linear_attention(const AttnParams& p, int n_groups, cudaStream_t s) {
   const size_t smem = attention_smem_bytes(p.C, p.L, p.NS);
+  auto kern = (p.L & 3) ? linear_attention_kernel<false> : linear_attention_kernel<true>;
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(linear_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  linear_attention_kernel<<<n_groups * (kGroupSamples / p.NS), kAttnThreads, smem, s>>>(p);
+  kern<<<n_groups * (kGroupSamples / p.NS), kAttnThreads, smem, s>>>(p);
   return cudaGetLastError();
 }
 

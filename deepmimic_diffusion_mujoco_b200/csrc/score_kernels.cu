@@ -177,6 +177,50 @@ __global__ void __launch_bounds__(256) fid_moments_kernel(const float* __restric
   if (ti == tj && threadIdx.x < kFidTile && i0 + (int)threadIdx.x < D) atomicAdd(&sum[i0 + threadIdx.x], (double)colsum);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Batched window statistics for SiFID (eval.py:59-77: per generated sample, mean and covariance over its W windows
+// of D = window_size * n_feats values, fid_score.py:24-43 arithmetic in fp32).  One CTA per (sample, 8-row band of
+// the covariance); the sample's W x D window matrix is centred in shared memory.  HBM-bound on the D x D output.
+// ------------------------------------------------------------------------------------------------
+constexpr int kWinRows = 8;
+
+__global__ void __launch_bounds__(256) window_moments_kernel(const float* __restrict__ X, int H, int F, int W, int win,
+                                                             int step, float* __restrict__ mu, float* __restrict__ sigma) {
+  extern __shared__ float wsm[];   // [W][D] centred windows
+  const int D = win * F;
+  const int n = blockIdx.y;
+  const float* xs = X + (size_t)n * H * F;
+  // window w covers frames [w*step, w*step + win): D contiguous floats starting at w*step*F
+  for (int i = threadIdx.x; i < W * D; i += blockDim.x) {
+    const int w = i / D, d = i - w * D;
+    wsm[i] = __ldg(xs + (size_t)w * step * F + d);
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float m = 0.f;
+    for (int w = 0; w < W; ++w) m += wsm[w * D + d];
+    m /= (float)W;
+    for (int w = 0; w < W; ++w) wsm[w * D + d] -= m;
+    if (blockIdx.x == 0) mu[(size_t)n * D + d] = m;
+  }
+  __syncthreads();
+  const float inv = 1.f / (float)(W - 1);
+  const int i0 = blockIdx.x * kWinRows;
+  for (int j = threadIdx.x; j < D; j += blockDim.x) {
+    float acc[kWinRows];
+#pragma unroll
+    for (int r = 0; r < kWinRows; ++r) acc[r] = 0.f;
+    for (int w = 0; w < W; ++w) {
+      const float b = wsm[w * D + j];
+#pragma unroll
+      for (int r = 0; r < kWinRows; ++r) if (i0 + r < D) acc[r] = fmaf(wsm[w * D + i0 + r], b, acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < kWinRows; ++r)
+      if (i0 + r < D) __stcs(sigma + ((size_t)n * D + i0 + r) * D + j, acc[r] * inv);
+  }
+}
+
 }  // namespace dm
 
 using namespace dm;
@@ -253,5 +297,28 @@ extern "C" int dm_fid_moments(const float* X_dev, int N, int D, double* sum_dev,
   fid_moments_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(st)>>>(X_dev, N, D, rows, sum_dev, sxx_dev);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(DM_ERR_CUDA, "fid_moments launch: %s", cudaGetErrorString(e));
+  return DM_OK;
+}
+
+extern "C" int dm_window_moments(const float* X_dev, int N, int H, int F, int window, int step, float* mu_dev, float* sigma_dev,
+                                 dm_stream_t st) {
+  if (!X_dev || !mu_dev || !sigma_dev) return fail(DM_ERR_ARG, "null argument");
+  if (N < 1 || H < 1 || F < 1 || window < 1 || step < 1 || window > H) return fail(DM_ERR_ARG, "need N, F, step >= 1 and 1 <= window <= H");
+  const int W = (H - window) / step + 1;   // offsets 0, step, 2 step, ... <= H - window (eval.py:15-21)
+  if (W < 2) return fail(DM_ERR_ARG, "need at least two windows per sample (covariance divides by W - 1)");
+  int rc = check_device();
+  if (rc) return rc;
+  const int D = window * F;
+  const size_t smem = (size_t)W * D * sizeof(float);
+  if (smem > 200 * 1024) return fail(DM_ERR_ARG, "window matrix %d x %d does not fit in shared memory", W, D);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(window_moments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail(DM_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  }
+  if (N > 65535) return fail(DM_ERR_ARG, "at most 65535 samples per call");
+  dim3 grid((D + kWinRows - 1) / kWinRows, N);
+  window_moments_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(st)>>>(X_dev, H, F, W, window, step, mu_dev, sigma_dev);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(DM_ERR_CUDA, "window_moments launch: %s", cudaGetErrorString(e));
   return DM_OK;
 }

@@ -51,6 +51,69 @@ def fid_moments(data, sum_out=None, sxx_out=None):
     return sum_out, sxx_out
 
 
+def slice_motion_sample(sample, window_size, step_size=10):
+    """eval.py:15-21: windows of `window_size` frames at offsets 0, step, 2 step, ... -> [W, window_size, nfeats]."""
+    return sample.unfold(0, window_size, step_size).permute(0, 2, 1).contiguous()
+
+
+def window_moments(samples, window_size=10, step_size=10):
+    """Per-sample mean [N,D] and covariance [N,D,D] (fp32) over each sample's windows -- the statistics calc_sifid
+    (eval.py:59-77) computes one sample at a time -- in one launch."""
+    _need_cuda(samples, "samples")
+    X = samples.to(torch.float32).contiguous()
+    N, H, F = X.shape
+    D = window_size * F
+    mu = torch.empty(N, D, device=X.device, dtype=torch.float32)
+    sigma = torch.empty(N, D, D, device=X.device, dtype=torch.float32)
+    with torch.cuda.device(X.device):
+        _lib.check(_lib.lib().dm_window_moments(X.data_ptr(), N, H, F, window_size, step_size, mu.data_ptr(),
+                                                sigma.data_ptr(), _lib.stream_ptr()))
+    return mu, sigma
+
+
+def calc_sifid(gen_samples, gt_sample, window_size=10, batch=64):
+    """SiFID (eval.py:59-77): mean over generated samples of the FID between the window statistics of the ground-truth
+    motion and of that sample.  Statistics: one dm_window_moments launch; the per-sample D x D SVDs
+    (fid_score.py:64-67) are batched torch.linalg.svd calls (library code by design)."""
+    _need_cuda(gen_samples, "gen_samples")
+    dev = gen_samples.device
+    gt = gt_sample.to(device=dev, dtype=torch.float32)
+    gmu, gsig = window_moments(gt[None], window_size)
+    gmu, gsig = gmu[0], gsig[0]
+    mu, sig = window_moments(gen_samples, window_size)
+    fids = []
+    for i in range(0, mu.shape[0], batch):
+        m, s = mu[i:i + batch], sig[i:i + batch]
+        diff = gmu[None] - m
+        U, sv, Vh = torch.linalg.svd(gsig[None] @ s)
+        covmean_tr = ((U * torch.sqrt(torch.clamp(sv, min=1e-6))[:, None, :]) * Vh.transpose(1, 2)).sum(dim=(1, 2))
+        fids.append((diff * diff).sum(1) + torch.trace(gsig) + s.diagonal(dim1=1, dim2=2).sum(1) - 2 * covmean_tr)
+    return torch.cat(fids).mean().item()
+
+
+def calc_inter_diversity(samples):
+    """eval.py:54-57: distance between the first and second half of the sample set.  The 'unet' wrapper returns the
+    samples themselves as embeddings (eval.py:31-35); the norm runs over axis 1 (frames), as in the reference."""
+    _need_cuda(samples, "samples")
+    h = samples.shape[0] // 2
+    d = samples[:h].float() - samples[h:2 * h].float()
+    return torch.linalg.norm(d, dim=1).mean().item()
+
+
+def calc_intra_diversity(samples, window_size=10, offsets=None):
+    """eval.py:80-89: per sample, the distance between two windows at random offsets.  offsets: optional int array
+    [N,2]; None draws them with np.random.randint like the reference."""
+    import numpy as np
+    _need_cuda(samples, "samples")
+    N, H, F = samples.shape
+    if offsets is None:
+        offsets = np.stack([np.random.randint(H - window_size, size=2) for _ in range(N)])
+    off = torch.as_tensor(np.asarray(offsets), device=samples.device, dtype=torch.long)
+    idx = off[:, :, None] + torch.arange(window_size, device=samples.device)[None, None, :]      # [N,2,w]
+    win = torch.gather(samples.float()[:, None].expand(N, 2, H, F), 2, idx[..., None].expand(N, 2, window_size, F))
+    return torch.linalg.norm((win[:, 0] - win[:, 1]).reshape(N, -1), dim=1).mean().item()
+
+
 def shard_range(n, rank, world):
     """Contiguous split of n independent samples over `world` ranks (sizes differ by at most one)."""
     base, rem = divmod(int(n), int(world))

@@ -107,6 +107,12 @@ int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, int H, floa
  * ranks all-reduce. */
 int dm_fid_moments(const float* X_dev, int N, int D, double* sum_dev, double* sxx_dev, dm_stream_t stream);
 
+/* SiFID statistics (eval.py:59-77 calc_sifid -> slice_motion_sample :15-21 -> fid_score.py:24-43), batched over
+ * samples: X_dev fp32 [N,H,F]; windows of `window` frames at offsets 0, step, 2 step, ...; per sample
+ * mu_dev [N, D] and sigma_dev [N, D, D] (D = window * F, covariance over the sample's W windows, / (W - 1)). */
+int dm_window_moments(const float* X_dev, int N, int H, int F, int window, int step, float* mu_dev, float* sigma_dev,
+                      dm_stream_t stream);
+
 /* Test / debug introspection: the activation written by each layer launch, unpacked to fp32 [B,C,L]. */
 int dm_plan_num_layers(const dm_plan_t* plan);
 int dm_plan_layer_info(const dm_plan_t* plan, int i, char* name, int name_cap, int* C, int* L);

@@ -194,3 +194,31 @@ def fid_from_statistics(mu1, sigma1, mu2, sigma2, eps=1e-6):
     U, s, Vh = np.linalg.svd(sigma1 @ sigma2)
     covmean = U @ np.diag(np.sqrt(np.clip(s, eps, None))) @ Vh
     return float(diff @ diff + np.trace(sigma1) + np.trace(sigma2) - 2 * np.trace(covmean))
+
+
+# ---- SiFID / diversity: eval.py:15-21, 54-89 ----
+def slice_windows(sample, window_size, step_size=10):
+    sample = np.asarray(sample, dtype=np.float64)
+    offs = np.arange(sample.shape[0] - window_size + 1)[0::step_size]
+    return np.stack([sample[o:o + window_size] for o in offs])
+
+
+def sifid(gen_samples, gt_sample, window_size=10):
+    gmu, gsig = activation_statistics(slice_windows(gt_sample, window_size))
+    vals = []
+    for x in np.asarray(gen_samples, dtype=np.float64):
+        mu, sig = activation_statistics(slice_windows(x, window_size))
+        vals.append(fid_from_statistics(gmu, gsig, mu, sig))
+    return float(np.mean(vals))
+
+
+def inter_diversity(samples):
+    s = np.asarray(samples, dtype=np.float64)
+    h = s.shape[0] // 2
+    return float(np.linalg.norm(s[:h] - s[h:2 * h], axis=1).mean())
+
+
+def intra_diversity(samples, offsets, window_size=10):
+    s = np.asarray(samples, dtype=np.float64)
+    return float(np.mean([np.linalg.norm(s[i, o[0]:o[0] + window_size] - s[i, o[1]:o[1] + window_size])
+                          for i, o in enumerate(offsets)]))

@@ -116,6 +116,35 @@ def v4_fixture():
     print("v4_reference", {k: v.shape for k, v in out.items()})
 
 
+def eval_metrics_fixture():
+    """eval.py:15-89 metric functions.  eval.py itself cannot be imported (it needs diffuser.models.qna, which the
+    reference does not ship), so the function definitions are compiled from its source, unmodified, at generation time."""
+    import ast
+    from scipy import linalg
+    with contextlib.redirect_stdout(io.StringIO()):
+        from metrics.fid_score import MotionFID
+    src = open("/root/reference/diffusion/eval.py").read()
+    want = {"slice_motion_sample", "CustomEvalWrapper", "calc_inter_diversity", "calc_sifid", "calc_intra_diversity"}
+    body = [n for n in ast.parse(src).body if isinstance(n, (ast.FunctionDef, ast.ClassDef)) and n.name in want]
+    ns = {"np": np, "linalg": linalg, "torch": torch, "MotionFID": MotionFID, "device": torch.device("cpu")}
+    exec(compile(ast.Module(body=body, type_ignores=[]), "eval.py", "exec"), ns)
+    g = torch.Generator().manual_seed(21)
+    N, H, F, w = 6, 40, 35, 10
+    gt = torch.randn(H, F, generator=g) * 0.4 + torch.linspace(0, 1, H)[:, None]
+    gen = gt[None] + 0.3 * torch.randn(N, H, F, generator=g)
+    wrap = ns["CustomEvalWrapper"](torch.nn.Identity())
+    sifid = ns["calc_sifid"](wrap, gen, gt, window_size=w)
+    inter = ns["calc_inter_diversity"](wrap, gen)
+    np.random.seed(5)
+    intra = ns["calc_intra_diversity"](wrap, gen, window_size=w)
+    np.random.seed(5)
+    offsets = np.stack([np.random.randint(H - w, size=2) for _ in range(N)])
+    slices = ns["slice_motion_sample"](gt, w).numpy()
+    np.savez_compressed(os.path.join(HERE, "eval_metrics_reference.npz"), gt=gt.numpy(), gen=gen.numpy(), sifid=np.array(sifid),
+                        inter=np.array(inter), intra=np.array(intra), offsets=offsets, gt_slices=slices)
+    print("eval_metrics_reference", sifid, inter, intra, slices.shape)
+
+
 def fid_fixture():
     """metrics/fid_score.py:24-81 run unmodified on CPU: statistics of two seeded sample sets and their FID."""
     with contextlib.redirect_stdout(io.StringIO()):
@@ -143,6 +172,7 @@ if __name__ == "__main__":
     run("unet_chain_attention", B=2, H=24, n_steps=5, pe=False, clip=False, cond=box_holding, seed=3, attention=True)
     fid_fixture()
     v4_fixture()
+    eval_metrics_fixture()
     # schedule buffers straight from the reference module
     with contextlib.redirect_stdout(io.StringIO()):
         net = TemporalUnet(8, 35, 35)

@@ -327,6 +327,26 @@ def test_fid_moments_match_oracle(dm):
     assert abs(f0 - f0_o) < 2e-2 * max(1.0, abs(f0_o))
 
 
+def test_eval_metrics_match_reference_fixture(dm, golden_dir):
+    """SiFID (batched window statistics kernel + batched SVD), inter / intra diversity vs eval.py:15-89."""
+    from deepmimic_diffusion_mujoco_b200 import scoring
+    z = np.load(os.path.join(golden_dir, "eval_metrics_reference.npz"))
+    gen, gt = torch.from_numpy(z["gen"]).cuda(), torch.from_numpy(z["gt"]).cuda()
+    assert np.array_equal(scoring.slice_motion_sample(gt, 10).cpu().numpy(), z["gt_slices"])
+    mu, sig = scoring.window_moments(gen, 10)
+    for i in range(gen.shape[0]):
+        mo, so = SO.activation_statistics(SO.slice_windows(z["gen"][i], 10))
+        assert np.abs(mu[i].cpu().numpy() - mo).max() < 1e-5
+        assert np.abs(sig[i].cpu().numpy() - so).max() < 1e-5 * max(1.0, np.abs(so).max())
+    assert abs(scoring.calc_sifid(gen, gt) - float(z["sifid"])) < 1e-2 * float(z["sifid"])
+    assert abs(scoring.calc_inter_diversity(gen) - float(z["inter"])) < 1e-5 * float(z["inter"])
+    assert abs(scoring.calc_intra_diversity(gen, offsets=z["offsets"]) - float(z["intra"])) < 1e-5 * float(z["intra"])
+    with pytest.raises(dm.DmError):
+        scoring.window_moments(gen[:, :15], 10)      # one window: covariance undefined
+    with pytest.raises(dm.DmError):
+        scoring.window_moments(gen.cpu(), 10)        # no CPU fallback
+
+
 def test_errors_are_loud(dm):
     net = dm.TemporalUnet(64, 35, 35)
     with pytest.raises(dm.DmError):
