@@ -139,6 +139,36 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
     }
     __syncthreads();
     // ---- ctx[d][e] = sum_l k[d][l] v[e][l] ----
+    if (kVec) {
+      // 4 x 4 register tile over rows {dq + 8a} x {eq + 8b}: rows 8 apart keep the 16-byte row loads of the eight
+      // threads that share a wavefront on distinct banks (pitch = 4 mod 32 words)
+      for (int i = tid; i < NS * 64; i += kAttnThreads) {
+        const int eq = i & 7, dq = (i >> 3) & 7, s = i >> 6;
+        const float* kr = qkv + (s * 96 + 32 + dq) * Lp;
+        const float* vr = qkv + (s * 96 + 64 + eq) * Lp;
+        float acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+        for (int l = 0; l < L; l += 4) {
+          float4 kv[4], vv[4];
+#pragma unroll
+          for (int a = 0; a < 4; ++a) kv[a] = *reinterpret_cast<const float4*>(kr + a * 8 * Lp + l);
+#pragma unroll
+          for (int b = 0; b < 4; ++b) vv[b] = *reinterpret_cast<const float4*>(vr + b * 8 * Lp + l);
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+              acc[a][b] = fmaf(kv[a].x, vv[b].x, fmaf(kv[a].y, vv[b].y, fmaf(kv[a].z, vv[b].z, fmaf(kv[a].w, vv[b].w, acc[a][b]))));
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) ctx[(s * 32 + dq + 8 * a) * 33 + eq + 8 * b] = acc[a][b];
+      }
+    } else
     for (int i = tid; i < NS * 1024; i += kAttnThreads) {
       const int e = i & 31, d = (i >> 5) & 31, s = i >> 10;
       const float* kr = qkv + (s * 96 + 32 + d) * Lp;
@@ -149,6 +179,32 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
     }
     __syncthreads();
     // ---- o[e][l] = sum_d ctx[d][e] q[d][l]; stored over the (dead) k rows ----
+    if (kVec) {
+      const int n_l4 = L >> 2;
+      for (int i = tid; i < NS * 8 * n_l4; i += kAttnThreads) {
+        const int eq = i & 7, l0 = ((i >> 3) % n_l4) << 2, s = (i >> 3) / n_l4;
+        const float* qc = qkv + (s * 96) * Lp + l0;
+        const float* cc = ctx + (s * 32) * 33 + eq;
+        float acc[4][4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[b][j] = 0.f;
+#pragma unroll 4
+        for (int d = 0; d < 32; ++d) {
+          const float4 q4 = *reinterpret_cast<const float4*>(qc + d * Lp);
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const float cv = cc[d * 33 + 8 * b];
+            acc[b][0] = fmaf(cv, q4.x, acc[b][0]); acc[b][1] = fmaf(cv, q4.y, acc[b][1]);
+            acc[b][2] = fmaf(cv, q4.z, acc[b][2]); acc[b][3] = fmaf(cv, q4.w, acc[b][3]);
+          }
+        }
+#pragma unroll
+        for (int b = 0; b < 4; ++b)   // k rows are dead after the ctx pass (barrier above)
+          *reinterpret_cast<float4*>(qkv + (s * 96 + 32 + eq + 8 * b) * Lp + l0) = make_float4(acc[b][0], acc[b][1], acc[b][2], acc[b][3]);
+      }
+    } else
     for (int i = tid; i < NS * 32 * L; i += kAttnThreads) {
       const int l = i % L, e = (i / L) & 31, s = i / (32 * L);
       const float* qc = qkv + (s * 96) * Lp + l;

@@ -60,7 +60,7 @@ static EncodeTiledFn get_encode() {
   }
   return fn;
 }
-static int encode_map(CUtensorMap* m, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+int encode_map(CUtensorMap* m, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                       const uint32_t* box, int swz) {
   EncodeTiledFn fn = get_encode();
   if (!fn) return fail(DM_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");

@@ -280,7 +280,7 @@ extern "C" int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, 
   return DM_OK;
 }
 
-extern "C" int dm_fid_moments(const float* X_dev, int N, int D, double* sum_dev, double* sxx_dev, dm_stream_t st) {
+int dm_fid_moments_simt(const float* X_dev, int N, int D, double* sum_dev, double* sxx_dev, dm_stream_t st) {
   if (!X_dev || !sum_dev || !sxx_dev) return fail(DM_ERR_ARG, "null argument");
   if (N < 1 || D < 1) return fail(DM_ERR_ARG, "need N >= 1, D >= 1");
   int rc = check_device();
