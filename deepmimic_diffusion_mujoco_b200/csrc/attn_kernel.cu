@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
   float* xn = xs + NS * C * Lp;               // [NS][C][Lp]  normalised input
   float* qkv = xn + NS * C * Lp;              // [NS][96][Lp] q | k (later o) | v of the current head
   float* ctx = qkv + NS * 96 * Lp;            // [NS][32][33]
+  float* wsm = ctx + NS * 32 * 33 + ((NS * 32 * 33) & 3 ? 4 - ((NS * 32 * 33) & 3) : 0);   // [32][96] weight chunk (16-byte aligned)
   const int tid = threadIdx.x;
   const int per_group = kGroupSamples / NS;
   const int g = blockIdx.x / per_group;
@@ -68,33 +69,49 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
   for (int h = 0; h < p.heads; ++h) {
     // ---- q, k, v rows of this head: W_qkv^T is [C][3*heads*32] so that a warp reads consecutive rows coalesced ----
     if (kVec) {
+      // The head's weight rows are staged through shared memory 32 input channels at a time by ALL threads (one
+      // exposed L2 latency per chunk instead of one per channel: at C = 256, L = 8 only 192 threads own a tile).
       const int n_l4 = L >> 2;
       const int OW = 3 * p.heads * 32;
-      for (int i = tid; i < 24 * NS * n_l4; i += kAttnThreads) {
-        const int oq = i % 24, s = (i / 24) % NS, l0 = (i / (24 * NS)) << 2;
-        const int o = oq << 2, part = o >> 5, d = o & 31;
-        const float* wr = p.wqkv_t + part * (p.heads * 32) + h * 32 + d;
+      const int n_items = 24 * NS * n_l4;
+      for (int i0 = 0; i0 < n_items; i0 += kAttnThreads) {
+        const int i = i0 + tid;
+        const bool live = i < n_items;
+        const int oq = i % 24, s = live ? (i / 24) % NS : 0, l0 = live ? (i / (24 * NS)) << 2 : 0;
+        const int o = oq << 2;
         const float* xr = xn + s * C * Lp + l0;
         float acc[4][4];
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
           for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
-#pragma unroll 4
-        for (int c = 0; c < C; ++c) {
-          const float4 w = __ldg(reinterpret_cast<const float4*>(wr + (size_t)c * OW));
-          const float4 x = *reinterpret_cast<const float4*>(xr + c * Lp);
-          const float wv[4] = {w.x, w.y, w.z, w.w}, xv[4] = {x.x, x.y, x.z, x.w};
+        for (int cb = 0; cb < C; cb += 32) {
+          __syncthreads();
+          for (int j = tid; j < 32 * 96; j += kAttnThreads) {
+            const int cc = j / 96, r = j - cc * 96;
+            wsm[j] = __ldg(p.wqkv_t + (size_t)(cb + cc) * OW + (r >> 5) * (p.heads * 32) + h * 32 + (r & 31));
+          }
+          __syncthreads();
+          if (live) {
+#pragma unroll 8
+            for (int cc = 0; cc < 32; ++cc) {
+              const float4 w = *reinterpret_cast<const float4*>(wsm + cc * 96 + o);
+              const float4 x = *reinterpret_cast<const float4*>(xr + (cb + cc) * Lp);
+              const float wv[4] = {w.x, w.y, w.z, w.w}, xv[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+              for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(wv[a], xv[b], acc[a][b]);
+            }
+          }
+        }
+        if (live) {
+          const float sc = (o >> 5) == 0 ? p.scale : 1.f;
 #pragma unroll
           for (int a = 0; a < 4; ++a)
-#pragma unroll
-            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(wv[a], xv[b], acc[a][b]);
+            *reinterpret_cast<float4*>(qkv + (s * 96 + o + a) * Lp + l0) =
+                make_float4(acc[a][0] * sc, acc[a][1] * sc, acc[a][2] * sc, acc[a][3] * sc);
         }
-        const float sc = part == 0 ? p.scale : 1.f;
-#pragma unroll
-        for (int a = 0; a < 4; ++a)
-          *reinterpret_cast<float4*>(qkv + (s * 96 + o + a) * Lp + l0) =
-              make_float4(acc[a][0] * sc, acc[a][1] * sc, acc[a][2] * sc, acc[a][3] * sc);
       }
     } else
     for (int i = tid; i < 96 * NS * n_lc; i += kAttnThreads) {
@@ -281,7 +298,7 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
 
 size_t attention_smem_bytes(int C, int L, int NS) {
   const int Lp = row_pitch(L);
-  return sizeof(float) * ((size_t)2 * NS * C * Lp + (size_t)NS * 96 * Lp + (size_t)NS * 32 * 33);
+  return sizeof(float) * ((size_t)2 * NS * C * Lp + (size_t)NS * 96 * Lp + (size_t)NS * 32 * 33 + 4 + 32 * 96);
 }
 
 int attention_pick_ns(int C, int L) {

@@ -1,4 +1,4 @@
-"""GPU-box measurement of the HBM-bound kernels against their roofline: K4 (DDPM update, standalone
+"""GPU-box measurement of the scoring-side kernels against their roofline: K4 (DDPM update, standalone
 launch), K5 (FK + tracking reward) and K6 (FID moments) at the configs[4] per-GPU size (8192 samples, H=64).
 Prints one JSON line per kernel: algorithmic bytes / CUDA-event time vs MEASURED_PEAKS.json hbm_gbs."""
 import ctypes, json, os, sys
@@ -50,12 +50,19 @@ print(json.dumps({"kernel": "fid_moments_kernel", "N": N, "D": D, "ms": ms, "TFL
 # K4 standalone
 net = dm.TemporalUnet(H, T, T); net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
 diff = dm.GaussianDiffusion(net, H, T, n_timesteps=100, predict_epsilon=False).cuda()
-B = 1024
-plan = net.plan_for(B, H); plan.set_schedule(diff._schedule_bufs(), diff._schedule_id())
-xk = torch.randn(B, H, T, device="cuda"); mo = torch.randn(B, H, T, device="cuda"); z = torch.randn(B, H, T, device="cuda")
 nul = ctypes.POINTER(_lib.DmCond)()
-for name, zp, bytes_per in [("ddpm_step_kernel (Philox noise)", None, 12 * T + 4 * 64), ("ddpm_step_kernel (injected noise)", z.data_ptr(), 16 * T + 4 * 64)]:
-    ms = timed(lambda: _lib.check(_lib.lib().dm_ddpm_step(plan.handle, xk.data_ptr(), mo.data_ptr(), zp, 1, 50, 0, 0, nul, _lib.stream_ptr())))
-    bb = B * H * bytes_per
-    print(json.dumps({"kernel": name, "frames": B * H, "ms": ms, "GBps": bb / ms / 1e6, "frac_hbm": bb / ms / 1e6 / peak,
-                      "note": "bytes = x read+write, model_out (+noise) read, plus the 64-channel fp16 hi/lo operand re-pack"}))
+for B in (1024, 16384):   # configs[1] batch (9 MB working set: launch-latency sized) and a batch far larger than L2
+    plan = net.plan_for(B, H); plan.set_schedule(diff._schedule_bufs(), diff._schedule_id())
+    xk = torch.randn(B, H, T, device="cuda"); mo = torch.randn(B, H, T, device="cuda"); z = torch.randn(B, H, T, device="cuda")
+    for name, zp, bytes_per in [("ddpm_step_kernel (Philox noise)", None, 12 * T + 4 * 64), ("ddpm_step_kernel (injected noise)", z.data_ptr(), 16 * T + 4 * 64)]:
+        ms = timed(lambda: _lib.check(_lib.lib().dm_ddpm_step(plan.handle, xk.data_ptr(), mo.data_ptr(), zp, 1, 50, 0, 0, nul, _lib.stream_ptr())))
+        bb = B * H * bytes_per
+        print(json.dumps({"kernel": name, "B": B, "frames": B * H, "ms": ms, "GBps": bb / ms / 1e6, "frac_hbm": bb / ms / 1e6 / peak,
+                          "note": "bytes = x read+write, model_out (+noise) read, plus the 64-channel fp16 hi/lo operand re-pack"}))
+    del plan, xk, mo, z
+# SiFID window statistics (eval.py:59-77), HBM-bound on the [N, 350, 350] covariance output
+Nw = 2048
+xw = torch.randn(Nw, 64, T, device="cuda")
+ms = timed(lambda: scoring.window_moments(xw, 10))
+bw = Nw * (64 * T * 4 + 350 * 4 + 350 * 350 * 4)
+print(json.dumps({"kernel": "window_moments_kernel", "N": Nw, "ms": ms, "GBps": bw / ms / 1e6, "frac_hbm": bw / ms / 1e6 / peak}))
