@@ -19,6 +19,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 H, T, N_DDPM, DIM = 64, 35, 100, 32
+NCU_DRAM_BYTES_PER_LAUNCH_B1024 = 39.75e9  # dram__bytes_read.sum + dram__bytes_write.sum, profiles/r1f_ncu_full_summary.md
 MFLOP_PER_SAMPLE_STEP = 78.868  # algorithmic FLOPs of one U-Net forward at H=64 (hooks on the reference)
 METRIC = "motion_frames_per_sec_sampled_100step_ddpm_h64"
 
@@ -202,7 +203,8 @@ def main():
     flops_step = MFLOP_PER_SAMPLE_STEP * 1e6 * B * N_DDPM
     achieved = flops_step / (ms_per_step / 1e3) / 1e12
     roofline = {"kernel": "sample_loop_kernel", "bound": "tensor", "achieved": achieved, "peak": tf_peak,
-                "unit": "TFLOP/s", "frac": achieved / tf_peak, "traffic": None, "peak_source": which + " bf16 sustained",
+                "unit": "TFLOP/s", "frac": achieved / tf_peak,
+                "traffic": NCU_DRAM_BYTES_PER_LAUNCH_B1024 if B == 1024 else None, "traffic_unit": "bytes per launch (ncu --set full, r1f)", "peak_source": which + " bf16 sustained",
                 "launches_per_step": diff.last_launch_count, "avg_launch_us": 1e3 * ms_per_step / diff.last_launch_count,
                 "algorithmic_flops_per_launch": flops_step / diff.last_launch_count,
                 "note": "fp16 hi/lo split: the tensor pipe executes 3x the algorithmic FLOPs; "

@@ -13,6 +13,6 @@ from .diffusion import GaussianDiffusion, InjectedNoise, Sample, default_sample_
 from .sampling_config import (apply_conditioning, apply_conditioning_motion_editing,  # noqa: F401
                               trace_conditioning)
 from .temporal import TemporalUnet  # noqa: F401
-from .motion_dataset import Batch, MotionDataset, save_motion_npy  # noqa: F401
+from .motion_dataset import Batch, MotionDataset, save_motion_npy, save_motions  # noqa: F401
 from .scoring import MotionFID  # noqa: F401
 from .diffusion_v4 import DiffusionV4  # noqa: F401

@@ -157,7 +157,7 @@ cudaError_t launch_ddpm_step(const StepParams& p, cudaStream_t s) {
                      (reinterpret_cast<uintptr_t>(p.chain) & 15) == 0 && (reinterpret_cast<uintptr_t>(p.xs) & 15) == 0;
   if (tiled) {
     long long blocks = (n_rows + kK4Rows - 1) / kK4Rows;
-    if (blocks > 148LL * 8) blocks = 148LL * 8;
+    if (blocks > 148LL * 16) blocks = 148LL * 16;
     const size_t smem = (size_t)kK4Rows * p.T * sizeof(float);
     ddpm_step_tiled_kernel<<<(unsigned)blocks, 256, smem, s>>>(p);
     return cudaGetLastError();

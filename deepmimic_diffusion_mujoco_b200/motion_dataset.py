@@ -108,3 +108,37 @@ def save_motion_npy(path, trajectory):
     if t.ndim != 2 or t.shape[1] != 35:
         raise ValueError("expected one trajectory [H, 35]")
     np.save(path, t.astype(np.float32))
+
+
+def save_motions(samples, output_dir, filenames=None, joint_indices=None):
+    """Bulk `.npy` export, the contract of transformer_inference.py:213-276 (`save_motions`): one float `[frames, 35]`
+    file per sample (first 35 features unless `joint_indices` says otherwise; padded with zeros / truncated to 35).
+    The whole sample set crosses PCIe ONCE (one device-to-host copy into pinned memory) instead of once per sample.
+    Returns the absolute paths."""
+    import os
+    os.makedirs(output_dir, exist_ok=True)
+    s = torch.as_tensor(samples).detach()
+    if s.dim() != 3:
+        raise ValueError("expected samples [N, frames, features]")
+    idx = list(range(35)) if joint_indices is None else list(joint_indices)
+    if len(idx) != 35:   # reference: "MuJoCo expects exactly 35 joints"
+        idx = idx[:35] if len(idx) > 35 else idx + list(range(len(idx), 35))
+    idx = [i for i in idx if i < s.shape[2]]
+    sel = s[:, :, idx].float()
+    if s.is_cuda:
+        host = torch.empty(sel.shape, dtype=torch.float32, pin_memory=True)
+        host.copy_(sel, non_blocking=True)
+        torch.cuda.current_stream(s.device).synchronize()
+    else:
+        host = sel.contiguous()
+    arr = host.numpy()
+    if arr.shape[2] < 35:
+        arr = np.concatenate([arr, np.zeros(arr.shape[:2] + (35 - arr.shape[2],), dtype=arr.dtype)], axis=2)
+    names = list(filenames or [])
+    names += [f"motion_{i}.npy" for i in range(len(names), arr.shape[0])]
+    out = []
+    for i in range(arr.shape[0]):
+        path = os.path.join(output_dir, names[i])
+        np.save(path, arr[i])
+        out.append(os.path.abspath(path))
+    return out

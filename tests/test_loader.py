@@ -53,3 +53,16 @@ def test_npy_writer_contract(tmp_path):
     back = np.load(str(p))
     assert back.dtype == np.float32 and back.shape == (64, 35)
     np.testing.assert_array_equal(back, traj.float().numpy())
+
+
+def test_bulk_writer_contract(tmp_path):
+    """save_motions (transformer_inference.py:213-276): one [frames, 35] file per sample, default names, 69 -> 35 features."""
+    s = torch.randn(3, 32, 69)
+    paths = MD.save_motions(s, str(tmp_path / "out"), filenames=["a.npy"])
+    assert [os.path.basename(p) for p in paths] == ["a.npy", "motion_1.npy", "motion_2.npy"]
+    for i, p in enumerate(paths):
+        back = np.load(p)
+        assert back.shape == (32, 35)
+        np.testing.assert_array_equal(back, s[i, :, :35].numpy())
+    small = MD.save_motions(torch.randn(1, 8, 20), str(tmp_path / "pad"))
+    assert np.load(small[0]).shape == (8, 35) and not np.load(small[0])[:, 20:].any()
