@@ -152,7 +152,9 @@ class GaussianDiffusion(nn.Module):
             values = torch.zeros(B, device=device)
             if verbose:
                 print(f"[ b200 sampler ] {timesteps} steps x {B} samples enqueued ({self.last_launch_count} launches)")
-            x, values = sort_by_values(x, values)   # advanced indexing: returns a fresh tensor, not the buffer
+            # sort_by_values (diffusion.py:225): the default sampler's values are all zero and a stable descending
+            # argsort of zeros is the identity, so the gather x[inds] is a plain copy out of the persistent buffer
+            x = x.clone()
         return Sample(x, values, chain)
 
     def _persistent(self, key, shape, dtype, device):

@@ -184,7 +184,13 @@ class TemporalUnet(nn.Module):
 
     # ---- plan cache: rebuilt when the batch/horizon or the weights change ----
     def _weights_version(self):
-        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+        # the Parameter objects never change after construction (load_state_dict / .to() update them in place);
+        # walking the module tree with self.parameters() on every sampling call cost 0.9 ms of host time
+        plist = self.__dict__.get("_param_list")
+        if plist is None:
+            plist = list(self.parameters())
+            self.__dict__["_param_list"] = plist
+        return tuple([(p.data_ptr(), p._version) for p in plist])
 
     def plan_for(self, B, H):
         key = (B, H)
