@@ -170,7 +170,9 @@ __global__ void __launch_bounds__(256) fid_reduce_kernel(const float* __restrict
   int ti = 0, rem = tile;
   while (rem >= nt - ti) { rem -= nt - ti; ++ti; }
   const int tj = ti + rem;
-  for (int e = threadIdx.x; e < kFidT * kFidT; e += 256) {
+  // blockIdx.y: one eighth (16 rows) of the tile, so that the grid covers the machine (171 tiles alone are 0.14 waves)
+  const int e0 = blockIdx.y * (kFidT * kFidT / 8);
+  for (int e = e0 + threadIdx.x; e < e0 + kFidT * kFidT / 8; e += 256) {
     const int r = e / kFidT, c = e % kFidT;
     const int i = ti * kFidT + r, j = tj * kFidT + c;
     if (i >= D || j >= D) continue;
@@ -256,7 +258,7 @@ extern "C" int dm_fid_moments(const float* X_dev, int N, int D, double* sum_dev,
     const int per = (chunks + best - 1) / best;
     const int splits = (chunks + per - 1) / per;
     fid_syrk_kernel<<<dim3(n_tiles, splits), kFidThreads, smem, s>>>(map, nt, chunks, per, partial);
-    fid_reduce_kernel<<<n_tiles, 256, 0, s>>>(partial, n_tiles, splits, nt, D, sxx_dev);
+    fid_reduce_kernel<<<dim3(n_tiles, 8), 256, 0, s>>>(partial, n_tiles, splits, nt, D, sxx_dev);
     e = cudaGetLastError();
   }
   cudaFreeAsync(partial, s);

@@ -182,8 +182,10 @@ __global__ void __launch_bounds__(256) fid_moments_kernel(const float* __restric
 // of D = window_size * n_feats values, fid_score.py:24-43 arithmetic in fp32).  One CTA per (sample, 8-row band of
 // the covariance); the sample's W x D window matrix is centred in shared memory.  HBM-bound on the D x D output.
 // ------------------------------------------------------------------------------------------------
-constexpr int kWinRows = 8;
+constexpr int kWinRows = 32;   // covariance rows per CTA
+constexpr int kWinMaxW = 32;   // windows per sample held in registers (H <= 320 at window 10, step 10)
 
+template <int kWMax>   // windows held in registers: the smallest of 8 / 16 / 32 that covers W (predicated-off FMAs still issue)
 __global__ void __launch_bounds__(256) window_moments_kernel(const float* __restrict__ X, int H, int F, int W, int win,
                                                              int step, float* __restrict__ mu, float* __restrict__ sigma) {
   extern __shared__ float wsm[];   // [W][D] centred windows
@@ -191,10 +193,8 @@ __global__ void __launch_bounds__(256) window_moments_kernel(const float* __rest
   const int n = blockIdx.y;
   const float* xs = X + (size_t)n * H * F;
   // window w covers frames [w*step, w*step + win): D contiguous floats starting at w*step*F
-  for (int i = threadIdx.x; i < W * D; i += blockDim.x) {
-    const int w = i / D, d = i - w * D;
-    wsm[i] = __ldg(xs + (size_t)w * step * F + d);
-  }
+  for (int w = 0; w < W; ++w)
+    for (int d = threadIdx.x; d < D; d += blockDim.x) wsm[w * D + d] = __ldg(xs + (size_t)w * step * F + d);
   __syncthreads();
   for (int d = threadIdx.x; d < D; d += blockDim.x) {
     float m = 0.f;
@@ -206,18 +206,22 @@ __global__ void __launch_bounds__(256) window_moments_kernel(const float* __rest
   __syncthreads();
   const float inv = 1.f / (float)(W - 1);
   const int i0 = blockIdx.x * kWinRows;
+  const int rows = min(kWinRows, D - i0);
+  // thread <-> column j: its W centred values stay in registers; the row values are shared-memory broadcasts, so an
+  // output element costs W FMAs + W broadcast loads and the D x D block leaves in coalesced streaming stores
   for (int j = threadIdx.x; j < D; j += blockDim.x) {
-    float acc[kWinRows];
+    float bcol[kWMax];
 #pragma unroll
-    for (int r = 0; r < kWinRows; ++r) acc[r] = 0.f;
-    for (int w = 0; w < W; ++w) {
-      const float b = wsm[w * D + j];
+    for (int w = 0; w < kWMax; ++w) bcol[w] = w < W ? wsm[w * D + j] : 0.f;
+    float* out = sigma + ((size_t)n * D + i0) * D + j;
+    for (int r = 0; r < rows; ++r) {
+      const float* arow = wsm + i0 + r;
+      float acc = 0.f;
 #pragma unroll
-      for (int r = 0; r < kWinRows; ++r) if (i0 + r < D) acc[r] = fmaf(wsm[w * D + i0 + r], b, acc[r]);
+      for (int w = 0; w < kWMax; ++w)
+        if (w < W) acc = fmaf(arow[w * D], bcol[w], acc);
+      __stcs(out + (size_t)r * D, acc * inv);
     }
-#pragma unroll
-    for (int r = 0; r < kWinRows; ++r)
-      if (i0 + r < D) __stcs(sigma + ((size_t)n * D + i0 + r) * D + j, acc[r] * inv);
   }
 }
 
@@ -306,18 +310,20 @@ extern "C" int dm_window_moments(const float* X_dev, int N, int H, int F, int wi
   if (N < 1 || H < 1 || F < 1 || window < 1 || step < 1 || window > H) return fail(DM_ERR_ARG, "need N, F, step >= 1 and 1 <= window <= H");
   const int W = (H - window) / step + 1;   // offsets 0, step, 2 step, ... <= H - window (eval.py:15-21)
   if (W < 2) return fail(DM_ERR_ARG, "need at least two windows per sample (covariance divides by W - 1)");
+  if (W > kWinMaxW) return fail(DM_ERR_ARG, "%d windows per sample; at most %d are supported", W, kWinMaxW);
   int rc = check_device();
   if (rc) return rc;
   const int D = window * F;
   const size_t smem = (size_t)W * D * sizeof(float);
   if (smem > 200 * 1024) return fail(DM_ERR_ARG, "window matrix %d x %d does not fit in shared memory", W, D);
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(window_moments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return fail(DM_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-  }
   if (N > 65535) return fail(DM_ERR_ARG, "at most 65535 samples per call");
   dim3 grid((D + kWinRows - 1) / kWinRows, N);
-  window_moments_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(st)>>>(X_dev, H, F, W, window, step, mu_dev, sigma_dev);
+  auto kern = W <= 8 ? window_moments_kernel<8> : (W <= 16 ? window_moments_kernel<16> : window_moments_kernel<32>);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail(DM_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  }
+  kern<<<grid, 256, smem, static_cast<cudaStream_t>(st)>>>(X_dev, H, F, W, window, step, mu_dev, sigma_dev);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(DM_ERR_CUDA, "window_moments launch: %s", cudaGetErrorString(e));
   return DM_OK;

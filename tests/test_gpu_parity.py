@@ -461,3 +461,56 @@ def test_full_size_properties(dm):
     assert torch.equal(a[:, :, 16], torch.full((1024, H), 1.57, device="cuda"))
     assert torch.equal(a[:, :, 17:20], torch.zeros(1024, H, 3, device="cuda"))
     assert torch.equal(a[:48], small)
+
+
+def test_fk_invariants_at_full_size(dm):
+    """configs[4] scoring size (65536 samples x 64 frames): properties of forward kinematics that hold whatever the
+    pose -- FK has no reference implementation to pin against (MuJoCo is absent), so besides the float64 oracle the
+    kernel is held to the model file's own numbers (assets/dp_env_v2.xml:20-107)."""
+    from deepmimic_diffusion_mujoco_b200 import scoring
+    N, H = 65536, 64
+    g = torch.Generator(device="cuda").manual_seed(3)
+    q = 0.5 * torch.randn(N, H, 35, device="cuda", generator=g)
+    q[:, :, 3] += 1.0
+    ref = q[0].clone()
+    out = scoring.fk_reward(q, ref, 1 / 60, return_body_pos=True)
+    bp = out["body_pos"]                                  # BODY_DEFS order
+    ROOT, CHEST, NECK, RHIP, RKNEE, RANK, RSHO, RELB, RWR, LHIP, LKNEE, LANK, LSHO, LELB, LWR = range(15)
+    assert torch.isfinite(bp).all() and torch.equal(bp[:, :, ROOT], q[:, :, 0:3])
+
+    def dist(a, b):
+        return (bp[:, :, a] - bp[:, :, b]).norm(dim=-1)
+    # rigid links between body origins joined by hinges through the child's origin
+    for a, b, length in [(CHEST, ROOT, 0.236151), (NECK, CHEST, 0.223894), (RWR, RELB, 0.258947), (LWR, LELB, 0.258947),
+                         (RSHO, CHEST, (0.02405 ** 2 + 0.18311 ** 2 + 0.2435 ** 2) ** 0.5),
+                         (LSHO, CHEST, (0.02405 ** 2 + 0.18311 ** 2 + 0.2435 ** 2) ** 0.5)]:
+        assert (dist(a, b) - length).abs().max().item() < 5e-6, (a, b)
+    # anchored hinges (elbow 0.028, knee 0.035, hip / ankle 0.02 off the body origin): the origin moves on a circle
+    # about the anchor, so the link length stays within the anchor offset of the nominal one
+    for a, b, length, slack in [(RELB, RSHO, 0.274788, 0.056), (RKNEE, RHIP, 0.421546, 0.07), (RANK, RKNEE, 0.40987, 0.04),
+                                (LANK, LKNEE, 0.40987, 0.04)]:
+        assert (dist(a, b) - length).abs().max().item() < slack + 1e-5
+    # rigid motion of the root moves every body rigidly: rotate by a fixed quaternion r and translate
+    r = torch.tensor([0.5, 0.5, -0.5, 0.5], device="cuda")           # unit quaternion (w, x, y, z)
+    def qmul(a, b):
+        aw, ax, ay, az = a.unbind(-1); bw, bx, by, bz = b.unbind(-1)
+        return torch.stack([aw * bw - ax * bx - ay * by - az * bz, aw * bx + ax * bw + ay * bz - az * by,
+                            aw * by - ax * bz + ay * bw + az * bx, aw * bz + ax * by - ay * bx + az * bw], -1)
+    def rot(v):
+        w, x, y, z = r.tolist()
+        R = torch.tensor([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                          [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                          [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]], device="cuda")
+        return v @ R.T
+    sub = q[:2048].clone()
+    qn = sub[:, :, 3:7] / sub[:, :, 3:7].norm(dim=-1, keepdim=True)
+    moved = sub.clone()
+    moved[:, :, 3:7] = qmul(r.expand_as(qn), qn)
+    shift = torch.tensor([0.3, -1.2, 0.7], device="cuda")
+    moved[:, :, 0:3] = rot(sub[:, :, 0:3]) + shift
+    bp2 = scoring.fk_reward(moved, ref, 1 / 60, return_body_pos=True)["body_pos"]
+    assert (bp2 - (rot(bp[:2048]) + shift)).abs().max().item() < 2e-5
+    # reward: a perfect tracker scores 1 on every frame; rewards lie in (0, 1]
+    assert (out["reward"][0] - 1.0).abs().max().item() < 1e-5
+    assert out["reward"].min().item() > 0 and out["reward"].max().item() <= 1.0 + 1e-6
+    assert out["sums"][6].item() == N * H
