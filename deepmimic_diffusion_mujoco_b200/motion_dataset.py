@@ -76,11 +76,17 @@ def load_mocap_frames(path):
 class MotionDataset(torch.utils.data.Dataset):
     """motion_dataset.py:12-56: every cyclic shift of the clip (truncated to a multiple of 8 frames)."""
 
-    def __init__(self, motion_src_path):
-        cfg = mocap_to_qpos(load_mocap_frames(motion_src_path))
-        self.dt = float(load_mocap_frames(motion_src_path)[0, 0])
-        n = cfg.shape[0] - cfg.shape[0] % 8            # temporal unet needs a multiple of 8 (motion_dataset.py:26-28)
-        cfg = torch.from_numpy(cfg[:n]).float()
+    def __init__(self, motion_src_path, device=None):
+        """device=None: host tensors like the reference.  device='cuda': the JSON is parsed on the host (it is text),
+        the frame conversion and the [n, n, 35] tensor of cyclic shifts are built by CUDA kernels (dm_mocap_to_qpos,
+        dm_motion_dataset) and stay on the device, ready to be passed as starting_motion / conditioning values."""
+        frames = load_mocap_frames(motion_src_path)
+        self.dt = float(frames[0, 0])
+        n = frames.shape[0] - frames.shape[0] % 8      # temporal unet needs a multiple of 8 (motion_dataset.py:26-28)
+        if device is not None and torch.device(device).type == "cuda":
+            self.motion_data = mocap_dataset_on_device(frames[:n], torch.device(device))
+            return
+        cfg = torch.from_numpy(mocap_to_qpos(frames)[:n]).float()
         idx = (torch.arange(n)[:, None] + torch.arange(n)[None, :]) % n
         self.motion_data = cfg[idx]                    # [n, n, 35]: row i = cat(cfg[i:], cfg[:i])
 
@@ -93,6 +99,27 @@ class MotionDataset(torch.utils.data.Dataset):
 
     def get_conditions(self, data_configs):
         return {0: data_configs[0]}
+
+
+def mocap_qpos_on_device(frames, device):
+    """[F, 44] DeepMimic frames (host array) -> qpos fp32 [F, 35] on `device`, computed by dm_mocap_to_qpos."""
+    from . import _lib
+    fr = torch.as_tensor(np.ascontiguousarray(frames, dtype=np.float64)).to(device)
+    out = torch.empty(fr.shape[0], 35, device=device, dtype=torch.float32)
+    with torch.cuda.device(device):
+        _lib.check(_lib.lib().dm_mocap_to_qpos(fr.data_ptr(), fr.shape[0], out.data_ptr(), _lib.stream_ptr()))
+    return out
+
+
+def mocap_dataset_on_device(frames, device):
+    """All cyclic shifts of the clip, fp32 [n, n, 35] on `device` (dm_mocap_to_qpos + dm_motion_dataset)."""
+    from . import _lib
+    q = mocap_qpos_on_device(frames, device)
+    n = q.shape[0]
+    out = torch.empty(n, n, 35, device=device, dtype=torch.float32)
+    with torch.cuda.device(device):
+        _lib.check(_lib.lib().dm_motion_dataset(q.data_ptr(), n, out.data_ptr(), _lib.stream_ptr()))
+    return out
 
 
 def tile_clip(clip, horizon):

@@ -113,6 +113,12 @@ int dm_fid_moments(const float* X_dev, int N, int D, double* sum_dev, double* sx
 int dm_window_moments(const float* X_dev, int N, int H, int F, int window, int step, float* mu_dev, float* sigma_dev,
                       dm_stream_t stream);
 
+/* On-device mocap loader (utils/mocap_v2.py:105-291 + utils/mocap_util.py:31-48): DeepMimic frames, host-parsed JSON
+ * "Frames" as double [F,44] on the device -> qpos rows fp32 [F,35] (float64 arithmetic, cast like motion_dataset.py:38). */
+int dm_mocap_to_qpos(const double* frames_dev, int F, float* qpos_dev, dm_stream_t stream);
+/* MotionDataset tensor (data_loaders/motion_dataset.py:31-42): out_dev fp32 [n,n,35], row i = the clip rolled by i frames. */
+int dm_motion_dataset(const float* qpos_dev, int n, float* out_dev, dm_stream_t stream);
+
 /* Test / debug introspection: the activation written by each layer launch, unpacked to fp32 [B,C,L]. */
 int dm_plan_num_layers(const dm_plan_t* plan);
 int dm_plan_layer_info(const dm_plan_t* plan, int i, char* name, int name_cap, int* C, int* L);

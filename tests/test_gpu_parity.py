@@ -514,3 +514,26 @@ def test_fk_invariants_at_full_size(dm):
     assert (out["reward"][0] - 1.0).abs().max().item() < 1e-5
     assert out["reward"].min().item() > 0 and out["reward"].max().item() <= 1.0 + 1e-6
     assert out["sums"][6].item() == N * H
+
+
+def test_on_device_loader_matches_oracle(dm, golden_dir, tmp_path):
+    """dm_mocap_to_qpos / dm_motion_dataset vs the loader oracle on the three committed clips (fp32 cast of the
+    float64 conversion: at most one fp32 ulp apart where the device's atan2 rounds the last double bit differently)."""
+    import json
+    from deepmimic_diffusion_mujoco_b200 import motion_dataset as MD
+    from oracle import loader_oracle as LO
+    z = np.load(os.path.join(golden_dir, "mocap_clips.npz"))
+    for name in ["walk", "cartwheel", "spinkick"]:
+        frames = z[name + "_frames"]
+        got = MD.mocap_qpos_on_device(frames, torch.device("cuda")).cpu().numpy()
+        want = z[name + "_config"].astype(np.float32)
+        assert got.shape == want.shape
+        assert np.abs(got - want).max() <= 2.4e-7 * max(1.0, np.abs(want).max())
+        path = tmp_path / f"humanoid3d_{name}.txt"
+        path.write_text(json.dumps({"Loop": "wrap", "Frames": frames.tolist()}))
+        ds = MD.MotionDataset(str(path), device="cuda")
+        ref = LO.motion_dataset(frames)
+        assert ds.motion_data.is_cuda and tuple(ds.motion_data.shape) == ref.shape
+        assert np.abs(ds.motion_data.cpu().numpy() - ref).max() <= 2.4e-7 * max(1.0, np.abs(ref).max())
+        b = ds[3]
+        assert torch.equal(b.conditions[0], b.trajectories[0]) and torch.equal(ds[0].trajectories[3], b.trajectories[0])
