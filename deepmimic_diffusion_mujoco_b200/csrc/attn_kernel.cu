@@ -29,7 +29,7 @@ __host__ __device__ __forceinline__ int row_pitch(int L) { return (L & 3) ? (L |
 // kVec: L is a multiple of 4 -> rows are 16-byte aligned (pitch L + 4) and the two 1x1 convs run on 4 x 4 register
 // tiles fed by one 16-byte weight load and one 16-byte activation load per 16 FMAs.
 template <bool kVec>
-__global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const AttnParams p) {
+__global__ void __launch_bounds__(kAttnThreads, 2) linear_attention_kernel(const AttnParams p) {
   extern __shared__ __align__(16) float sm[];
   const int C = p.C, L = p.L, NS = p.NS;
   const int Lp = row_pitch(L);
@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
   float* xn = xs + NS * C * Lp;               // [NS][C][Lp]  normalised input
   float* qkv = xn + NS * C * Lp;              // [NS][96][Lp] q | k (later o) | v of the current head
   float* ctx = qkv + NS * 96 * Lp;            // [NS][32][33]
-  float* wsm = ctx + NS * 32 * 33 + ((NS * 32 * 33) & 3 ? 4 - ((NS * 32 * 33) & 3) : 0);   // [32][96] weight chunk (16-byte aligned)
+  float* wsm = ctx + NS * 32 * 33 + ((NS * 32 * 33) & 3 ? 4 - ((NS * 32 * 33) & 3) : 0);   // [2][32][96] weight chunks (16-byte aligned, double-buffered)
   const int tid = threadIdx.x;
   const int per_group = kGroupSamples / NS;
   const int g = blockIdx.x / per_group;
@@ -85,17 +85,33 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
         for (int a = 0; a < 4; ++a)
 #pragma unroll
           for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
-        for (int cb = 0; cb < C; cb += 32) {
-          __syncthreads();
-          for (int j = tid; j < 32 * 96; j += kAttnThreads) {
+        // double-buffered cp.async staging: chunk cb + 32 is in flight while chunk cb is consumed
+        auto stage = [&](int cb, float* dst) {
+#pragma unroll
+          for (int k = 0; k < (32 * 96) / kAttnThreads; ++k) {
+            const int j = tid + k * kAttnThreads;
             const int cc = j / 96, r = j - cc * 96;
-            wsm[j] = __ldg(p.wqkv_t + (size_t)(cb + cc) * OW + (r >> 5) * (p.heads * 32) + h * 32 + (r & 31));
+            const float* src = p.wqkv_t + (size_t)(cb + cc) * OW + (r >> 5) * (p.heads * 32) + h * 32 + (r & 31);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + j)), "l"(src) : "memory");
+          }
+          asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        __syncthreads();            // both buffers free (previous round / head fully consumed)
+        stage(0, wsm);
+        int buf = 0;
+        for (int cb = 0; cb < C; cb += 32, buf ^= 1) {
+          const float* wcur = wsm + buf * (32 * 96);
+          if (cb + 32 < C) {
+            stage(cb + 32, wsm + (buf ^ 1) * (32 * 96));
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+          } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
           }
           __syncthreads();
           if (live) {
-#pragma unroll 8
+#pragma unroll 4
             for (int cc = 0; cc < 32; ++cc) {
-              const float4 w = *reinterpret_cast<const float4*>(wsm + cc * 96 + o);
+              const float4 w = *reinterpret_cast<const float4*>(wcur + cc * 96 + o);
               const float4 x = *reinterpret_cast<const float4*>(xr + (cb + cc) * Lp);
               const float wv[4] = {w.x, w.y, w.z, w.w}, xv[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
@@ -104,6 +120,7 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
                 for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(wv[a], xv[b], acc[a][b]);
             }
           }
+          __syncthreads();          // chunk consumed before its buffer is refilled two iterations later
         }
         if (live) {
           const float sc = (o >> 5) == 0 ? p.scale : 1.f;
@@ -234,34 +251,63 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
     __syncthreads();
     // ---- xs += W_out[:, head] o  (+ bias once): W_out^T is [heads*32][C] ----
     if (kVec) {
+      // W_out^T rows of this head ([32][C]) are staged through the same double buffer, ec rows (ec * C <= 3072) at a time
       const int n_l4 = L >> 2, n_c4 = C >> 2;
-      for (int i = tid; i < n_c4 * NS * n_l4; i += kAttnThreads) {
-        const int co = (i % n_c4) << 2, s = (i / n_c4) % NS, l0 = (i / (n_c4 * NS)) << 2;
+      const int ec = C <= 96 ? 32 : (C <= 192 ? 16 : (C <= 384 ? 8 : (C <= 768 ? 4 : (C <= 1536 ? 2 : 1))));
+      const int n_items = n_c4 * NS * n_l4;
+      auto stage_o = [&](int e0, float* dst) {
+        for (int j = tid; j < ec * C; j += kAttnThreads) {
+          const float* src = p.wout_t + (size_t)(h * 32 + e0) * C + j;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + j)), "l"(src) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      };
+      for (int i0 = 0; i0 < n_items; i0 += kAttnThreads) {
+        const int i = i0 + tid;
+        const bool live = i < n_items;
+        const int co = (i % n_c4) << 2, s = live ? (i / n_c4) % NS : 0, l0 = live ? (i / (n_c4 * NS)) << 2 : 0;
         float acc[4][4];
 #pragma unroll
         for (int a = 0; a < 4; ++a) {
-          const float b0 = h == 0 ? __ldg(p.bout + co + a) : 0.f;
+          const float b0 = (h == 0 && live) ? __ldg(p.bout + co + a) : 0.f;
 #pragma unroll
           for (int b = 0; b < 4; ++b) acc[a][b] = b0;
         }
         const float* orow = qkv + (s * 96 + 32) * Lp + l0;
-        const float* wr = p.wout_t + (size_t)(h * 32) * C + co;
+        __syncthreads();            // both buffers free
+        stage_o(0, wsm);
+        int buf = 0;
+        for (int e0 = 0; e0 < 32; e0 += ec, buf ^= 1) {
+          const float* wcur = wsm + buf * (32 * 96);
+          if (e0 + ec < 32) {
+            stage_o(e0 + ec, wsm + (buf ^ 1) * (32 * 96));
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+          } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+          }
+          __syncthreads();
+          if (live) {
 #pragma unroll 4
-        for (int e = 0; e < 32; ++e) {
-          const float4 w = __ldg(reinterpret_cast<const float4*>(wr + (size_t)e * C));
-          const float4 x = *reinterpret_cast<const float4*>(orow + e * Lp);
-          const float wv[4] = {w.x, w.y, w.z, w.w}, xv[4] = {x.x, x.y, x.z, x.w};
+            for (int e = 0; e < ec; ++e) {
+              const float4 w = *reinterpret_cast<const float4*>(wcur + e * C + co);
+              const float4 x = *reinterpret_cast<const float4*>(orow + (e0 + e) * Lp);
+              const float wv[4] = {w.x, w.y, w.z, w.w}, xv[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-          for (int a = 0; a < 4; ++a)
+              for (int a = 0; a < 4; ++a)
 #pragma unroll
-            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(wv[a], xv[b], acc[a][b]);
+                for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(wv[a], xv[b], acc[a][b]);
+            }
+          }
+          __syncthreads();
         }
+        if (live) {
 #pragma unroll
-        for (int a = 0; a < 4; ++a) {
-          float4* dst = reinterpret_cast<float4*>(xs + (s * C + co + a) * Lp + l0);
-          float4 v = *dst;
-          v.x += acc[a][0]; v.y += acc[a][1]; v.z += acc[a][2]; v.w += acc[a][3];
-          *dst = v;
+          for (int a = 0; a < 4; ++a) {
+            float4* dst = reinterpret_cast<float4*>(xs + (s * C + co + a) * Lp + l0);
+            float4 v = *dst;
+            v.x += acc[a][0]; v.y += acc[a][1]; v.z += acc[a][2]; v.w += acc[a][3];
+            *dst = v;
+          }
         }
       }
     } else
@@ -298,7 +344,7 @@ __global__ void __launch_bounds__(kAttnThreads) linear_attention_kernel(const At
 
 size_t attention_smem_bytes(int C, int L, int NS) {
   const int Lp = row_pitch(L);
-  return sizeof(float) * ((size_t)2 * NS * C * Lp + (size_t)NS * 96 * Lp + (size_t)NS * 32 * 33 + 4 + 32 * 96);
+  return sizeof(float) * ((size_t)2 * NS * C * Lp + (size_t)NS * 96 * Lp + (size_t)NS * 32 * 33 + 4 + 2 * 32 * 96);
 }
 
 int attention_pick_ns(int C, int L) {
