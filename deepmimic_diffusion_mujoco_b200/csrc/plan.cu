@@ -924,6 +924,9 @@ static int fill_step(dm_plan* P, StepParams* sp, float* x, const float* model_ou
   sp->B = P->B; sp->H = P->H; sp->T = P->T;
   sp->n_elems = (long long)P->B * P->H * P->T;
   if (sp->n_elems % 4) return fail(DM_ERR_ARG, "B*H*T must be a multiple of 4");
+  // Philox counter = index of the float4 inside the GLOBAL [B_total, H, T] tensor: a shard that starts at sample
+  // `sample_offset` draws exactly the noise a single-GPU run would draw for those rows
+  sp->rng_offset = (unsigned long long)P->sample_offset * (unsigned long long)(((long long)P->H * P->T) >> 2);
   return DM_OK;
 }
 
@@ -937,7 +940,7 @@ extern "C" int dm_ddpm_step(dm_plan_t* P, float* x_dev, const float* model_out_d
   int rc = fill_step(P, &sp, x_dev, model_out_dev, noise_dev, seed, t, predict_epsilon, clip_denoised, cond);
   if (rc) return rc;
   sp.rng_stream = (unsigned)t + 1;
-  sp.rng_offset = P->rng_calls++ << 40;
+  sp.rng_offset += P->rng_calls++ << 40;
   DM_CUDA(launch_ddpm_step(sp, static_cast<cudaStream_t>(st)));
   P->last_launches = 1;
   return DM_OK;
@@ -1060,3 +1063,10 @@ extern "C" int dm_plan_set_trace(dm_plan_t* P, unsigned long long* trace_dev, in
 }
 
 extern "C" int dm_plan_last_launch_count(const dm_plan_t* P) { return P ? P->last_launches : 0; }
+
+extern "C" int dm_plan_set_sample_offset(dm_plan_t* P, long long first_sample) {
+  if (!P || first_sample < 0) return fail(DM_ERR_ARG, "bad sample offset");
+  if (((long long)P->H * P->T) % 4) return fail(DM_ERR_ARG, "H*T must be a multiple of 4");
+  P->sample_offset = first_sample;
+  return DM_OK;
+}

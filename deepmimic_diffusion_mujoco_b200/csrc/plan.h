@@ -58,6 +58,7 @@ struct dm_plan {
   std::vector<float> sr, srm1, c1, c2, logvar;
   int last_launches = 0;
   unsigned long long rng_calls = 0;
+  long long sample_offset = 0;     // global index of this plan's sample 0 (multi-GPU shards draw the noise of their global rows)
   unsigned long long* seed_dev = nullptr;
   // persistent sampling-loop kernel arguments
   dm::ConvMaps* maps_dev = nullptr;

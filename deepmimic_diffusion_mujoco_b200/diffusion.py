@@ -100,7 +100,7 @@ class GaussianDiffusion(nn.Module):
     @torch.no_grad()
     def p_sample_loop(self, shape, cond, verbose=True, return_chain=False, sample_fn=default_sample_fn,
                       conditioning_fn=apply_conditioning, starting_motion=None, max_timesteps=None,
-                      fused=True, seed=None, **sample_kwargs):
+                      fused=True, seed=None, sample_offset=0, **sample_kwargs):
         device = self.betas.device
         if device.type != "cuda":
             raise _lib.DmError("GaussianDiffusion.p_sample_loop needs the module on a B200 (no CPU fallback)")
@@ -134,6 +134,8 @@ class GaussianDiffusion(nn.Module):
                 mask, value = mbuf, vbuf
             plan = self.model.plan_for(B, H)
             plan.set_schedule(self._schedule_bufs(), self._schedule_id())
+            # multi-GPU shards: rows [sample_offset, sample_offset + B) of one global batch (same seed on every rank)
+            _lib.check(_lib.lib().dm_plan_set_sample_offset(plan.handle, int(sample_offset)))
             chain = torch.empty(B, timesteps + 1, H, T, device=device) if return_chain else None
             c = _lib.DmCond()
             if mask is not None:

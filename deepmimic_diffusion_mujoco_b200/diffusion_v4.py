@@ -71,7 +71,8 @@ class DiffusionV4:
                 "time_values": torch.arange(1, n + 1, dtype=torch.float32)}
 
     @torch.no_grad()
-    def sample(self, model, n, custom_frames=None, condition=None, y=None, noise=None, return_chain=False, seed=None):
+    def sample(self, model, n, custom_frames=None, condition=None, y=None, noise=None, return_chain=False, seed=None,
+               sample_offset=0):
         """Reverse diffusion of n samples (diffusion_v4.py:82-149).  model: this package's TemporalUnet.
         noise: optional injected stack [noise_steps, n, frames, joint_dim] (slot 0 = the initial draw, slot k = the k-th
         randn_like; the reference zeroes the last one itself).  Returns x [n, frames, joint_dim]."""
@@ -90,6 +91,7 @@ class DiffusionV4:
             plan = model.plan_for(B, H)
             plan.set_schedule(self.step_table(), ("v4", id(self), self.predict_x0, self.schedule_type, self.noise_steps,
                                                   float(self.beta_start), float(self.beta_end)))
+            _lib.check(_lib.lib().dm_plan_set_sample_offset(plan.handle, int(sample_offset)))
             x = torch.empty(B, H, T, device=device, dtype=torch.float32)
             stack = None
             if noise is not None:

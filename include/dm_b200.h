@@ -119,6 +119,10 @@ int dm_mocap_to_qpos(const double* frames_dev, int F, float* qpos_dev, dm_stream
 /* MotionDataset tensor (data_loaders/motion_dataset.py:31-42): out_dev fp32 [n,n,35], row i = the clip rolled by i frames. */
 int dm_motion_dataset(const float* qpos_dev, int n, float* out_dev, dm_stream_t stream);
 
+/* Multi-GPU sharding: global index of this plan's sample 0.  The in-kernel Philox counters are then
+ * those of rows [first_sample, first_sample + B) of one global batch, so N shards reproduce the 1-GPU trajectories. */
+int dm_plan_set_sample_offset(dm_plan_t* plan, long long first_sample);
+
 /* Test / debug introspection: the activation written by each layer launch, unpacked to fp32 [B,C,L]. */
 int dm_plan_num_layers(const dm_plan_t* plan);
 int dm_plan_layer_info(const dm_plan_t* plan, int i, char* name, int name_cap, int* C, int* L);

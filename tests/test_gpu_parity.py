@@ -461,6 +461,11 @@ def test_full_size_properties(dm):
     assert torch.equal(a[:, :, 16], torch.full((1024, H), 1.57, device="cuda"))
     assert torch.equal(a[:, :, 17:20], torch.zeros(1024, H, 3, device="cuda"))
     assert torch.equal(a[:48], small)
+    # a shard that starts at global sample 16 reproduces rows 16..63 of the global batch (same seed on every rank)
+    shard = diff.p_sample_loop((48, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=5, sample_offset=16).trajectories
+    assert torch.equal(a[16:64], shard)
+    again = diff.p_sample_loop((48, H, 35), {}, verbose=False, conditioning_fn=box_holding, seed=5).trajectories
+    assert torch.equal(again, small)          # the offset does not stick to the plan
 
 
 def test_fk_invariants_at_full_size(dm):
