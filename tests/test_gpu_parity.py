@@ -542,3 +542,36 @@ def test_on_device_loader_matches_oracle(dm, golden_dir, tmp_path):
         assert np.abs(ds.motion_data.cpu().numpy() - ref).max() <= 2.4e-7 * max(1.0, np.abs(ref).max())
         b = ds[3]
         assert torch.equal(b.conditions[0], b.trajectories[0]) and torch.equal(ds[0].trajectories[3], b.trajectories[0])
+
+
+def test_scoring_edge_sizes(dm):
+    """Ragged / minimal sizes of the scoring kernels: one frame, one sample, a sample count that crosses the K6 chunk
+    boundary (8192 + 1) and a feature width that is not a multiple of the 128-wide SYRK tile, the minimum of two
+    SiFID windows, an unaligned qpos pointer."""
+    from deepmimic_diffusion_mujoco_b200 import scoring
+    g = np.random.default_rng(11)
+    # FK + reward: N = 1, H = 1 (no previous frame), and H = 3 through an offset (16-byte misaligned) view
+    for N, H in [(1, 1), (3, 3), (2, 129)]:
+        q = 0.3 * g.standard_normal((N + 1, H, 35)); q[:, :, 3] += 1.0
+        ref = q[0]
+        qt = torch.tensor(q, dtype=torch.float32).cuda()[1:]          # storage offset H*35 floats
+        out = scoring.fk_reward(qt, torch.tensor(ref, dtype=torch.float32), 1 / 30, return_body_pos=True)
+        q32 = qt.cpu().double().numpy()
+        r, _ = SO.tracking_reward(q32, torch.tensor(ref, dtype=torch.float32).double().numpy(), 1 / 30)
+        assert np.abs(out["reward"].cpu().numpy() - r).max() < 2e-4
+        assert np.abs(out["body_pos"].cpu().numpy() - SO.body_positions(q32)).max() < 1e-5
+        assert out["sums"][6].item() == N * H
+    # FID moments: N = 1; N = 8193 with D = 200 (two 128-wide tiles, the second one ragged)
+    for N, D in [(1, 70), (8193, 200), (130, 129)]:
+        X = torch.tensor(g.standard_normal((N, D)) * 0.5 + 0.2, dtype=torch.float32)
+        s, sxx = scoring.fid_moments(X.cuda())
+        Xd = X.double()
+        assert torch.allclose(s.cpu(), Xd.sum(0), rtol=1e-6, atol=1e-4)
+        assert torch.allclose(sxx.cpu(), Xd.T @ Xd, rtol=2e-5, atol=2e-3)
+        assert torch.allclose(sxx, sxx.T, rtol=1e-6, atol=1e-4)
+    # SiFID statistics: exactly two windows
+    x = torch.tensor(g.standard_normal((3, 20, 35)), dtype=torch.float32)
+    mu, sig = scoring.window_moments(x.cuda(), 10)
+    for i in range(3):
+        mo, so = SO.activation_statistics(SO.slice_windows(x[i].numpy(), 10))
+        assert np.abs(mu[i].cpu().numpy() - mo).max() < 1e-5 and np.abs(sig[i].cpu().numpy() - so).max() < 1e-5
