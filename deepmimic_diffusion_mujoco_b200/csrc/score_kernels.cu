@@ -73,7 +73,7 @@ fk_reward_kernel(const float* __restrict__ qpos, const float* __restrict__ feat,
     __syncthreads();
     if ((int)threadIdx.x < nf) {
       const long long fi = f0 + threadIdx.x;
-      const int h = (int)(fi % H);
+      const int h = (int)(((unsigned)(f0 % H) + threadIdx.x) % (unsigned)H);   // one 64-bit modulo per tile (uniform), 32-bit per thread
       const float* q = sq + threadIdx.x * 35;
       const float* qp = h == 0 ? q : (threadIdx.x == 0 ? sprev : q - 35);
       const float* g = (kFeatSmem ? sfeat : feat) + (size_t)h * fk::kFeatStride;
