@@ -21,7 +21,7 @@ typedef void* dm_stream_t; /* cudaStream_t */
 
 enum dm_status {
   DM_OK = 0,
-  DM_ERR_ARG = -1,     /* bad argument / unsupported shape (e.g. H % 8 != 0, H > 256, attention=True) */
+  DM_ERR_ARG = -1,     /* bad argument / unsupported shape (e.g. H % 8 != 0, an attention tile beyond shared memory) */
   DM_ERR_DEVICE = -2,  /* no CUDA device, or device is not sm_100 */
   DM_ERR_CUDA = -3,    /* a CUDA runtime / driver call failed */
   DM_ERR_WEIGHT = -4,  /* a state_dict tensor is missing or has the wrong shape */
