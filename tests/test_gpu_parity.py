@@ -148,6 +148,27 @@ def test_attention_unet_layers_match_oracle(dm, B, H):
     assert rel(y, y_ref) < 1e-4
 
 
+def test_wide_attention_unet_matches_oracle(dm):
+    """dim=128 with attention=True: 128..1024-channel attention stages (weight chunks of 16 down to 2 rows)."""
+    B, H, T, dim = 2, 32, 35, 128
+    sd = O.seeded_state_dict(H=H, T=T, dim=dim, seed=9, attention=True)
+    net = dm.TemporalUnet(H, T, T, dim=dim, attention=True)
+    net.load_state_dict(sd)
+    g = torch.Generator().manual_seed(77)
+    x = torch.randn(B, H, T, generator=g)
+    t = torch.randint(0, 100, (B,), generator=g)
+    rec = {}
+    y_ref = O.unet_forward(sd, x, t, dim=dim, record=rec)
+    y = net(x.cuda(), {}, t.cuda()).cpu()
+    plan = net.plan_for(B, H)
+    for i, (name, C, L) in enumerate(plan.layer_names()):
+        if C == 0:
+            continue
+        got = plan.read_layer(i, C, L).cpu()
+        assert rel(got, rec[name]) < 1e-4, (name, rel(got, rec[name]))
+    assert rel(y, y_ref) < 1e-4
+
+
 def test_attention_chain_matches_reference_fixture(dm, golden_dir):
     """p_sample_loop of the attention=True model against the chain recorded from the UNMODIFIED reference."""
     z = np.load(os.path.join(golden_dir, "unet_chain_attention.npz"))
