@@ -349,7 +349,7 @@ size_t attention_smem_bytes(int C, int L, int NS) {
 
 int attention_pick_ns(int C, int L) {
   for (int ns = 4; ns >= 1; ns >>= 1)
-    if (attention_smem_bytes(C, L, ns) <= 200 * 1024) return ns;
+    if (attention_smem_bytes(C, L, ns) <= 224 * 1024) return ns;
   return 0;
 }
 
