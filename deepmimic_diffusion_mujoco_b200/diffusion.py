@@ -53,6 +53,21 @@ def make_timesteps(batch_size, i, device):
     return torch.full((batch_size,), i, device=device, dtype=torch.long)
 
 
+class _LossWeights(nn.Module):
+    """State holder for the reference's loss module (helpers.py:163-167 WeightedLoss; :182-185 ValueLoss has no
+    state).  Training is out of scope, but Trainer.save (utils/training.py:133-137) stores the GaussianDiffusion
+    state_dict, which carries `loss_fn.weights`: the buffer must exist for those checkpoints to load strictly."""
+
+    def __init__(self, weights, action_dim):
+        super().__init__()
+        if weights is not None:
+            self.register_buffer("weights", weights)
+        self.action_dim = action_dim
+
+    def forward(self, pred, targ):
+        raise NotImplementedError("training losses (helpers.py:169-214) are outside the accelerated hot path")
+
+
 class GaussianDiffusion(nn.Module):
     def __init__(self, model, horizon, transition_dim, n_timesteps=1000, loss_type="l1", clip_denoised=False,
                  predict_epsilon=True, action_weight=1.0, loss_discount=1.0, loss_weights=None):
@@ -84,10 +99,27 @@ class GaussianDiffusion(nn.Module):
         reg("posterior_log_variance_clipped", torch.log(torch.clamp(posterior_variance, min=1e-20)))
         reg("posterior_mean_coef1", betas * np.sqrt(alphas_cumprod_prev) / (1.0 - alphas_cumprod))
         reg("posterior_mean_coef2", (1.0 - alphas_cumprod_prev) * np.sqrt(alphas) / (1.0 - alphas_cumprod))
+        # loss coefficients (diffusion.py:112-145): kept only so that the state_dict matches the reference's
+        lw = self.get_loss_weights(action_weight, loss_discount, loss_weights)
+        if loss_type not in ("l1", "l2", "value_l1", "value_l2"):
+            raise KeyError(loss_type)   # Losses[loss_type] (helpers.py:233-238)
+        self.loss_fn = _LossWeights(lw if loss_type in ("l1", "l2") else None, self.action_dim)
         self.seed = 1234
         self._calls = 0
         self._bufs = {}
         self.last_launch_count = 0
+
+    def get_loss_weights(self, action_weight, discount, weights_dict):
+        """diffusion.py:116-145: discount**t over the horizon (mean-normalised) x per-dimension weights, a0 weight set."""
+        self.action_weight = action_weight
+        dim_weights = torch.ones(self.transition_dim, dtype=torch.float32)
+        for ind, w in (weights_dict or {}).items():
+            dim_weights[self.action_dim + ind] *= w
+        discounts = discount ** torch.arange(self.horizon, dtype=torch.float)
+        discounts = discounts / discounts.mean()
+        loss_weights = torch.einsum("h,t->ht", discounts, dim_weights)
+        loss_weights[0, : self.action_dim] = action_weight
+        return loss_weights
 
     def _schedule_bufs(self):
         return {k: getattr(self, k) for k in ("sqrt_recip_alphas_cumprod", "sqrt_recipm1_alphas_cumprod",

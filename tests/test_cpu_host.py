@@ -125,3 +125,27 @@ def test_attention_state_dict_matches_reference_keys():
     assert tuple(mine["downs.0.2.fn.norm.g"].shape) == (1, 32, 1)
     with pytest.raises(dm.DmError):                      # still no CPU path
         net(torch.zeros(1, 64, 35), {}, torch.zeros(1))
+
+
+@pytest.mark.parametrize("case", ["default_h64", "attention_h32_l2", "wide_t69_dim128"])
+def test_reference_checkpoint_state_dict_loads_strictly(case):
+    """Trainer.save stores GaussianDiffusion.state_dict() under 'model' / 'ema' (utils/training.py:133-137): `model.`
+    prefixed U-Net tensors, the schedule buffers and loss_fn.weights.  The fixture lists the keys / shapes / dtypes of
+    the UNMODIFIED reference module (tests/golden/make_state_dict_golden.py); a checkpoint with exactly those entries
+    must load with strict=True, and a bare U-Net state_dict is its `model.`-prefixed slice."""
+    import json
+    fx = json.load(open(os.path.join(ROOT, "tests", "golden", "state_dict_reference.json")))[case]
+    net = dm.TemporalUnet(**fx["unet"])
+    diff = dm.GaussianDiffusion(net, fx["unet"]["horizon"], fx["unet"]["transition_dim"], **fx["diffusion"])
+    mine = diff.state_dict()
+    assert list(mine) == list(fx["keys"])                       # same keys, same order
+    for k, (shape, dtype) in fx["keys"].items():
+        assert list(mine[k].shape) == shape and str(mine[k].dtype) == dtype, k
+    assert torch.allclose(mine["loss_fn.weights"], torch.tensor(fx["loss_fn.weights"]), rtol=0, atol=0)
+    g = torch.Generator().manual_seed(3)
+    ckpt = {"step": 7, "model": {k: torch.randn(shape, generator=g).to(getattr(torch, dtype.split(".")[1]))
+                                 for k, (shape, dtype) in fx["keys"].items()}}
+    diff.load_state_dict(ckpt["model"])                          # strict
+    assert torch.equal(diff.state_dict()["model.final_conv.1.weight"], ckpt["model"]["model.final_conv.1.weight"])
+    unet_sd = {k[len("model."):]: v for k, v in ckpt["model"].items() if k.startswith("model.")}
+    dm.TemporalUnet(**fx["unet"]).load_state_dict(unet_sd)       # strict

@@ -1,11 +1,11 @@
 """Developer A/B (GPU box): time the fused sampling loop for several builds of libdm_b200.so in ONE gpurun call,
-interleaved, so box-to-box clock variance cancels.  usage: python tests/ab_bench.py libA.so libB.so [B] [H] [reps]"""
+interleaved, so box-to-box clock variance cancels.  usage: python tools/ab_bench.py libA.so libB.so [B] [H] [reps]"""
 import os, subprocess, sys, json
 if len(sys.argv) > 1 and sys.argv[1] == "--one":
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     import torch
     import deepmimic_diffusion_mujoco_b200 as dm
-    from oracle import diffusion_oracle as O
+    from deepmimic_diffusion_mujoco_b200 import synthetic as O
     B, H, reps = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
     net = dm.TemporalUnet(H, 35, 35)
     net.load_state_dict(O.seeded_state_dict(H=H, seed=0))

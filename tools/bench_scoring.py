@@ -6,7 +6,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import deepmimic_diffusion_mujoco_b200 as dm
 from deepmimic_diffusion_mujoco_b200 import _lib, scoring
-from oracle import diffusion_oracle as O
+from deepmimic_diffusion_mujoco_b200 import synthetic as O
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 H, T = 64, 35

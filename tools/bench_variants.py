@@ -4,7 +4,7 @@ import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import deepmimic_diffusion_mujoco_b200 as dm
-from oracle import diffusion_oracle as O
+from deepmimic_diffusion_mujoco_b200 import synthetic as O
 
 
 def box(x):

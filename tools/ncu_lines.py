@@ -1,5 +1,5 @@
 """Aggregate an ncu report's warp-stall samples by CUDA source line (reads the .ncu-rep with the ncu CLI).
-usage: python tests/ncu_lines.py gpurun_out/prof.ncu-rep [top_n]"""
+usage: python tools/ncu_lines.py gpurun_out/prof.ncu-rep [top_n]"""
 import csv, subprocess, sys, io
 rep = sys.argv[1]; top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"],

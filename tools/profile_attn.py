@@ -3,7 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import deepmimic_diffusion_mujoco_b200 as dm
-from oracle import diffusion_oracle as O
+from deepmimic_diffusion_mujoco_b200 import synthetic as O
 B, H = 1024, 64
 net = dm.TemporalUnet(H, 35, 35, attention=True)
 net.load_state_dict(O.seeded_state_dict(H=H, seed=0, attention=True))

@@ -3,7 +3,7 @@
 moments) and the packed statistics are all-reduced over NCCL -- the path's only collective.  Rank 0 then repeats the
 job alone on the first 2 shards' rows and checks that the trajectories are bit-identical and the statistics agree
 (1-GPU == N-GPU).  Prints one JSON line.
-usage: torchrun --nproc-per-node N tests/run_config5_multi.py [samples_total] [ddpm_steps]"""
+usage: torchrun --nproc-per-node N tools/run_config5_multi.py [samples_total] [ddpm_steps]"""
 import json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -12,7 +12,7 @@ import torch
 import torch.distributed as dist
 import deepmimic_diffusion_mujoco_b200 as dm
 from deepmimic_diffusion_mujoco_b200 import scoring, motion_dataset as MD
-from oracle import diffusion_oracle as O
+from deepmimic_diffusion_mujoco_b200 import synthetic as O
 
 total = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 100

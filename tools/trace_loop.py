@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import deepmimic_diffusion_mujoco_b200 as dm
 from deepmimic_diffusion_mujoco_b200 import _lib
-from oracle import diffusion_oracle as O
+from deepmimic_diffusion_mujoco_b200 import synthetic as O
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 H = int(sys.argv[2]) if len(sys.argv) > 2 else 64
