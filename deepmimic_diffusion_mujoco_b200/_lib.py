@@ -36,7 +36,7 @@ class DmSchedule(ctypes.Structure):
 
 class DmCond(ctypes.Structure):
     _fields_ = [("mask_dev", ctypes.c_void_p), ("value_dev", ctypes.c_void_p), ("mask_batched", ctypes.c_int),
-                ("value_batched", ctypes.c_int)]
+                ("value_batched", ctypes.c_int), ("flags_dev", ctypes.c_void_p)]
 
 
 def build(verbose=False):

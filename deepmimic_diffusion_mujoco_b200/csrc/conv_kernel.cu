@@ -25,6 +25,8 @@
 #include "ptx.cuh"
 #include "step_device.cuh"
 
+#include <mutex>
+
 namespace dm {
 
 __device__ __forceinline__ float mish_f(float x) {
@@ -40,6 +42,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kMaxDynSmem = 201 * 1024;   // dynamic shared memory opt-in of both kernels (plan.cu budgets 200 KB + alignment slack)
 constexpr int kPollWarp = 2;   // epilogue warp that waits on the accumulator mbarrier (SMSP 2: neither TMA nor MMA warp)
 
 // Optional phase trace (debug): tr points at kTraceSlots slots of this (job, unit); null in production.
@@ -860,28 +863,35 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device (context): done once for each device this process
+// launches on, under a lock (host threads may drive different GPUs).
+static cudaError_t ensure_smem_attr() {
+  static std::mutex mu;
+  static bool done[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lock(mu);
+  if (dev >= 0 && dev < 64 && done[dev]) return cudaSuccess;
+  e = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(sample_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(sample_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev] = true;
+  return e;
+}
+
 cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes,
                             cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  cudaError_t e = ensure_smem_attr();
+  if (e != cudaSuccess) return e;
   dim3 grid(n_groups * (kGroupSamples / job.S), n_slices);
   conv_gemm_kernel<<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
   return cudaGetLastError();
 }
 
 cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(sample_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(sample_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  cudaError_t e = ensure_smem_attr();
+  if (e != cudaSuccess) return e;
   if (lp.trace) sample_loop_kernel<true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
   else sample_loop_kernel<false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
   return cudaGetLastError();

@@ -187,8 +187,6 @@ __global__ void __launch_bounds__(256) fid_reduce_kernel(const float* __restrict
 
 using namespace dm;
 
-int dm_fid_moments_simt(const float* X_dev, int N, int D, double* sum_dev, double* sxx_dev, dm_stream_t st);
-
 static cudaMemPool_t fid_pool(int dev) {
   // library-owned stream-ordered pool that never trims (the default pool frees at every synchronisation)
   static cudaMemPool_t pools[64] = {};
@@ -210,7 +208,6 @@ extern "C" int dm_fid_moments(const float* X_dev, int N, int D, double* sum_dev,
   if (N < 1 || D < 1) return fail(DM_ERR_ARG, "need N >= 1, D >= 1");
   int rc = check_device();
   if (rc) return rc;
-  if (getenv("DM_B200_FID_SIMT")) return dm_fid_moments_simt(X_dev, N, D, sum_dev, sxx_dev, st);   // A/B aid
   cudaStream_t s = static_cast<cudaStream_t>(st);
   int dev = 0;
   cudaGetDevice(&dev);

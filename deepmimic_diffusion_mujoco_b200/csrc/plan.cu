@@ -3,6 +3,7 @@
 #include "plan.h"
 
 #include <math.h>
+#include <algorithm>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -42,6 +43,17 @@ int check_device() {
   DM_CUDA(cudaGetDevice(&dev));
   DM_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
   if (major != 10) return fail(DM_ERR_DEVICE, "device compute capability %d.x is not sm_100 (B200)", major);
+  return DM_OK;
+}
+
+// Every entry point that takes a plan runs on the plan's device: a different current device would launch kernels on
+// a GPU that holds none of the plan's memory.
+int check_plan_device(const dm_plan* P) {
+  int dev = -1;
+  DM_CUDA(cudaGetDevice(&dev));
+  if (dev != P->device)
+    return fail(DM_ERR_STATE, "plan was created on device %d but the current device is %d (use cudaSetDevice / "
+                              "torch.cuda.device)", P->device, dev);
   return DM_OK;
 }
 
@@ -112,7 +124,6 @@ static int find_w(const WeightMap& W, const std::string& name, std::vector<int64
 // Weight loads of `nx`'s first channel chunk that may be issued while `cur`'s epilogue runs: ring slots of nx
 // that lie beyond cur's staged output tile (cur's operand stages are dead by then).
 static int prefetchable_w_loads(const ConvJob& cur, const ConvJob& nx) {
-  if (getenv("DM_B200_NO_WPREFETCH")) return 0;
   int cur_st = cur.st_cw ? 2 * cur.st_nq * cur.st_blk_stride : 0;
   if (cur.f32_stride && cur.S * cur.f32_stride * 4 > cur_st) cur_st = cur.S * cur.f32_stride * 4;
   const int w_off = nx.a_res ? nx.w_off_res : nx.n_a_stages * nx.a_stage_bytes;
@@ -236,7 +247,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   // two MMA issuer warps with one accumulator set each (conv_kernel.cu, mma_unit) when TMEM has room for it
   j.acc2 = 0;
   j.acc2_off = 0;
-  if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_all * Nc <= 512 && !getenv("DM_B200_SINGLE_ISSUER")) {
+  if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_all * Nc <= 512) {
     j.acc2 = 1;
     j.acc2_off = j.nphase * mt_all * Nc;
     acc_sets += j.nphase;
@@ -356,8 +367,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     j.out_f32 = P->model_out;
     j.out_f32_C = sp.Cout;
     const int per_sample = Lout * sp.Cout;
-    if (per_sample % 4 == 0 && ly.slices == 1 && (size_t)j.S * (per_sample + 4) * 4 <= (size_t)budget &&
-        !getenv("DM_B200_NO_F32STAGE")) {
+    if (per_sample % 4 == 0 && ly.slices == 1 && (size_t)j.S * (per_sample + 4) * 4 <= (size_t)budget) {
       j.f32_stride = per_sample + 4;
       const size_t need = (size_t)j.S * j.f32_stride * 4 + 1024;
       if (ly.smem < need) ly.smem = need;
@@ -452,7 +462,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   }
   j.mma_mode = j.acc2;   // 1: both issuer warps share every tap (conv_kernel.cu, mma_unit)
   // ---- resident link: read the previous layer's staged tile in place (fused loop only) ----
-  if (!P->layers.empty() && !getenv("DM_B200_NO_RESIDENT")) {
+  if (!P->layers.empty()) {
     Layer& pv = P->layers.back();
     const ConvJob& pj = pv.job;
     const int halo_hi_rows = (j.box_l - j.halo_lo - Lin) * j.S;
@@ -508,7 +518,7 @@ static int add_resblock(dm_plan* P, const WeightMap& W, const std::string& key, 
   c0.Cout = Cout;
   c0.tb_off = *tb_cursor;
   bool fused_res = false;
-  if (cin_real != Cout && !getenv("DM_B200_NO_AUXFUSE")) {
+  if (cin_real != Cout) {
     c0.aux_wkey = key + ".residual_conv";
     const size_t n_alloc = P->allocs.size(), n_acts = P->acts.size();
     rc = add_conv(P, W, c0, &mid, &res);
@@ -734,8 +744,7 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if ((rc = add_conv(P, W, f1, &o2))) return rc;
   }
   P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, P->layers.front().job);
-  if (!getenv("DM_B200_NO_LOCALSYNC"))
-    for (size_t i = 0; i + 1 < P->layers.size(); ++i)
+  for (size_t i = 0; i + 1 < P->layers.size(); ++i)
       P->layers[i].job.sync_local = P->layers[i].job.S == 8 && P->layers[i + 1].job.S == 8;
   if (tb != P->TB) return fail(DM_ERR_ARG, "internal: time-bias layout mismatch (%d vs %d)", tb, P->TB);
 
@@ -792,13 +801,15 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
     j.sync_local = 0;
     DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));
     P->last_launches++;
-    if (getenv("DM_B200_DEBUG_SYNC")) {   // debugging aid: find the layer whose kernel faults
+#ifdef DM_DEV_DEBUG
+    {   // debugging aid (compile with -DDM_DEV_DEBUG): find the layer whose kernel faults
       const cudaError_t e = cudaStreamSynchronize(s);
       fprintf(stderr, "[dm debug] %-28s mode %d S %d Mt %d ltiles %d Nc %d slices %d chunks %d+%d taps %d aux %d : %s\n", ly.name.c_str(),
               j.mma_mode, j.S, j.Mt, j.n_ltiles, j.Nc, j.slices, j.src_chunks[0], j.nsrc > 1 ? j.src_chunks[1] : 0, j.ntaps, j.aux,
               cudaGetErrorString(e));
       if (e != cudaSuccess) return fail(DM_ERR_CUDA, "layer %s failed", ly.name.c_str());
     }
+#endif
   }
   return DM_OK;
 }
@@ -859,30 +870,81 @@ extern "C" void dm_plan_free(dm_plan_t* P) {
   delete P;
 }
 
+static unsigned long long fnv1a(unsigned long long h, const void* data, size_t bytes) {
+  const unsigned char* p = static_cast<const unsigned char*>(data);
+  for (size_t i = 0; i < bytes; ++i) { h ^= p[i]; h *= 1099511628211ull; }
+  return h;
+}
+
+static void free_tracked(dm_plan* P, void* p) {
+  if (!p) return;
+  for (size_t i = 0; i < P->allocs.size(); ++i)
+    if (P->allocs[i] == p) { P->allocs.erase(P->allocs.begin() + i); break; }
+  cudaFree(p);
+}
+
 extern "C" int dm_plan_set_schedule(dm_plan_t* P, const dm_schedule_t* s) {
   if (!P || !s || s->n_timesteps < 1) return fail(DM_ERR_ARG, "bad schedule");
+  int rc = check_plan_device(P);
+  if (rc) return rc;
   const int n = s->n_timesteps;
-  P->sr.assign(s->sqrt_recip_alphas_cumprod, s->sqrt_recip_alphas_cumprod + n);
-  P->srm1.assign(s->sqrt_recipm1_alphas_cumprod, s->sqrt_recipm1_alphas_cumprod + n);
-  P->c1.assign(s->posterior_mean_coef1, s->posterior_mean_coef1 + n);
-  P->c2.assign(s->posterior_mean_coef2, s->posterior_mean_coef2 + n);
-  P->logvar.assign(s->posterior_log_variance_clipped, s->posterior_log_variance_clipped + n);
-  P->n_timesteps = n;
   std::vector<float> tv(n);
   for (int i = 0; i < n; ++i) tv[i] = s->time_values ? s->time_values[i] : (float)i;
-  int rc;
-  if ((rc = upload(P, tv, &P->t_table))) return rc;
-  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->tb_table), (size_t)n * P->TB * sizeof(float)))) return rc;
-  if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->steps_dev), (size_t)(n + 1) * sizeof(StepParams)))) return rc;
-  if (P->steps_host) cudaFreeHost(P->steps_host);
-  DM_CUDA(cudaMallocHost(reinterpret_cast<void**>(&P->steps_host), (size_t)(n + 1) * sizeof(StepParams)));
-  DM_CUDA(launch_time_bias(P->tmlp, P->t_table, n, P->tb_table, 0));
-  DM_CUDA(cudaDeviceSynchronize());
+  unsigned long long h = fnv1a(14695981039346656037ull, &n, sizeof(n));
+  const float* arrs[5] = {s->sqrt_recip_alphas_cumprod, s->sqrt_recipm1_alphas_cumprod, s->posterior_mean_coef1,
+                          s->posterior_mean_coef2, s->posterior_log_variance_clipped};
+  for (const float* a : arrs) h = fnv1a(h, a, (size_t)n * sizeof(float));
+  h = fnv1a(h, tv.data(), (size_t)n * sizeof(float));
+  // step table staging sized for the longest schedule seen (one denoising step per entry + the init entry)
+  if (n + 1 > P->steps_capacity) {
+    if (P->steps_pending) { DM_CUDA(cudaEventSynchronize(P->steps_event)); P->steps_pending = false; }
+    DM_CUDA(cudaDeviceSynchronize());   // a running loop kernel may still read the old table
+    free_tracked(P, P->steps_dev);
+    P->steps_dev = nullptr;
+    if (P->steps_host) { cudaFreeHost(P->steps_host); P->steps_host = nullptr; }
+    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->steps_dev), (size_t)(n + 1) * sizeof(StepParams)))) return rc;
+    DM_CUDA(cudaMallocHost(reinterpret_cast<void**>(&P->steps_host), (size_t)(n + 1) * sizeof(StepParams)));
+    P->steps_capacity = n + 1;
+  }
+  ScheduleTables* hit = nullptr;
+  for (size_t i = 0; i < P->schedules.size(); ++i)
+    if (P->schedules[i].hash == h && P->schedules[i].n == n) {
+      std::rotate(P->schedules.begin(), P->schedules.begin() + i, P->schedules.begin() + i + 1);   // most recent first
+      hit = &P->schedules.front();
+      break;
+    }
+  if (!hit) {
+    ScheduleTables e;
+    if (P->schedules.size() >= 4) {   // recycle the least recently used entry (nothing on the device may still read it)
+      DM_CUDA(cudaDeviceSynchronize());
+      free_tracked(P, P->schedules.back().t_table);
+      free_tracked(P, P->schedules.back().tb_table);
+      P->schedules.pop_back();
+    }
+    e.hash = h;
+    e.n = n;
+    e.sr.assign(arrs[0], arrs[0] + n);
+    e.srm1.assign(arrs[1], arrs[1] + n);
+    e.c1.assign(arrs[2], arrs[2] + n);
+    e.c2.assign(arrs[3], arrs[3] + n);
+    e.logvar.assign(arrs[4], arrs[4] + n);
+    if ((rc = upload(P, tv, &e.t_table))) return rc;
+    if ((rc = dev_alloc(P, reinterpret_cast<void**>(&e.tb_table), (size_t)n * P->TB * sizeof(float)))) return rc;
+    DM_CUDA(launch_time_bias(P->tmlp, e.t_table, n, e.tb_table, 0));   // legacy stream: ordered before later work
+    DM_CUDA(cudaStreamSynchronize(0));
+    P->schedules.insert(P->schedules.begin(), std::move(e));
+    hit = &P->schedules.front();
+  }
+  P->sr = hit->sr; P->srm1 = hit->srm1; P->c1 = hit->c1; P->c2 = hit->c2; P->logvar = hit->logvar;
+  P->t_table = hit->t_table;
+  P->tb_table = hit->tb_table;
+  P->n_timesteps = n;
   return DM_OK;
 }
 
 extern "C" int dm_unet_forward(dm_plan_t* P, const float* x_dev, const float* t_dev, float* out_dev, dm_stream_t st) {
   if (!P || !x_dev || !t_dev || !out_dev) return fail(DM_ERR_ARG, "null argument");
+  if (int drc = check_plan_device(P)) return drc;
   cudaStream_t s = static_cast<cudaStream_t>(st);
   P->last_launches = 0;
   const Act& xs = P->acts[P->xs_act];
@@ -917,6 +979,11 @@ static int fill_step(dm_plan* P, StepParams* sp, float* x, const float* model_ou
     sp->value = cond->value_dev;
     sp->mask_bstride = cond->mask_batched ? (long long)P->H * P->T : 0;
     sp->value_bstride = cond->value_batched ? (long long)P->H * P->T : 0;
+    if (cond->flags_dev) {
+      if (!cond->mask_batched || !cond->value_batched)
+        return fail(DM_ERR_ARG, "dm_cond_t::flags_dev needs the full [B,H*T] mask and value tensors");
+      sp->cond_flags = cond->flags_dev;
+    }
   }
   sp->xs = xs.p;
   sp->xs_plane_stride = xs.plane;
@@ -936,6 +1003,7 @@ extern "C" int dm_ddpm_step(dm_plan_t* P, float* x_dev, const float* model_out_d
   if (!P || !x_dev || !model_out_dev) return fail(DM_ERR_ARG, "null argument");
   if (P->n_timesteps == 0) return fail(DM_ERR_STATE, "dm_plan_set_schedule has not been called");
   if (t < 0 || t >= P->n_timesteps) return fail(DM_ERR_ARG, "timestep %d out of range", t);
+  if (int drc = check_plan_device(P)) return drc;
   StepParams sp;
   int rc = fill_step(P, &sp, x_dev, model_out_dev, noise_dev, seed, t, predict_epsilon, clip_denoised, cond);
   if (rc) return rc;
@@ -979,6 +1047,7 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   if (!P || !x_dev) return fail(DM_ERR_ARG, "null argument");
   if (P->n_timesteps == 0) return fail(DM_ERR_STATE, "dm_plan_set_schedule has not been called");
   if (timesteps < 0 || timesteps > P->n_timesteps) return fail(DM_ERR_ARG, "timesteps %d out of range", timesteps);
+  if (int drc = check_plan_device(P)) return drc;
   cudaStream_t s = static_cast<cudaStream_t>(st);
   P->last_launches = 0;
   if (P->steps_pending) { DM_CUDA(cudaEventSynchronize(P->steps_event)); P->steps_pending = false; }
@@ -1008,10 +1077,15 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
     sp[k].chain = chain_dev; sp[k].chain_len = timesteps + 1; sp[k].chain_slot = k;
   }
   DM_CUDA(cudaMemcpyAsync(P->steps_dev, sp, (size_t)(timesteps + 1) * sizeof(StepParams), cudaMemcpyHostToDevice, s));
+  // the pinned step table is rewritten by the next call: that call waits for THIS copy only (not for the loop kernel
+  // behind it), so back-to-back passes queue without a host stall
+  DM_CUDA(cudaEventRecord(P->steps_event, s));
+  P->steps_pending = true;
   static thread_local LoopParams lp;   // ~19 KB: keep it off the stack
   lp.n_jobs = (int)P->layers.size();
   for (int i = 0; i < lp.n_jobs; ++i) lp.jobs[i] = P->layers[i].job;
-  if (getenv("DM_B200_DUMP_PLAN")) {   // debugging aid: the fused loop's job list
+#ifdef DM_DEV_DEBUG
+  {   // debugging aid (compile with -DDM_DEV_DEBUG): the fused loop's job list
     for (int i = 0; i < lp.n_jobs; ++i) {
       const ConvJob& j = lp.jobs[i];
       fprintf(stderr, "[dm plan] %2d %-24s S %2d Mt %d lt %d Nc %3d sl %d ch %d+%d taps %d aux %d mode %d acc2 %d | A st %d x %6d  W st %d x %6d "
@@ -1021,15 +1095,13 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
               j.next_res, j.sync_local, j.tmem_cols);
     }
   }
+#endif
   lp.maps = P->maps_dev;
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
-  lp.k4_local = P->layers.front().job.S == 8 && P->layers.back().job.S == 8 && !getenv("DM_B200_NO_LOCALSYNC");
+  lp.k4_local = P->layers.front().job.S == 8 && P->layers.back().job.S == 8;
   lp.trace = P->trace_dev; lp.trace_cluster = P->trace_cluster; lp.trace_step = P->trace_step;
   DM_CUDA(launch_sample_loop(lp, P->loop_smem, s));
-  // the pinned step table is reused by the next call: wait until the copy engine has consumed it
-  DM_CUDA(cudaEventRecord(P->steps_event, s));
-  P->steps_pending = true;
   P->last_launches = 1;
   return DM_OK;
 }

@@ -33,6 +33,16 @@ struct Layer {
   std::string name;
 };
 
+// Device tables of one schedule (dm_plan_set_schedule): kept per content hash, so that alternating schedules on one
+// plan (GaussianDiffusion and DiffusionV4 over the same U-Net, eval.py-style loops) neither re-runs K3 nor leaks.
+struct ScheduleTables {
+  unsigned long long hash = 0;
+  int n = 0;
+  float* t_table = nullptr;    // [n] timestep value embedded at each schedule index
+  float* tb_table = nullptr;   // [n, TB] time-bias rows
+  std::vector<float> sr, srm1, c1, c2, logvar;
+};
+
 struct HostTensor {
   const float* data;
   std::vector<int64_t> shape;
@@ -51,7 +61,9 @@ struct dm_plan {
   float* model_out = nullptr;      // fp32 [B,H,T] scratch for the sampling loop
   dm::TimeMlpParams tmlp{};
   int TB = 0;
-  float* tb_table = nullptr;       // [n_timesteps, TB]
+  float* tb_table = nullptr;       // [n_timesteps, TB]  (points into the active entry of `schedules`)
+  std::vector<dm::ScheduleTables> schedules;   // small cache, least recently used entry is replaced
+  int steps_capacity = 0;          // entries allocated in steps_dev / steps_host
   float* tb_rows = nullptr;        // [G*16, TB] per-sample rows for dm_unet_forward
   float* t_table = nullptr;        // [n_timesteps] 0..n-1
   int n_timesteps = 0;

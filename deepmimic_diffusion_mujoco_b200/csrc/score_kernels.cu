@@ -117,67 +117,6 @@ fk_reward_kernel(const float* __restrict__ qpos, const float* __restrict__ feat,
 }
 
 // ------------------------------------------------------------------------------------------------
-// K6: sum[D] += sum_n x ; sxx[D,D] += X^T X.  64x64 output tile per CTA (upper-triangular tiles, mirrored),
-// rows split over gridDim.z, fp32 register-tiled accumulation per split, fp64 atomics across splits.
-// ------------------------------------------------------------------------------------------------
-constexpr int kFidTile = 64, kFidK = 32;
-
-__global__ void __launch_bounds__(256) fid_moments_kernel(const float* __restrict__ X, int N, int D, int rows_per_split,
-                                                          double* __restrict__ sum, double* __restrict__ sxx) {
-  // map linear block index to an upper-triangular tile (ti <= tj)
-  const int nt = (D + kFidTile - 1) / kFidTile;
-  int ti = 0, rem = blockIdx.x;
-  while (rem >= nt - ti) { rem -= nt - ti; ++ti; }
-  const int tj = ti + rem;
-  const int i0 = ti * kFidTile, j0 = tj * kFidTile;
-  const int r0 = blockIdx.z * rows_per_split;
-  const int r1 = min(N, r0 + rows_per_split);
-  __shared__ float sa[kFidK][kFidTile + 4], sb[kFidK][kFidTile + 4];
-  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  float acc[4][4];
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
-  float colsum = 0.f;   // threads 0..63 of diagonal tiles accumulate the column sums
-  for (int r = r0; r < r1; r += kFidK) {
-    for (int e = threadIdx.x; e < kFidK * kFidTile; e += 256) {
-      const int k = e / kFidTile, c = e % kFidTile;
-      const int row = r + k;
-      sa[k][c] = (row < r1 && i0 + c < D) ? __ldg(X + (size_t)row * D + i0 + c) : 0.f;
-      sb[k][c] = (row < r1 && j0 + c < D) ? __ldg(X + (size_t)row * D + j0 + c) : 0.f;
-    }
-    __syncthreads();
-#pragma unroll 8
-    for (int k = 0; k < kFidK; ++k) {
-      const float4 av = *reinterpret_cast<const float4*>(&sa[k][ty * 4]);
-      const float4 bv = *reinterpret_cast<const float4*>(&sb[k][tx * 4]);
-      const float a[4] = {av.x, av.y, av.z, av.w}, b[4] = {bv.x, bv.y, bv.z, bv.w};
-#pragma unroll
-      for (int p = 0; p < 4; ++p)
-#pragma unroll
-        for (int q = 0; q < 4; ++q) acc[p][q] = fmaf(a[p], b[q], acc[p][q]);
-    }
-    if (ti == tj && threadIdx.x < kFidTile) {
-      for (int k = 0; k < kFidK; ++k) colsum += sa[k][threadIdx.x];
-    }
-    __syncthreads();
-  }
-#pragma unroll
-  for (int p = 0; p < 4; ++p) {
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int i = i0 + ty * 4 + p, j = j0 + tx * 4 + q;
-      if (i < D && j < D) {
-        atomicAdd(&sxx[(size_t)i * D + j], (double)acc[p][q]);
-        if (ti != tj) atomicAdd(&sxx[(size_t)j * D + i], (double)acc[p][q]);
-      }
-    }
-  }
-  if (ti == tj && threadIdx.x < kFidTile && i0 + (int)threadIdx.x < D) atomicAdd(&sum[i0 + threadIdx.x], (double)colsum);
-}
-
-// ------------------------------------------------------------------------------------------------
 // Batched window statistics for SiFID (eval.py:59-77: per generated sample, mean and covariance over its W windows
 // of D = window_size * n_feats values, fid_score.py:24-43 arithmetic in fp32).  One CTA per (sample, 8-row band of
 // the covariance); the sample's W x D window matrix is centred in shared memory.  HBM-bound on the D x D output.
@@ -281,26 +220,6 @@ extern "C" int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, 
   else e = feat_in_smem ? launch(fk_reward_kernel<false, true>) : launch(fk_reward_kernel<false, false>);
   cudaFreeAsync(feat, s);
   if (e != cudaSuccess) return fail(DM_ERR_CUDA, "fk_reward launch: %s", cudaGetErrorString(e));
-  return DM_OK;
-}
-
-int dm_fid_moments_simt(const float* X_dev, int N, int D, double* sum_dev, double* sxx_dev, dm_stream_t st) {
-  if (!X_dev || !sum_dev || !sxx_dev) return fail(DM_ERR_ARG, "null argument");
-  if (N < 1 || D < 1) return fail(DM_ERR_ARG, "need N >= 1, D >= 1");
-  int rc = check_device();
-  if (rc) return rc;
-  const int nt = (D + kFidTile - 1) / kFidTile;
-  const int tiles = nt * (nt + 1) / 2;
-  int splits = (148 * 4 + tiles - 1) / tiles;
-  if (splits < 1) splits = 1;
-  int rows = (N + splits - 1) / splits;
-  rows = (rows + kFidK - 1) / kFidK * kFidK;
-  if (rows > 4096) rows = 4096;   // bound the fp32 accumulation length per partial sum
-  splits = (N + rows - 1) / rows;
-  dim3 grid(tiles, 1, splits);
-  fid_moments_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(st)>>>(X_dev, N, D, rows, sum_dev, sxx_dev);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return fail(DM_ERR_CUDA, "fid_moments launch: %s", cudaGetErrorString(e));
   return DM_OK;
 }
 

@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(256) ddpm_step_tiled_kernel(StepParams p) {
   const long long n_rows = (long long)p.B * H;
   const long long n_tiles = (n_rows + kK4Rows - 1) / kK4Rows;
   const int pieces_per_row = p.xs_C >> 3;
+  const CondView cv = resolve_cond(p);
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long r0 = tile * kK4Rows;
     const int rows = (int)min((long long)kK4Rows, n_rows - r0);
@@ -120,11 +121,12 @@ __global__ void __launch_bounds__(256) ddpm_step_tiled_kernel(StepParams p) {
       // inpaint: HT is a multiple of 4 and so is e0, so the four values belong to one sample
       const long long b = e0 / HT;
       const int rem = (int)(e0 - b * HT);
-      if (p.mask) {
+      if (cv.mask) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          if (p.mask[(size_t)b * p.mask_bstride + rem + k]) rv[k] = p.value[(size_t)b * p.value_bstride + rem + k];
+          if (cv.mask[(size_t)b * cv.mask_bstride + rem + k]) rv[k] = cv.value[(size_t)b * cv.value_bstride + rem + k];
       }
+      if (cv.poison) rv[0] = rv[1] = rv[2] = rv[3] = __int_as_float(0x7fc00000);
       const float4 r4 = make_float4(rv[0], rv[1], rv[2], rv[3]);
       reinterpret_cast<float4*>(p.x)[i4] = r4;
       if (p.chain) *reinterpret_cast<float4*>(p.chain + ((size_t)b * p.chain_len + p.chain_slot) * HT + rem) = r4;

@@ -35,6 +35,7 @@ struct StepParams {
   const unsigned char* mask;   // [H*T] (bstride 0) or [B,H*T]; null = no conditioning
   const float* value;
   long long mask_bstride, value_bstride;
+  const unsigned char* cond_flags;   // dm_cond_t::flags_dev (device-side {any, mask uniform, value uniform, pure}) or null
   __half* xs;          // operand planes of the first conv: [2][G][H][16][xs_C]
   long long xs_plane_stride;
   int xs_C;

@@ -12,7 +12,7 @@ import torch
 from torch import nn
 
 from . import _lib
-from .sampling_config import apply_conditioning, trace_conditioning
+from .sampling_config import apply_conditioning, trace_conditioning_device
 
 Sample = namedtuple("Sample", "trajectories values chains")
 
@@ -157,13 +157,15 @@ class GaussianDiffusion(nn.Module):
                 if tuple(starting_motion.shape) != (B, H, T):
                     raise _lib.DmError("starting_motion shape does not match `shape`")
                 x.copy_(starting_motion)
-            mask, value = trace_conditioning(conditioning_fn, (B, H, T), device)
-            if mask is not None:
-                mbuf = self._persistent(("mask", B, H, T, mask.dim()), tuple(mask.shape), torch.uint8, device)
-                vbuf = self._persistent(("value", B, H, T, value.dim()), tuple(value.shape), torch.float32, device)
-                mbuf.copy_(mask)
-                vbuf.copy_(value)
-                mask, value = mbuf, vbuf
+            traced = trace_conditioning_device(conditioning_fn, (B, H, T), device)
+            mask = value = flags = None
+            if traced is not None:
+                mask = self._persistent(("mask", B, H, T), (B, H, T), torch.uint8, device)
+                value = self._persistent(("value", B, H, T), (B, H, T), torch.float32, device)
+                flags = self._persistent(("flags", B, H, T), (4,), torch.uint8, device)
+                mask.copy_(traced[0])
+                value.copy_(traced[1])
+                flags.copy_(traced[2])
             plan = self.model.plan_for(B, H)
             plan.set_schedule(self._schedule_bufs(), self._schedule_id())
             # multi-GPU shards: rows [sample_offset, sample_offset + B) of one global batch (same seed on every rank)
@@ -171,8 +173,9 @@ class GaussianDiffusion(nn.Module):
             chain = torch.empty(B, timesteps + 1, H, T, device=device) if return_chain else None
             c = _lib.DmCond()
             if mask is not None:
-                c.mask_dev, c.value_dev = mask.data_ptr(), value.data_ptr()
-                c.mask_batched, c.value_batched = int(mask.dim() == 3), int(value.dim() == 3)
+                # full [B,H,T] tensors + device-resident structure flags: the kernel picks row 0 when batch-uniform
+                c.mask_dev, c.value_dev, c.flags_dev = mask.data_ptr(), value.data_ptr(), flags.data_ptr()
+                c.mask_batched = c.value_batched = 1
             if seed is None:
                 seed = self.seed + 7919 * self._calls
                 self._calls += 1

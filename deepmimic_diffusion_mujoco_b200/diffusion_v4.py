@@ -11,7 +11,6 @@ through dm_schedule_t.time_values.  No CPU fallback.
 """
 import ctypes
 import math
-import os
 
 import torch
 
@@ -72,7 +71,7 @@ class DiffusionV4:
 
     @torch.no_grad()
     def sample(self, model, n, custom_frames=None, condition=None, y=None, noise=None, return_chain=False, seed=None,
-               sample_offset=0):
+               sample_offset=0, fused=True):
         """Reverse diffusion of n samples (diffusion_v4.py:82-149).  model: this package's TemporalUnet.
         noise: optional injected stack [noise_steps, n, frames, joint_dim] (slot 0 = the initial draw, slot k = the k-th
         randn_like; the reference zeroes the last one itself).  Returns x [n, frames, joint_dim]."""
@@ -89,8 +88,10 @@ class DiffusionV4:
         steps = self.noise_steps - 1
         with torch.cuda.device(device):
             plan = model.plan_for(B, H)
-            plan.set_schedule(self.step_table(), ("v4", id(self), self.predict_x0, self.schedule_type, self.noise_steps,
-                                                  float(self.beta_start), float(self.beta_end)))
+            sched_id = ("v4", id(self), self.predict_x0, self.schedule_type, self.noise_steps,
+                        float(self.beta_start), float(self.beta_end), self.beta.data_ptr(), self.beta._version)
+            if plan.schedule_id != sched_id:   # the table costs device->host reads: build it only when the plan needs it
+                plan.set_schedule(self.step_table(), sched_id)
             _lib.check(_lib.lib().dm_plan_set_sample_offset(plan.handle, int(sample_offset)))
             x = torch.empty(B, H, T, device=device, dtype=torch.float32)
             stack = None
@@ -107,6 +108,6 @@ class DiffusionV4:
                 plan.handle, x.data_ptr(), 0, stack.data_ptr() if stack is not None else None,
                 ctypes.c_uint64(seed & (2 ** 64 - 1)), steps, 0, 0, ctypes.byref(c),
                 chain.data_ptr() if chain is not None else None,
-                0 if os.environ.get("DM_B200_V4_UNFUSED") else 1, _lib.stream_ptr()))
+                int(bool(fused)), _lib.stream_ptr()))
             self.last_launch_count = plan.last_launch_count()
         return (x, chain) if return_chain else x

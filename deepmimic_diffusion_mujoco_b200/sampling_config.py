@@ -38,12 +38,16 @@ def apply_conditioning_motion_editing(x):
 import weakref
 
 _PROBES = {}
-# conditioning function -> {(shape, device): (mask is batch-uniform, value is batch-uniform)}: the STRUCTURE of a function
-# verified once as a pure overwrite.  Values (and which entries are masked) are re-read on every call; only the
-# host-side decisions are cached, so that a sampling call needs no device->host round trip.  A round trip per call
-# serialises the host behind the previous 50 ms sampling kernel (measured: 2 % of the pass).
-_STRUCTURE = weakref.WeakKeyDictionary()
-_PENDING = []   # (pinned flags, event, fn name, expected): deferred re-verification of the cached structure
+# conditioning function -> {(shape, device)}: functions verified ONCE, synchronously, as a pure overwrite for that shape.
+# Nothing about their structure is cached: on later calls every decision the kernels need (anything masked? mask /
+# value batch-uniform? still a pure overwrite?) is computed on the device into a 4-byte flag vector that the kernels
+# read themselves (dm_cond_t::flags_dev), so a sampling call needs no device->host round trip (a round trip per call
+# serialises the host behind the previous 50 ms sampling kernel: measured 2 % of the pass) and a stale host-side
+# decision cannot exist.  A function that stops being a pure overwrite gets its samples poisoned with NaN by the
+# kernel and a DmError from the deferred check below.
+_VERIFIED = weakref.WeakKeyDictionary()
+_PENDING = []   # (pinned flags, event, fn name): deferred host-side report of a purity violation
+_MAX_PENDING = 64
 
 
 def _probes(shape, device):
@@ -59,77 +63,90 @@ def _probes(shape, device):
 
 
 def check_pending(block=False):
-    """Deferred half of the tracer: flags computed on the device during earlier calls are compared with the cached
-    structure once they have arrived (never waits unless block=True).  A mismatch means an earlier sampling call
-    used a stale [H,T]-vs-[B,H,T] decision: the cache entry is dropped and the error is raised now, loudly."""
-    keep = []
-    for flags, ev, name, expect, fn_ref, key in _PENDING:
-        if not block and ev is not None and not ev.query():
-            keep.append((flags, ev, name, expect, fn_ref, key))
+    """Deferred half of the tracer: the purity flag of earlier fast-path calls is inspected once it has arrived in
+    pinned memory (never waits unless block=True).  The kernel already poisoned that call's samples with NaN; this
+    raises the matching error on the host."""
+    keep, bad = [], None
+    for host, ev, name in _PENDING:
+        if not block and not ev.query():
+            keep.append((host, ev, name))
             continue
-        if ev is not None:
-            ev.synchronize()
-        got = tuple(bool(v) for v in flags.tolist())
-        if got != expect:
-            fn = fn_ref()
-            if fn is not None and fn in _STRUCTURE:
-                _STRUCTURE[fn].pop(key, None)
-            _PENDING[:] = keep
-            raise DmError(f"conditioning_fn {name} changed its structure (any / batch-uniform mask / batch-uniform "
-                          f"value = {got}, was {expect}) between calls; the previous sampling call used the old one")
+        ev.synchronize()
+        if not bool(host[3]) and bad is None:
+            bad = name
     _PENDING[:] = keep
+    if bad is not None:
+        raise DmError(f"conditioning_fn {bad} stopped being an x-independent overwrite between calls; the samples of "
+                      "that call were poisoned with NaN by the kernel")
 
 
-def _finish(mask, value, shape, any_, mask_uniform, value_uniform):
-    if not any_:
-        return None, None
-    if mask_uniform:
-        mask = mask[0]
-    if value_uniform and mask.dim() == 2:
-        value = value[0]
-    elif mask.dim() == 2:
-        mask = mask.unsqueeze(0).expand(shape).contiguous()
-    return mask.to(torch.uint8).contiguous(), value.contiguous()
-
-
-def trace_conditioning(fn, shape, device):
-    """Returns (mask uint8, value fp32) with shapes [H,T] (batch-uniform) or [B,H,T], or (None, None) for the
-    identity.  Raises DmError if fn is not an x-independent overwrite."""
-    if fn is None or fn is apply_conditioning or fn is apply_conditioning_in_betweening \
-            or fn is apply_conditioning_motion_blending:
-        return None, None
-    check_pending()
-    shape = tuple(shape)
+def _trace(fn, shape, device):
+    """mask (bool), value (fp32), both [B,H,T], and the device flag vector uint8[4] = {any, mask batch-uniform, value
+    batch-uniform, pure overwrite}."""
     nan_probe, keep = _probes(shape, device)
     out = fn(nan_probe.clone())
     if not torch.is_tensor(out) or tuple(out.shape) != shape:
         raise DmError("conditioning_fn must return a tensor of the input shape")
     mask = ~torch.isnan(out)
     value = torch.where(mask, out, torch.zeros_like(out))
+    out2 = fn(keep.clone())                       # x-independence: a second probe must give where(mask, value, x)
+    pure = (out2 == torch.where(mask, value, keep)).all()
+    flags = torch.stack([mask.any(), (mask == mask[:1]).all(), (value == value[:1]).all(), pure]).to(torch.uint8)
+    return mask, value, flags
+
+
+def _is_identity(fn):
+    return fn is None or fn is apply_conditioning or fn is apply_conditioning_in_betweening \
+        or fn is apply_conditioning_motion_blending
+
+
+def trace_conditioning_device(fn, shape, device):
+    """What p_sample_loop hands to the kernels: None for the identity, else (mask uint8 [B,H,T], value fp32 [B,H,T],
+    flags uint8[4]) all on `device`.  First sight of (fn, shape): one synchronous read of the flags (raises DmError
+    if fn is not a pure overwrite).  Afterwards: no host read at all -- the kernels take every decision from `flags`."""
+    if _is_identity(fn):
+        return None
+    check_pending()
+    shape = tuple(shape)
+    mask, value, flags = _trace(fn, shape, device)
     key = (shape, str(device))
     try:
-        known = _STRUCTURE.setdefault(fn, {})
-    except TypeError:          # not weak-referenceable: verify every time
-        known = {}
-    flags_dev = torch.stack([mask.any(), (mask == mask[:1]).all(), (value == value[:1]).all()])
-    if key in known and out.is_cuda:
-        # fast path: no host round trip.  The flags travel to pinned memory behind the kernels above and are compared
-        # with the cached structure by a later call (check_pending).
-        host = torch.empty(3, dtype=torch.bool, pin_memory=True)
-        host.copy_(flags_dev, non_blocking=True)
+        seen = _VERIFIED.setdefault(fn, set())
+    except TypeError:          # not weak-referenceable: verify synchronously every time
+        seen = set()
+    if key in seen and flags.is_cuda:
+        if len(_PENDING) >= _MAX_PENDING:          # never drop a check: settle the oldest ones first
+            check_pending(block=True)
+        host = torch.empty(4, dtype=torch.uint8, pin_memory=True)
+        host.copy_(flags, non_blocking=True)
         ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(out.device))
-        if len(_PENDING) < 64:
-            _PENDING.append((host, ev, getattr(fn, "__name__", repr(fn)), (True,) + known[key], weakref.ref(fn), key))
-        return _finish(mask, value, shape, True, *known[key])
-    # first sight of this function for this shape: x-independence is verified with a second probe, and every
-    # property the host needs comes back in ONE device->host read
-    out2 = fn(keep.clone())
-    pure = (out2 == torch.where(mask, value, keep)).all()
-    flags = torch.cat([pure.reshape(1), flags_dev]).cpu().tolist()
-    if not flags[0]:
+        ev.record(torch.cuda.current_stream(flags.device))
+        _PENDING.append((host, ev, getattr(fn, "__name__", repr(fn))))
+        return mask.to(torch.uint8), value, flags
+    f = flags.cpu().tolist()
+    if not f[3]:
         raise DmError("conditioning_fn is not an x-independent overwrite x = where(mask, value, x); it cannot be "
                       "fused into the sampling kernels (no fallback)")
-    if flags[1]:
-        known[key] = (bool(flags[2]), bool(flags[3]))   # functions that overwrite nothing are re-verified every call
-    return _finish(mask, value, shape, flags[1], flags[2], flags[3])
+    if not f[0]:
+        return None            # overwrites nothing (e.g. writes into a captured tensor): identity, re-verified every call
+    seen.add(key)
+    return mask.to(torch.uint8), value, flags
+
+
+def trace_conditioning(fn, shape, device):
+    """Returns (mask uint8, value fp32) with shapes [H,T] (batch-uniform) or [B,H,T], or (None, None) for the
+    identity.  Raises DmError if fn is not an x-independent overwrite.  Synchronous, compact form (host tooling and
+    tests); the sampling path uses trace_conditioning_device."""
+    if _is_identity(fn):
+        return None, None
+    shape = tuple(shape)
+    mask, value, flags = _trace(fn, shape, device)
+    any_, mask_uniform, value_uniform, pure = (bool(v) for v in flags.cpu().tolist())
+    if not pure:
+        raise DmError("conditioning_fn is not an x-independent overwrite x = where(mask, value, x); it cannot be "
+                      "fused into the sampling kernels (no fallback)")
+    if not any_:
+        return None, None
+    if mask_uniform and value_uniform:
+        mask, value = mask[0], value[0]
+    return mask.to(torch.uint8).contiguous(), value.contiguous()

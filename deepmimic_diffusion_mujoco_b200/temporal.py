@@ -193,7 +193,7 @@ class TemporalUnet(nn.Module):
         return tuple([(p.data_ptr(), p._version) for p in plist])
 
     def plan_for(self, B, H):
-        key = (B, H)
+        key = (B, H, torch.cuda.current_device() if torch.cuda.is_available() else -1)   # a plan lives on ONE device
         ver = self._weights_version()
         hit = self._plans.get(key)
         if hit is not None and hit[0] == ver:
@@ -212,11 +212,12 @@ class TemporalUnet(nn.Module):
             raise _lib.DmError(f"expected fp32 [B, H, {self.transition_dim}], got {x.dtype} {tuple(x.shape)}")
         x = x.contiguous()
         B, H, _ = x.shape
-        plan = self.plan_for(B, H)
         t = time.to(device=x.device, dtype=torch.float32).contiguous()
         if t.numel() != B:
             raise _lib.DmError("time must have one entry per sample")
-        out = torch.empty_like(x)
-        _lib.check(_lib.lib().dm_unet_forward(plan.handle, x.data_ptr(), t.data_ptr(), out.data_ptr(),
-                                              _lib.stream_ptr()))
+        with torch.cuda.device(x.device):      # plans, launches and the stream all belong to x's device
+            plan = self.plan_for(B, H)
+            out = torch.empty_like(x)
+            _lib.check(_lib.lib().dm_unet_forward(plan.handle, x.data_ptr(), t.data_ptr(), out.data_ptr(),
+                                                  _lib.stream_ptr()))
         return out

@@ -59,6 +59,12 @@ typedef struct {
   const float* value_dev;
   int mask_batched;
   int value_batched;
+  /* Optional device-resident decision, uint8[4] = {any entry masked, mask is batch-uniform, value is batch-uniform,
+   * the function is a pure overwrite}.  When non-NULL, mask_dev / value_dev must be the full [B,H*T] tensors
+   * (mask_batched = value_batched = 1) and the KERNEL picks row 0 for batch-uniform tensors, skips the inpaint when
+   * nothing is masked, and poisons x with NaN when the traced function was not a pure overwrite -- so a caller's
+   * tracer never needs a device->host read-back, and a stale host-side guess can never select the wrong rows. */
+  const uint8_t* flags_dev;
 } dm_cond_t;
 
 const char* dm_last_error(void);

@@ -200,12 +200,7 @@ def test_v4_sampler_matches_reference_fixture(dm, golden_dir, tag, sched, fused)
     net.load_state_dict(sd)
     d = dm.DiffusionV4(T, 1e-4, 0.02, 35, H, device="cuda", predict_x0=bool(px0), schedule_type=sched)
     noise = torch.from_numpy(z[tag + "_noise"])
-    if not fused:
-        os.environ["DM_B200_V4_UNFUSED"] = "1"
-    try:
-        x, chain = d.sample(net.cuda(), B, noise=noise, return_chain=True)
-    finally:
-        os.environ.pop("DM_B200_V4_UNFUSED", None)
+    x, chain = d.sample(net.cuda(), B, noise=noise, return_chain=True, fused=fused)
     ref = torch.from_numpy(z[tag + "_x"])
     assert rel(x.cpu(), ref) < REL_STEP
     oc = O.v4_sample(sd, O.v4_betas(T, 1e-4, 0.02, sched), noise, bool(px0))
@@ -382,6 +377,46 @@ def test_errors_are_loud(dm):
         diff.p_sample_loop((1, 64, 35), {}, verbose=False, conditioning_fn=lambda x: x * 0.5)
     with pytest.raises(dm.DmError):
         diff.p_sample_loop((1, 64, 35), {}, verbose=False, sample_fn=lambda *a: None)
+
+
+def test_conditioning_structure_may_change_between_calls(dm):
+    """The same function object goes from batch-uniform to per-sample values (and back) between calls: every call must
+    inpaint each sample with ITS OWN constraints.  The kernels take the [H,T]-vs-[B,H,T] decision from device-resident
+    flags, so no host-side cache can go stale; a function that stops being a pure overwrite poisons its samples with
+    NaN and raises on a later call."""
+    from deepmimic_diffusion_mujoco_b200 import sampling_config as SC
+    B, H = 6, 16
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(O.seeded_state_dict(H=H, seed=1))
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=3, predict_epsilon=False).cuda()
+    keys = torch.zeros(B, H, 35, device="cuda")
+    state = {"impure": False}
+
+    def cond(x):
+        if state["impure"]:
+            return x * 0.5
+        x[:, 3:9, 0:7] = keys[:, 3:9, 0:7]
+        return x
+
+    a = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=cond, seed=4).trajectories   # first sight: uniform zeros
+    assert torch.equal(a[:, 3:9, 0:7], keys[:, 3:9, 0:7])
+    keys.copy_(torch.randn(B, H, 35, generator=torch.Generator().manual_seed(2)))                        # now per-sample
+    b = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=cond, seed=4).trajectories
+    assert torch.equal(b[:, 3:9, 0:7], keys[:, 3:9, 0:7]) and not torch.equal(b[0, 3:9, 0:7], b[1, 3:9, 0:7])
+    free = torch.ones(B, H, 35, dtype=torch.bool)
+    free[:, 3:9, 0:7] = False
+    assert torch.isfinite(b).all() and not torch.equal(a[free.cuda()], torch.zeros_like(a[free.cuda()]))
+    keys[:] = keys[:1]                                                                                   # uniform again
+    c = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=cond, seed=4).trajectories
+    assert torch.equal(c[:, 3:9, 0:7], keys[:, 3:9, 0:7])
+    state["impure"] = True
+    bad = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=cond, seed=4).trajectories
+    assert torch.isnan(bad).all()
+    with pytest.raises(dm.DmError):
+        SC.check_pending(block=True)
+    state["impure"] = False
+    ok = diff.p_sample_loop((B, H, 35), {}, verbose=False, conditioning_fn=cond, seed=4).trajectories
+    assert torch.equal(ok, c)
 
 
 # ---------------------------------------------------------------------------------------------------
