@@ -352,62 +352,6 @@ def main():
 
         clip = np.load(os.path.join(ROOT, "tests", "golden", "mocap_clips.npz"))["spinkick_config"]
         ref = MD.tile_clip(torch.from_numpy(clip).float(), H).to(dev)
-        x = last.trajectories
-        frames = B * H
-        D = H * T
-        s = torch.zeros(D, device=dev, dtype=torch.float64)
-        sxx = torch.zeros(D, D, device=dev, dtype=torch.float64)
-        plan = net.plan_for(B, H)
-        xk, mo = torch.randn(B, H, T, device=dev), torch.randn(B, H, T, device=dev)
-        nul = ctypes.POINTER(_lib.DmCond)()
-
-        def hbm_entry(name, ms, nbytes, note):
-            return {"name": name, "ms": ms, "bound": "hbm", "algorithmic_bytes": nbytes, "achieved_gbs": nbytes / ms / 1e6,
-                    "frac": nbytes / ms / 1e6 / pk["hbm"], "peak_source": pk["source"] + " hbm_gbs", "note": note}
-
-        kernels = []
-        ms = timed(lambda: _lib.check(_lib.lib().dm_ddpm_step(plan.handle, xk.data_ptr(), mo.data_ptr(), None, 1, 50, 0, 0,
-                                                              nul, _lib.stream_ptr())))
-        kernels.append(hbm_entry("K4 ddpm_step_tiled_kernel (stand-alone launch, Philox noise)", ms, frames * 12 * T,
-                                 f"{frames} frames x 420 B; at this size (9 MB) the launch is latency-sized -- inside the "
-                                 "fused loop K4 is part of sample_loop_kernel"))
-        ms = timed(lambda: scoring.fk_reward(x, ref, 0.016666))
-        kernels.append(hbm_entry("K5 fk_reward_kernel (reward only)", ms, frames * 144, f"{frames} frames x (140 B read + 4 B written)"))
-        ms = timed(lambda: scoring.fk_reward(x, ref, 0.016666, return_body_pos=True))
-        kernels.append(hbm_entry("K5 fk_reward_kernel (+ body positions)", ms, frames * 324, f"{frames} frames x (140 + 4 + 180 B)"))
-        ms = timed(lambda: scoring.fid_moments(x, s, sxx))
-        fl = 2.0 * B * D * D
-        kernels.append({"name": "K6 fid_transpose + fid_syrk (tcgen05) + fid_reduce", "ms": ms, "bound": "tensor",
-                        "algorithmic_flops": fl, "achieved_tflops": fl / ms / 1e9, "frac": fl / ms / 1e9 / pk["tf_burst"],
-                        "peak_source": pk["source"] + " bf16 burst", "note": f"N={B}, D={D}: 2 N D^2 (full matrix; the upper "
-                        "triangle is computed, 3 MMAs per product for the fp16 hi/lo split)"})
-        nw = min(B, 2048)
-        ms = timed(lambda: scoring.window_moments(x[:nw], 10))
-        kernels.append(hbm_entry("K8 window_moments_kernel (SiFID statistics)", ms, nw * (H * T * 4 + 350 * 4 + 350 * 350 * 4),
-                                 f"{nw} samples x (input + 350 mean + 350x350 covariance, fp32)"))
-
-        # ---- the one exchange step: all-reduce of {N, sum x, sum xx^T, reward sums} (fp64), NCCL ----
-        sums = scoring.fk_reward(x, ref, 0.016666)["sums"]
-        nbytes = (1 + s.numel() + sxx.numel() + sums.numel()) * 8
-        if world > 1:
-            scoring.allreduce_statistics(B, s, sxx, sums)
-            barrier()
-            ts = []
-            for _ in range(5):
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                scoring.allreduce_statistics(B, s, sxx, sums)
-                e1.record()
-                torch.cuda.synchronize()
-                ts.append(e0.elapsed_time(e1))
-            ms = max_over_ranks(median(ts))
-            collective = {"op": "all_reduce(SUM) fp64, NCCL", "bytes": nbytes, "ms": ms, "n_ranks": world,
-                          "algbw_gbs": nbytes / ms / 1e6, "busbw_gbs": 2.0 * (world - 1) / world * nbytes / ms / 1e6,
-                          "note": "includes packing / unpacking the statistics into one flat buffer (scoring.allreduce_statistics)"}
-        else:
-            collective = {"op": "all_reduce(SUM) fp64, NCCL", "bytes": nbytes, "ms": 0.0, "n_ranks": 1, "busbw_gbs": None,
-                          "note": "single rank: nothing to exchange"}
-
         # ---- configs[4] at this rank count: sample `score_batch` motions per GPU of ONE global batch (global Philox rows),
         #      FK + reward + FID moments, all-reduce; wall clock barrier to barrier ----
         Ns = args.score_batch
@@ -423,18 +367,75 @@ def main():
             n = scoring.allreduce_statistics(Ns, s2, sxx2, sc["sums"])
             evs[3].record()
             torch.cuda.synchronize()
-            return n, sc["sums"], [evs[i].elapsed_time(evs[i + 1]) for i in range(3)]
+            return n, sc["sums"], [evs[i].elapsed_time(evs[i + 1]) for i in range(3)], xs
 
         score_job_once()
         barrier()
         t0 = time.perf_counter()
-        n_tot, sums2, parts = score_job_once()
+        n_tot, sums2, parts, xs = score_job_once()
         barrier()
         wall = max_over_ranks(time.perf_counter() - t0)
         score_job = {"workload": f"configs[4]: {world * Ns} samples sampled (100 steps), FK + tracking reward vs spinkick frames "
                                  "0-63, FID moments, statistics all-reduced", "samples": world * Ns, "wall_s": wall,
                      "frames_per_s": world * Ns * H / wall, "rank0_ms": {"sample": parts[0], "score": parts[1], "allreduce": parts[2]},
                      "count": n_tot, "mean_reward": float(sums2[0].item() / max(sums2[6].item(), 1.0))}
+
+        # kernel-by-kernel numbers at the configs[4] per-GPU size (the bench batch, 9 MB, would be launch-latency sized)
+        x = xs
+        frames = Ns * H
+        D = H * T
+        s = torch.zeros(D, device=dev, dtype=torch.float64)
+        sxx = torch.zeros(D, D, device=dev, dtype=torch.float64)
+        plan = net.plan_for(B, H)
+        xk, mo = torch.randn(B, H, T, device=dev), torch.randn(B, H, T, device=dev)
+        nul = ctypes.POINTER(_lib.DmCond)()
+
+        def hbm_entry(name, ms, nbytes, note):
+            return {"name": name, "ms": ms, "bound": "hbm", "algorithmic_bytes": nbytes, "achieved_gbs": nbytes / ms / 1e6,
+                    "frac": nbytes / ms / 1e6 / pk["hbm"], "peak_source": pk["source"] + " hbm_gbs", "note": note}
+
+        kernels = []
+        ms = timed(lambda: _lib.check(_lib.lib().dm_ddpm_step(plan.handle, xk.data_ptr(), mo.data_ptr(), None, 1, 50, 0, 0,
+                                                              nul, _lib.stream_ptr())))
+        kernels.append(hbm_entry("K4 ddpm_step_tiled_kernel (stand-alone launch at the bench batch, Philox noise)", ms, B * H * 12 * T,
+                                 f"{B * H} frames x 420 B; at this size (9 MB) the launch is latency-sized -- inside the "
+                                 "fused loop K4 is part of sample_loop_kernel"))
+        ms = timed(lambda: scoring.fk_reward(x, ref, 0.016666))
+        kernels.append(hbm_entry("K5 fk_reward_kernel (reward only)", ms, frames * 144, f"{frames} frames x (140 B read + 4 B written)"))
+        ms = timed(lambda: scoring.fk_reward(x, ref, 0.016666, return_body_pos=True))
+        kernels.append(hbm_entry("K5 fk_reward_kernel (+ body positions)", ms, frames * 324, f"{frames} frames x (140 + 4 + 180 B)"))
+        ms = timed(lambda: scoring.fid_moments(x, s, sxx))
+        fl = 2.0 * Ns * D * D
+        kernels.append({"name": "K6 fid_transpose + fid_syrk (tcgen05) + fid_reduce", "ms": ms, "bound": "tensor",
+                        "algorithmic_flops": fl, "achieved_tflops": fl / ms / 1e9, "frac": fl / ms / 1e9 / pk["tf_burst"],
+                        "peak_source": pk["source"] + " bf16 burst", "note": f"N={Ns}, D={D}: 2 N D^2 (full matrix; the upper "
+                        "triangle is computed, 3 MMAs per product for the fp16 hi/lo split)"})
+        nw = min(Ns, 2048)
+        ms = timed(lambda: scoring.window_moments(x[:nw], 10))
+        kernels.append(hbm_entry("K8 window_moments_kernel (SiFID statistics)", ms, nw * (H * T * 4 + 350 * 4 + 350 * 350 * 4),
+                                 f"{nw} samples x (input + 350 mean + 350x350 covariance, fp32)"))
+
+        # ---- the one exchange step: all-reduce of {N, sum x, sum xx^T, reward sums} (fp64), NCCL ----
+        sums = scoring.fk_reward(x, ref, 0.016666)["sums"]
+        nbytes = (1 + s.numel() + sxx.numel() + sums.numel()) * 8
+        if world > 1:
+            scoring.allreduce_statistics(Ns, s, sxx, sums)
+            barrier()
+            ts = []
+            for _ in range(5):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                scoring.allreduce_statistics(Ns, s, sxx, sums)
+                e1.record()
+                torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            ms = max_over_ranks(median(ts))
+            collective = {"op": "all_reduce(SUM) fp64, NCCL", "bytes": nbytes, "ms": ms, "n_ranks": world,
+                          "algbw_gbs": nbytes / ms / 1e6, "busbw_gbs": 2.0 * (world - 1) / world * nbytes / ms / 1e6,
+                          "note": "includes packing / unpacking the statistics into one flat buffer (scoring.allreduce_statistics)"}
+        else:
+            collective = {"op": "all_reduce(SUM) fp64, NCCL", "bytes": nbytes, "ms": 0.0, "n_ranks": 1, "busbw_gbs": None,
+                          "note": "single rank: nothing to exchange"}
 
         if rank == 0 and world == 1:
             eager = gpu_eager_baseline(B)

@@ -75,6 +75,56 @@ __global__ void mocap_to_qpos_kernel(const double* __restrict__ frames, int F, f
   }
 }
 
+// utils/mocap_v2.py:155-178 calc_rot_vel(seg_0 = frame k, seg_1 = frame k-1, dura): q_diff = conj(q_0) * q_1, velocity =
+// angle / dura * axis with pyquaternion 0.9.9's .axis / .angle: normalise unless |1 - |q|^2| < 1e-14; axis = vector /
+// |vector| (zeros below 1e-17); angle = 2 atan2(|vector|, scalar) wrapped into (-pi, pi].
+__device__ __forceinline__ void rot_vel(Qd q_now, Qd q_prev, double dura, float* out) {
+  const Qd conj = {q_now.w, -q_now.x, -q_now.y, -q_now.z};
+  Qd d = qmul_d(conj, q_prev);
+  const double ss = d.w * d.w + d.x * d.x + d.y * d.y + d.z * d.z;
+  if (!(fabs(1.0 - ss) < 1e-14)) {
+    const double n = sqrt(ss);
+    if (n > 0.0) { d.w /= n; d.x /= n; d.y /= n; d.z /= n; }
+  }
+  const double nv = sqrt(d.x * d.x + d.y * d.y + d.z * d.z);
+  double ax = 0.0, ay = 0.0, az = 0.0;
+  if (!(nv < 1e-17)) { ax = d.x / nv; ay = d.y / nv; az = d.z / nv; }
+  const double pi = 3.14159265358979323846;
+  double ang = fmod(2.0 * atan2(nv, d.w) + pi, 2.0 * pi) - pi;
+  if (ang == -pi) ang = pi;
+  const double w = ang / dura;
+  out[0] = (float)(w * ax); out[1] = (float)(w * ay); out[2] = (float)(w * az);
+}
+
+// data_vel rows (utils/mocap_v2.py:196-291): [root linear 3 | root angular 3 | joints in qpos order: 3 or 1] = 34 values.
+// Row 0 is zero; row k differences frame k against frame k-1 over durations[k-1] (0.0167 when zero).
+__global__ void mocap_to_qvel_kernel(const double* __restrict__ frames, int F, float* __restrict__ qvel) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  float* o = qvel + (size_t)f * 34;
+  if (f == 0) {
+    for (int i = 0; i < 34; ++i) o[i] = 0.f;
+    return;
+  }
+  const double* fr = frames + (size_t)f * 44;
+  const double* pv = fr - 44;
+  double dura = pv[0];
+  if (dura == 0.0) dura = 0.0167;
+  o[0] = (float)((fr[1] - pv[1]) * 1.0 / dura);
+  o[1] = (float)(((-fr[3]) - (-pv[3])) * 1.0 / dura);
+  o[2] = (float)((fr[2] - pv[2]) * 1.0 / dura);
+  rot_vel(align_rotation(fr + 4), align_rotation(pv + 4), dura, o + 3);
+  const int dp_off[12] = {8, 12, 16, 20, 21, 25, 29, 30, 34, 35, 39, 43};
+  const int dp_hinge[12] = {0, 0, 0, 1, 0, 0, 1, 0, 1, 0, 0, 1};
+  // offsets inside the velocity row: qpos offset minus 1 (the root quaternion has 4 values, its velocity 3)
+  const int to_qvel[12] = {6, 9, 20, 23, 24, 12, 15, 27, 30, 31, 16, 19};
+#pragma unroll
+  for (int j = 0; j < 12; ++j) {
+    if (dp_hinge[j]) o[to_qvel[j]] = (float)((fr[dp_off[j]] - pv[dp_off[j]]) * 1.0 / dura);
+    else rot_vel(align_rotation(fr + dp_off[j]), align_rotation(pv + dp_off[j]), dura, o + to_qvel[j]);
+  }
+}
+
 // dataset[i][j][:] = qpos[(i + j) % n][:]   (motion_dataset.py:31-37: cat(cfg[i:], cfg[:i]))
 __global__ void motion_dataset_kernel(const float* __restrict__ qpos, int n, float* __restrict__ out) {
   const long long total = (long long)n * n * 35;
@@ -98,6 +148,17 @@ extern "C" int dm_mocap_to_qpos(const double* frames_dev, int F, float* qpos_dev
   mocap_to_qpos_kernel<<<(F + 63) / 64, 64, 0, static_cast<cudaStream_t>(st)>>>(frames_dev, F, qpos_dev);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(DM_ERR_CUDA, "mocap_to_qpos launch: %s", cudaGetErrorString(e));
+  return DM_OK;
+}
+
+extern "C" int dm_mocap_to_qvel(const double* frames_dev, int F, float* qvel_dev, dm_stream_t st) {
+  if (!frames_dev || !qvel_dev) return fail(DM_ERR_ARG, "null argument");
+  if (F < 1) return fail(DM_ERR_ARG, "need at least one frame");
+  int rc = check_device();
+  if (rc) return rc;
+  mocap_to_qvel_kernel<<<(F + 63) / 64, 64, 0, static_cast<cudaStream_t>(st)>>>(frames_dev, F, qvel_dev);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(DM_ERR_CUDA, "mocap_to_qvel launch: %s", cudaGetErrorString(e));
   return DM_OK;
 }
 

@@ -68,6 +68,54 @@ def mocap_to_qpos(frames):
     return np.concatenate(cols, axis=-1)
 
 
+def _rot_vel(q_now, q_prev, dura):
+    """utils/mocap_v2.py:155-178 (calc_rot_vel(data[k], data[k-1], dura)), vectorised: q_diff = conj(q_now) * q_prev,
+    velocity = angle / dura * axis with pyquaternion's .axis / .angle semantics (normalise unless already unit to
+    1e-14, axis = vector / |vector| or zeros below 1e-17, angle = 2 atan2(|vector|, scalar) wrapped into (-pi, pi])."""
+    conj = q_now * np.array([1.0, -1.0, -1.0, -1.0])
+    qd = _qmul(conj, q_prev)
+    ss = np.sum(qd * qd, axis=-1, keepdims=True)
+    unit = np.abs(1.0 - ss) < 1e-14
+    n = np.sqrt(ss)
+    qd = np.where(unit | (n <= 0), qd, qd / np.where(n > 0, n, 1.0))
+    nv = np.sqrt(qd[..., 1] ** 2 + qd[..., 2] ** 2 + qd[..., 3] ** 2)
+    axis = np.where((nv < 1e-17)[..., None], 0.0, qd[..., 1:] / np.where(nv < 1e-17, 1.0, nv)[..., None])
+    theta = 2.0 * np.arctan2(nv, qd[..., 0])
+    ang = np.fmod(theta + np.pi, 2 * np.pi) - np.pi
+    ang = np.where(ang == -np.pi, np.pi, ang)
+    return (ang / dura)[..., None] * axis
+
+
+def mocap_to_qvel(frames):
+    """[F, 44] DeepMimic frames -> [F, 34] float64 velocity rows (`MocapDM.data_vel`, utils/mocap_v2.py:196-291): root
+    linear 3, root angular 3, then per joint in MuJoCo order an angular velocity (3) or a hinge rate (1).  Row 0 is zero;
+    row k differences frame k against frame k-1 over durations[k-1] (0.0167 when that is zero)."""
+    fr = np.asarray(frames, dtype=np.float64)
+    F = fr.shape[0]
+    out = np.zeros((F, 34), dtype=np.float64)
+    if F < 2:
+        return out
+    dura = fr[:-1, 0].copy()
+    dura[dura == 0] = 0.0167
+    pos = np.stack([fr[:, 1], -fr[:, 3], fr[:, 2]], axis=-1)
+    cols = [(pos[1:] - pos[:-1]) * 1.0 / dura[:, None]]
+    rq = _align_rotation(fr[:, 4:8])
+    cols.append(_rot_vel(rq[1:], rq[:-1], dura))
+    joint, off = {}, 8
+    for name in _DP_ORDER:
+        width = 1 if name in _HINGES else 4
+        joint[name] = fr[:, off:off + width]
+        off += width
+    for name in _BODY_JOINTS:
+        if name in _HINGES:
+            cols.append((joint[name][1:] - joint[name][:-1]) * 1.0 / dura[:, None])
+        else:
+            q = _align_rotation(joint[name])
+            cols.append(_rot_vel(q[1:], q[:-1], dura))
+    out[1:] = np.concatenate(cols, axis=-1)
+    return out
+
+
 def load_mocap_frames(path):
     with open(path, "r") as f:
         return np.array(json.load(f)["Frames"], dtype=np.float64)
@@ -99,6 +147,82 @@ class MotionDataset(torch.utils.data.Dataset):
 
     def get_conditions(self, data_configs):
         return {0: data_configs[0]}
+
+
+BatchV2 = namedtuple("BatchV2", "trajectories motion_class")
+
+MOTION_CLASSES = {"humanoid3d_walk": 0, "humanoid3d_run": 1, "humanoid3d_spinkick": 2, "humanoid3d_roll": 3,
+                  "humanoid3d_dance_a": 4, "humanoid3d_dance_b": 5, "humanoid3d_jump": 6, "humanoid3d_cartwheel": 7,
+                  "humanoid3d_backflip": 8}      # data_loaders/motion_dataset_v2.py:11-21
+
+
+class MotionDatasetV2(torch.utils.data.Dataset):
+    """Drop-in for data_loaders/motion_dataset_v2.py:30-136, the loader of the 69-wide (qpos | qvel) models
+    (eval.py:189-197, TemporalUnet dim=128): every item is a [F, 69] float32 trajectory plus its motion class.
+    shuffle=False: the clip itself, 1000 times (:104-107); shuffle=True: every cyclic shift with the root translation
+    kept continuous across the wrap (:85-103).  device='cuda': rows are computed by dm_mocap_to_qpos / dm_mocap_to_qvel
+    and stay on the device.  One file per dataset (a directory keeps its first two .txt files, as the reference does)."""
+
+    def __init__(self, motion_src_path, shuffle=False, device=None):
+        import os
+        if not motion_src_path.endswith(".txt"):
+            files = [os.path.join(motion_src_path, f) for f in os.listdir(motion_src_path) if f.endswith(".txt")][:2]
+        else:
+            files = [motion_src_path]
+        self.motion_data, classes = [], []
+        self.max_sequence_length = 0
+        on_dev = device is not None and torch.device(device).type == "cuda"
+        for path in files:
+            cls = MOTION_CLASSES[path.split("/")[-1].split(".")[0]]
+            frames = load_mocap_frames(path)
+            if on_dev:
+                combined = torch.cat([mocap_qpos_on_device(frames, torch.device(device)),
+                                      mocap_qvel_on_device(frames, torch.device(device))], dim=1)
+            else:
+                combined = torch.from_numpy(np.concatenate([mocap_to_qpos(frames), mocap_to_qvel(frames)], axis=1))
+            F = combined.shape[0]
+            self.max_sequence_length = max(self.max_sequence_length, F)
+            if shuffle:
+                c = combined.double() if not on_dev else combined
+                diff = c[-1] - c[0]
+                for i in range(F):
+                    prefix, suffix = c[i:].clone(), c[:i].clone()
+                    if i != 0 and i != F - 1:
+                        suffix[:, :3] += diff[:3]
+                        first = prefix[0] - c[0]
+                        prefix[:, :3] -= first[:3]
+                        suffix[:, :3] -= first[:3]
+                    self.motion_data.append(torch.cat([prefix.float(), suffix.float()], dim=0))
+                    classes.append(cls)
+            else:
+                row = combined.float()
+                self.motion_data += [row] * 1000
+                classes += [cls] * 1000
+        self.motion_classes = torch.tensor(classes)
+
+    def __len__(self):
+        return len(self.motion_classes)
+
+    def __getitem__(self, idx):
+        return BatchV2(trajectories=self.motion_data[idx], motion_class=self.motion_classes[idx])
+
+    def collate_fn(self, batch):
+        """motion_dataset_v2.py:116-130: a jagged nested tensor of the batch's trajectories, stacked classes."""
+        traj = torch.nested.nested_tensor([b.trajectories for b in batch], layout=torch.jagged)
+        return BatchV2(trajectories=traj, motion_class=torch.stack([b.motion_class for b in batch]))
+
+    def get_conditions(self, data_configs):
+        return {0: data_configs[0]}
+
+
+def mocap_qvel_on_device(frames, device):
+    """[F, 44] DeepMimic frames (host array) -> qvel fp32 [F, 34] on `device`, computed by dm_mocap_to_qvel."""
+    from . import _lib
+    fr = torch.as_tensor(np.ascontiguousarray(frames, dtype=np.float64)).to(device)
+    out = torch.empty(fr.shape[0], 34, device=device, dtype=torch.float32)
+    with torch.cuda.device(device):
+        _lib.check(_lib.lib().dm_mocap_to_qvel(fr.data_ptr(), fr.shape[0], out.data_ptr(), _lib.stream_ptr()))
+    return out
 
 
 def mocap_qpos_on_device(frames, device):

@@ -122,6 +122,10 @@ int dm_window_moments(const float* X_dev, int N, int H, int F, int window, int s
 /* On-device mocap loader (utils/mocap_v2.py:105-291 + utils/mocap_util.py:31-48): DeepMimic frames, host-parsed JSON
  * "Frames" as double [F,44] on the device -> qpos rows fp32 [F,35] (float64 arithmetic, cast like motion_dataset.py:38). */
 int dm_mocap_to_qpos(const double* frames_dev, int F, float* qpos_dev, dm_stream_t stream);
+/* Velocity rows of the same loader (utils/mocap_v2.py:196-291 data_vel, calc_rot_vel :155-178): frames_dev double [F,44]
+ * -> qvel rows fp32 [F,34] (root linear 3, root angular 3, per joint 3 or 1); with dm_mocap_to_qpos these are the 69
+ * features of data_loaders/motion_dataset_v2.py:66-83 (the dim=128 TemporalUnet's inputs, eval.py:189-197). */
+int dm_mocap_to_qvel(const double* frames_dev, int F, float* qvel_dev, dm_stream_t stream);
 /* MotionDataset tensor (data_loaders/motion_dataset.py:31-42): out_dev fp32 [n,n,35], row i = the clip rolled by i frames. */
 int dm_motion_dataset(const float* qpos_dev, int n, float* out_dev, dm_stream_t stream);
 

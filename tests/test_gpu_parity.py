@@ -233,6 +233,51 @@ def test_hundred_step_chain_vs_oracle(dm):
     assert torch.equal(chain[:, -1][m], ref[:, -1][m])
 
 
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("B,H", [(3, 128), (2, 256)])
+def test_hundred_step_chain_long_horizons(dm, B, H, fused):
+    """100 free-running steps at H = 128 / 256 with injected noise: these horizons take different code from H = 64
+    (several l-tiles per unit, the one-issuer fallback at H = 256, non-staged epilogues), so their error accumulation
+    over a whole chain is checked slot by slot against the fp32 oracle."""
+    n = 100
+    sd = O.seeded_state_dict(H=H, seed=6)
+    noise = torch.randn(n + 1, B, H, 35, generator=torch.Generator().manual_seed(H + B))
+    mask, value = box_cond(H)
+    ref = O.p_sample_loop(sd, O.make_schedule(n), noise, mask=mask, value=value)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=dm.InjectedNoise(noise),
+                             conditioning_fn=box_holding, fused=fused)
+    chain = out.chains.cpu()
+    worst = max(rel(chain[:, k], ref[:, k]) for k in range(n + 1))
+    assert worst < REL_STEP, worst
+    m = mask.expand(B, H, 35)
+    assert torch.equal(chain[:, -1][m], ref[:, -1][m])
+
+
+def test_full_batch_rows_match_oracle(dm):
+    """configs[1] batch (B = 1024, 64 clusters): rows spread over the first, middle and last clusters -- and both CTAs
+    of a cluster -- are compared VALUE by value with the oracle run on just those rows (samples never interact)."""
+    B, H, n = 1024, 64, 10
+    rows = [0, 7, 8, 15, 16, 500, 777, 1015, 1016, 1023]
+    sd = O.seeded_state_dict(H=H, seed=0)
+    noise = torch.randn(n + 1, B, H, 35, generator=torch.Generator().manual_seed(31))
+    mask, value = box_cond(H)
+    ref = O.p_sample_loop(sd, O.make_schedule(n), noise[:, rows].contiguous(), mask=mask, value=value)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=dm.InjectedNoise(noise),
+                             conditioning_fn=box_holding)
+    assert diff.last_launch_count == 1
+    chain = out.chains[rows].cpu()
+    for k in range(n + 1):
+        assert rel(chain[:, k], ref[:, k]) < REL_STEP, k
+    m = mask.expand(len(rows), H, 35)
+    assert torch.equal(chain[:, -1][m], ref[:, -1][m])
+
+
 def test_ddpm_step_kernel_matches_oracle(dm):
     """K4 alone through dm_ddpm_step, both parameterisations, with clamp and a per-sample mask."""
     import ctypes
@@ -598,6 +643,17 @@ def test_on_device_loader_matches_oracle(dm, golden_dir, tmp_path):
         assert np.abs(ds.motion_data.cpu().numpy() - ref).max() <= 2.4e-7 * max(1.0, np.abs(ref).max())
         b = ds[3]
         assert torch.equal(b.conditions[0], b.trajectories[0]) and torch.equal(ds[0].trajectories[3], b.trajectories[0])
+        # velocity rows (dm_mocap_to_qvel): one fp32 ulp of each value, relative to the row's scale
+        gv = MD.mocap_qvel_on_device(frames, torch.device("cuda")).cpu().numpy()
+        wv = z[name + "_vel"].astype(np.float32)
+        assert gv.shape == wv.shape and not gv[0].any()
+        assert (np.abs(gv - wv) <= 1.2e-7 * np.maximum(1.0, np.abs(wv)) + 1e-6 * 0).all() or \
+            np.abs(gv - wv).max() <= 2.4e-7 * max(1.0, np.abs(wv).max())
+        ds2 = MD.MotionDatasetV2(str(path), device="cuda")
+        row = ds2[0].trajectories
+        assert row.is_cuda and tuple(row.shape) == (frames.shape[0], 69) and int(ds2[0].motion_class) == MD.MOTION_CLASSES[f"humanoid3d_{name}"]
+        want69 = LO.motion_dataset_v2_rows(frames)
+        assert np.abs(row.cpu().numpy() - want69).max() <= 2.4e-7 * max(1.0, np.abs(want69).max())
 
 
 def test_scoring_edge_sizes(dm):

@@ -31,6 +31,55 @@ def test_product_loader_matches_oracle(golden_dir):
         np.testing.assert_allclose(got, z[name + "_config"], rtol=0, atol=1e-12)
 
 
+def test_velocity_rows_oracle_fixture_and_product(golden_dir):
+    """data_vel (utils/mocap_v2.py:196-291, calc_rot_vel :155-178): oracle == fixture, product host code == oracle, and
+    properties the reference arithmetic implies: row 0 is zero, linear / hinge rates are finite differences over the
+    PREVIOUS frame's duration, and angle * axis rotates frame k's root orientation onto frame k-1's."""
+    z = clips(golden_dir)
+    for name in ["walk", "cartwheel", "spinkick"]:
+        fr = z[name + "_frames"]
+        vel = LO.data_vel_from_frames(fr)
+        assert vel.shape == (fr.shape[0], 34)
+        np.testing.assert_allclose(vel, z[name + "_vel"], rtol=0, atol=1e-12)
+        np.testing.assert_allclose(MD.mocap_to_qvel(fr), z[name + "_vel"], rtol=0, atol=1e-11)
+        assert not vel[0].any()
+        cfg = z[name + "_config"]
+        dura = fr[:-1, 0]
+        np.testing.assert_allclose(vel[1:, :3], (cfg[1:, :3] - cfg[:-1, :3]) / dura[:, None], atol=1e-12)
+        for qpos_i, qvel_i in [(16, 15), (20, 19), (24, 23), (31, 30)]:      # elbows, knees: hinge rates
+            np.testing.assert_allclose(vel[1:, qvel_i], (cfg[1:, qpos_i] - cfg[:-1, qpos_i]) / dura, atol=1e-12)
+        k = 5
+        rv = vel[k, 3:6] * dura[k - 1]
+        ang = np.linalg.norm(rv)
+        half = np.concatenate([[np.cos(ang / 2)], np.sin(ang / 2) * rv / ang])
+        q_prev = LO.quat_mul(cfg[k, 3:7], half)                                  # q_k * q_diff == q_{k-1}
+        want = cfg[k - 1, 3:7] / np.linalg.norm(cfg[k - 1, 3:7])                 # the clip's quaternions are unit to ~1e-7
+        q_prev = q_prev / np.linalg.norm(q_prev)
+        np.testing.assert_allclose(q_prev * np.sign(q_prev[0]), want * np.sign(want[0]), atol=1e-9)
+
+
+def test_motion_dataset_v2_semantics(golden_dir, tmp_path):
+    """data_loaders/motion_dataset_v2.py: 69-wide rows (qpos | qvel), motion class from the file name, 1000 copies
+    (shuffle=False) or root-continuous cyclic shifts (shuffle=True)."""
+    z = clips(golden_dir)
+    path = tmp_path / "humanoid3d_spinkick.txt"
+    path.write_text(json.dumps({"Loop": "wrap", "Frames": z["spinkick_frames"].tolist()}))
+    ds = MD.MotionDatasetV2(str(path))
+    ref = LO.motion_dataset_v2_rows(z["spinkick_frames"])
+    assert len(ds) == 1000 and ds.max_sequence_length == 78
+    b = ds[3]
+    assert int(b.motion_class) == 2 and b.trajectories.shape == (78, 69)
+    assert torch.equal(b.trajectories, torch.from_numpy(ref))
+    assert torch.equal(ds.get_conditions(b.trajectories)[0], b.trajectories[0])
+    sh = MD.MotionDatasetV2(str(path), shuffle=True)
+    ref_sh = LO.motion_dataset_v2_shuffled(z["spinkick_frames"])
+    assert len(sh) == 78
+    for i in (0, 1, 40, 77):
+        assert torch.equal(sh[i].trajectories, torch.from_numpy(ref_sh[i])), i
+    batch = sh.collate_fn([sh[0], sh[5]])
+    assert batch.trajectories.is_nested and batch.motion_class.tolist() == [2, 2]
+
+
 def test_motion_dataset_semantics(golden_dir, tmp_path):
     z = clips(golden_dir)
     path = tmp_path / "humanoid3d_walk.txt"
