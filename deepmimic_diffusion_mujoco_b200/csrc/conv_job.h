@@ -22,11 +22,11 @@ constexpr int kMmaWarp = 17;        // one elected lane issues tcgen05.mma; the 
 constexpr int kMmaWarpB = 18;       // second MMA issuer: one thread alone cannot keep the tensor pipe busy (see mma_unit)
 constexpr int kConvThreads = (kEpiWarps + 3) * 32;
 
-struct ConvTap {
-  int wtap;    // index into the packed weight's tap dimension
-  int shift;   // l offset of this tap's view inside the A box (in l positions)
-  int phase;   // accumulator set (ConvTranspose: 0 = even outputs, 1 = odd outputs)
-  int first;   // 1 if this is the first tap accumulated into its phase
+struct ConvTap {       // bytes: 80 of these descriptors travel as ONE kernel parameter block (32 KB limit)
+  signed char wtap;    // index into the packed weight's tap dimension
+  signed char shift;   // l offset of this tap's view inside the A box (in l positions)
+  signed char phase;   // accumulator set (ConvTranspose: 0 = even outputs, 1 = odd outputs)
+  signed char first;   // 1 if this is the first tap accumulated into its phase
 };
 
 enum { EPI_BIAS = 0, EPI_GN_MISH = 1 };
@@ -34,10 +34,10 @@ enum { EPI_BIAS = 0, EPI_GN_MISH = 1 };
 // TMA descriptors of one layer; they live in global memory (or in a __grid_constant__ kernel parameter).
 struct ConvMaps {
   CUtensorMap a_map[2];   // 5-D (C, 16, L, G, plane) fp16, one per input source (2 = channel concat)
-  CUtensorMap w_map;      // 4-D (CinTot, CoutPad, ntaps, plane) fp16
+  CUtensorMap w_map;      // 5-D (Cc, CoutPad, chunk, ntaps, plane) fp16: chunk-major, a tile is one contiguous block per plane
   CUtensorMap o_map;      // 5-D store map of the output activation (box = one staged plane x channel block)
   CUtensorMap r_map;      // 5-D load map of the residual activation, same box as o_map
-  CUtensorMap x_map;      // 4-D weights of the fused auxiliary 1x1 conv (the block's residual_conv), box as w_map
+  CUtensorMap x_map;      // 5-D weights of the fused auxiliary 1x1 conv (the block's residual_conv), layout and box as w_map
   CUtensorMap p_map;      // 5-D store map of the auxiliary output activation, same box as o_map
 };
 
@@ -109,6 +109,8 @@ struct ConvJob {
   int sync_local;         // the next layer only reads what THIS CTA wrote (both layers S = 8): block barrier, no cluster barrier
   int pre_next;           // weight loads of the NEXT layer's first chunk the producer may issue during this epilogue
   int next_res;           // the next layer reads this layer's staged tile in place (zero the gaps, defer the store wait)
+  int no_store;           // fused loop only: the resident consumer is the ONLY reader of this layer's output, so the tile
+                          // never leaves shared memory (no TMA store to the global activation planes)
   // auxiliary 1x1 conv sharing this layer's A operand (ResidualTemporalBlock.residual_conv, temporal.py:34-35,46):
   // one extra weight tile per channel chunk, accumulated into its own TMEM columns, bias-only epilogue
   int aux;                // 1 if present

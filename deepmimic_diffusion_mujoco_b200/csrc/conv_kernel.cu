@@ -61,6 +61,7 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full, res_full;
+  uint64_t tile_ready;   // resident link: the previous layer's staged tile is complete (one arrival, by epilogue thread 0)
   uint32_t tmem_slot;
   alignas(16) float par[5][256];        // bias, gamma, beta, time bias, auxiliary-conv bias of this unit's Nc channels
   alignas(16) unsigned char qgrp[64];   // GroupNorm group (within the unit) of every 4-channel quad
@@ -74,7 +75,7 @@ struct ConvShared {
 // used; producer and MMA issuer walk the same stage sequence, so their private copies stay in step even
 // though ring depths change from layer to layer inside the persistent kernel.
 struct RoleState {
-  uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0;
+  uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0, tile_count = 0;
   int pre_w = 0;   // producer: weight loads of the current unit that were already issued during the previous epilogue
 };
 
@@ -83,6 +84,7 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
   for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], 2); }
   mbar_init(&sh.acc_full, 2);
   mbar_init(&sh.res_full, 1);
+  mbar_init(&sh.tile_ready, 1);
   fence_barrier_init();
 }
 
@@ -97,7 +99,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
   if (leader) trace_mark<TR>(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
-    int cin_off = 0;
+    int chunk0 = 0;   // index of the source's first channel chunk inside the concatenated input (weights are chunk-major)
     for (int src = 0; src < job.nsrc; ++src) {
       const int nch = job.src_chunks[src];
       for (int ch = 0; ch < nch; ++ch) {
@@ -116,8 +118,8 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
             mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
             if (leader) {
               mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
-              tma_load_4d(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws],
-                          cin_off + ch * job.Cc, n0, t < job.ntaps ? job.taps[t].wtap : 0, 0);
+              tma_load_5d(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws], 0, n0,
+                          chunk0 + ch, t < job.ntaps ? job.taps[t].wtap : 0, 0);
 #ifdef DM_TRACE_WLOADS
               if (tr && wi < 24) trace_mark<TR>(tr, 16 + 2 * wi);
 #endif
@@ -129,13 +131,16 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
         }
         if (!job.a_res && ++as == job.n_a_stages) as = 0;
       }
-      cin_off += nch * job.Cc;
+      chunk0 += nch;
     }
   }
   if (leader) trace_mark<TR>(tr, 4);
   // Weight prefetch across the layer boundary: weights do not depend on activations.  Once this unit's MMAs
   // have all completed (its operand stages are dead), the first weight tiles of the next layer are loaded into
   // that layer's ring slots that lie beyond this layer's staged output tile; they land during the epilogue.
+  // A resident link has no block barrier behind it (the roles run ahead, see sample_loop_kernel): this warp may only
+  // touch the next layer's ring once this layer's MMAs have completed, whether or not it prefetches.
+  if (job.next_res && !(nj != nullptr && job.pre_next > 0)) mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x710);
   if (nj != nullptr && job.pre_next > 0) {
     mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x700);
     const uint32_t nw_smem = smem_base + (uint32_t)(nj->a_res ? nj->w_off_res : nj->n_a_stages * nj->a_stage_bytes);
@@ -143,7 +148,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
       mbar_wait(&sh.w_empty[i], ((rs.w_bits >> i) & 1) ^ 1, 0x780 + i);
       if (leader) {
         mbar_arrive_expect_tx(&sh.w_full[i], nj->w_tx_bytes);
-        tma_load_4d(nw_smem + i * nj->w_stage_bytes, n_w_map, &sh.w_full[i], 0, n_n0, nj->taps[i].wtap, 0);
+        tma_load_5d(nw_smem + i * nj->w_stage_bytes, n_w_map, &sh.w_full[i], 0, n_n0, 0, nj->taps[i].wtap, 0);
       }
       rs.w_bits ^= 1u << i;
     }
@@ -193,6 +198,13 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
         if (!job.a_res) {
           mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
           rs.a_bits ^= 1u << as;
+          tc_fence_after();
+        } else if (lt == 0 && cidx == 0) {
+          // resident link: this warp ran ahead of the previous layer's epilogue (descriptors and loop state are set up,
+          // the first weight tiles were prefetched); the tile it reads in place -- and the TMEM columns it overwrites --
+          // are handed over by ONE mbarrier arrival instead of a block barrier
+          mbar_wait(&sh.tile_ready, rs.tile_count & 1, 0x310);
+          rs.tile_count++;
           tc_fence_after();
         }
         if (leader && lt == 0 && cidx == 0) trace_mark<TR>(tr, 5);
@@ -681,9 +693,11 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       }
     }
     fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine / next MMAs
+    tc_fence_before();                    // this thread's TMEM reads are complete before the hand-over below
     named_bar_sync(1, kEpiThreads);
+    if (job.next_res && threadIdx.x == 0) mbar_arrive(&sh.tile_ready);   // releases the MMA warps waiting in the next layer
     trace_mark<TR>(tr, 15);
-    if (tid == 0) {
+    if (tid == 0 && !job.no_store) {
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
           tma_store_5d(&maps->o_map, stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0, 0,
@@ -833,10 +847,14 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
           }
         }
         if (threadIdx.x == 0) trace_mark<TR>(tr, 12);
-        if (job.next_res) {   // CTA-local hand-over of the staged tile (writers fenced the async proxy already)
+        if (job.next_res) {
+          // resident link: NO barrier.  The consumer is this CTA's next layer; its MMA warps wait on sh.tile_ready, its
+          // producer waited for this layer's accumulator, its epilogue warps are the threads that just finished.
+#ifdef DM_NO_RUNAHEAD   // A/B aid: the old block-wide hand-over
           tc_fence_before();
           __syncthreads();
           tc_fence_after();
+#endif
         } else if (job.sync_local) {
           local_sync(warp < kEpiWarps && job.st_cw == 0, warp == kProducerWarp);
         } else {

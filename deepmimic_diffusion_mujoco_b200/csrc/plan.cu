@@ -159,6 +159,8 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   memset(&ly.maps, 0, sizeof(ly.maps));
   ly.name = sp.name;
   ly.tb_off = sp.tb_off;
+  for (int s = 0; s < sp.nsrc; ++s) ly.src_acts[s] = sp.src[s];
+  ly.res_act = sp.res;
 
   const Act& a0 = P->acts[sp.src[0]];
   const int Lin = a0.L;
@@ -223,7 +225,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     j.taps[3] = {0, 2, 1, 0};
   } else {
     j.ntaps = ktaps;
-    for (int t = 0; t < ktaps; ++t) j.taps[t] = {t, t, 0, t == 0 ? 1 : 0};
+    for (int t = 0; t < ktaps; ++t) j.taps[t] = {(signed char)t, (signed char)t, 0, (signed char)(t == 0 ? 1 : 0)};
   }
 
   // N split and TMEM budget
@@ -275,7 +277,9 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   j.n_w_stages = nw;
   ly.smem = (size_t)j.n_a_stages * j.a_stage_bytes + (size_t)nw * j.w_stage_bytes + 1024;
 
-  // ---- pack weights: planes [2][ktaps][cout_pad][cin_tot] fp16, zero padded ----
+  // ---- pack weights: planes [2][ktaps][chunk][cout_pad][Cc] fp16, zero padded.  Chunk-major: the Nc x Cc tile one
+  //      TMA load fetches is ONE contiguous block per plane (rows 128 / 64 bytes apart), not Nc pieces strided by the
+  //      layer's full input width ----
   const float* wsrc = nullptr;
   int rc;
   if (sp.kind == CONV_T4) rc = find_w(W, sp.wkey + ".weight", {cin_real, sp.Cout, ktaps}, &wsrc);
@@ -283,7 +287,11 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (rc) return rc;
   const float* bsrc = nullptr;
   if ((rc = find_w(W, sp.wkey + ".bias", {sp.Cout}, &bsrc))) return rc;
+  const int n_chunks_tot = cin_tot / j.Cc;
   const size_t wplane = (size_t)ktaps * cout_pad * cin_tot;
+  auto w_index = [&](int k, int co, int col) {   // col: channel position inside the concatenated, padded input
+    return (((size_t)k * n_chunks_tot + col / j.Cc) * cout_pad + co) * j.Cc + col % j.Cc;
+  };
   std::vector<__half> wp(2 * wplane, __float2half_rn(0.f));
   {
     int col0 = 0, real0 = 0;
@@ -296,7 +304,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
                                                : wsrc[((size_t)co * cin_real + cr) * ktaps + k];
             const __half hi = __float2half_rn(v);
             const __half lo = __float2half_rn(v - __half2float(hi));
-            const size_t o = ((size_t)k * cout_pad + co) * cin_tot + col0 + ci;
+            const size_t o = w_index(k, co, col0 + ci);
             wp[o] = hi;
             wp[wplane + o] = lo;
           }
@@ -310,10 +318,11 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if ((rc = dev_alloc(P, reinterpret_cast<void**>(&wdev), wp.size() * sizeof(__half), false))) return rc;
   DM_CUDA(cudaMemcpy(wdev, wp.data(), wp.size() * sizeof(__half), cudaMemcpyHostToDevice));
   {
-    const uint64_t dims[4] = {(uint64_t)cin_tot, (uint64_t)cout_pad, (uint64_t)ktaps, 2};
-    const uint64_t str[3] = {(uint64_t)cin_tot * 2, (uint64_t)cin_tot * cout_pad * 2, (uint64_t)wplane * 2};
-    const uint32_t box[4] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 2};
-    if ((rc = encode_map(&ly.maps.w_map, wdev, 4, dims, str, box, j.swz))) return rc;
+    const uint64_t dims[5] = {(uint64_t)j.Cc, (uint64_t)cout_pad, (uint64_t)n_chunks_tot, (uint64_t)ktaps, 2};
+    const uint64_t str[4] = {(uint64_t)j.Cc * 2, (uint64_t)cout_pad * j.Cc * 2, (uint64_t)cin_tot * cout_pad * 2,
+                             (uint64_t)wplane * 2};
+    const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 1, 2};
+    if ((rc = encode_map(&ly.maps.w_map, wdev, 5, dims, str, box, j.swz))) return rc;
   }
   for (int s = 0; s < sp.nsrc; ++s) {
     const Act& a = P->acts[sp.src[s]];
@@ -424,8 +433,9 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
         for (int co = 0; co < sp.Cout; ++co) {
           const float v = xw[(size_t)co * cin_real + real0 + ci];
           const __half hi = __float2half_rn(v);
-          xp[(size_t)co * cin_tot + col0 + ci] = hi;
-          xp[xplane + (size_t)co * cin_tot + col0 + ci] = __float2half_rn(v - __half2float(hi));
+          const size_t o = w_index(0, co, col0 + ci);   // same chunk-major tile layout as the main weights, one tap
+          xp[o] = hi;
+          xp[xplane + o] = __float2half_rn(v - __half2float(hi));
         }
       col0 += P->acts[sp.src[s]].C;
       real0 += sp.src_real_c[s];
@@ -434,10 +444,11 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     if ((rc = dev_alloc(P, reinterpret_cast<void**>(&xdev), xp.size() * sizeof(__half), false))) return rc;
     DM_CUDA(cudaMemcpy(xdev, xp.data(), xp.size() * sizeof(__half), cudaMemcpyHostToDevice));
     {
-      const uint64_t dims[4] = {(uint64_t)cin_tot, (uint64_t)cout_pad, 1, 2};
-      const uint64_t str[3] = {(uint64_t)cin_tot * 2, (uint64_t)cin_tot * cout_pad * 2, (uint64_t)xplane * 2};
-      const uint32_t box[4] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 2};
-      if ((rc = encode_map(&ly.maps.x_map, xdev, 4, dims, str, box, j.swz))) return rc;
+      const uint64_t dims[5] = {(uint64_t)j.Cc, (uint64_t)cout_pad, (uint64_t)n_chunks_tot, 1, 2};
+      const uint64_t str[4] = {(uint64_t)j.Cc * 2, (uint64_t)cout_pad * j.Cc * 2, (uint64_t)cin_tot * cout_pad * 2,
+                               (uint64_t)xplane * 2};
+      const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 1, 2};
+      if ((rc = encode_map(&ly.maps.x_map, xdev, 5, dims, str, box, j.swz))) return rc;
     }
     std::vector<float> hxb(cout_pad, 0.f);
     for (int c = 0; c < sp.Cout; ++c) hxb[c] = xb[c];
@@ -747,6 +758,19 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
   for (size_t i = 0; i + 1 < P->layers.size(); ++i)
       P->layers[i].job.sync_local = P->layers[i].job.S == 8 && P->layers[i + 1].job.S == 8;
   if (tb != P->TB) return fail(DM_ERR_ARG, "internal: time-bias layout mismatch (%d vs %d)", tb, P->TB);
+  // An output tile whose only reader is the next layer's in-place (resident) read never has to reach global memory.
+  for (size_t i = 0; i + 1 < P->layers.size(); ++i) {
+    Layer& ly = P->layers[i];
+    if (ly.kind != 0 || !ly.job.next_res || ly.out_act < 0) continue;
+    int readers = 0;
+    for (size_t k = 0; k < P->layers.size(); ++k) {
+      const Layer& c = P->layers[k];
+      if (c.kind == 1) { if (c.attn.in == P->acts[ly.out_act].p) ++readers; continue; }
+      for (int s = 0; s < 2; ++s) readers += c.src_acts[s] == ly.out_act;
+      readers += c.res_act == ly.out_act;
+    }
+    if (readers == 1 && P->layers[i + 1].src_acts[0] == ly.out_act) ly.job.no_store = 1;
+  }
 
   // time MLP parameters
   const float *w1, *b1, *w2, *b2;
@@ -797,6 +821,7 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
     if (j.out_f32) j.out_f32 = out_f32;
     j.a_res = 0;       // per-layer launches always go through global memory
     j.next_res = 0;
+    j.no_store = 0;
     j.pre_next = 0;
     j.sync_local = 0;
     DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));

@@ -30,6 +30,8 @@ struct Layer {
   int tb_off = -1;       // offset into a time-bias row, or -1
   int out_act = -1;      // index into acts (for dm_plan_read_layer), -1 if fp32-only
   int aux_act = -1;      // output of the fused auxiliary 1x1 conv, -1 if none
+  int src_acts[2] = {-1, -1};   // activations this layer reads as conv input ...
+  int res_act = -1;             // ... and as residual (consumer bookkeeping for ConvJob::no_store)
   std::string name;
 };
 

@@ -60,6 +60,7 @@ struct LoopParams {
   unsigned long long* trace;  // debug: [n_jobs][16] globaltimer stamps of one (cluster, step); null in production
   int trace_cluster, trace_step;
 };
+static_assert(sizeof(LoopParams) <= 32764, "LoopParams is a kernel parameter: 32764 bytes at most (shrink ConvJob or kMaxLoopJobs)");
 cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStream_t stream);
 
 cudaError_t launch_time_bias(const TimeMlpParams& p, const float* t_dev, int nt, float* out, cudaStream_t s);
