@@ -14,11 +14,11 @@
 
 namespace dm {
 
-constexpr int kGroupSamples = 16;   // samples per activation group: layout [plane][G][L][16][C] fp16
+constexpr int kGroupSamples = 16;   // samples per activation group: layout [plane][G][L][16][C] fp16; one CTA PAIR per group
 constexpr int kMaxTaps = 5;
 constexpr int kEpiWarps = 16;       // epilogue warps 0-15: TMEM lane quarter = warp % 4, work slice = warp / 4
 constexpr int kProducerWarp = 16;   // one elected lane issues TMA
-constexpr int kMmaWarp = 17;        // one elected lane issues tcgen05.mma; the warp owns the TMEM allocation
+constexpr int kMmaWarp = 17;        // one elected lane (leader CTA only) issues tcgen05.mma.cta_group::2; the warp owns the TMEM allocation
 constexpr int kMmaWarpB = 18;       // second MMA issuer: one thread alone cannot keep the tensor pipe busy (see mma_unit)
 constexpr int kConvThreads = (kEpiWarps + 3) * 32;
 
@@ -50,22 +50,25 @@ struct ConvJob {
   int row_bytes;          // Cc * 2
   int ksteps;             // k-steps (16 channels) issued per chunk: Cc / 16, less when the only chunk is zero padded
   int swz;                // UMMA layout code (2 = 128B, 4 = 64B)
-  int S;                  // samples per CTA: 8 or 16
+  int S;                  // samples per CTA: always 8 (CTA r of the pair owns samples 8r .. 8r+7 of the group)
+  int mrows;              // GEMM rows per CTA per MMA: 128 (tcgen05.mma.cta_group::2 with M = 256) or 64 (M = 128, L <= 8 layers)
+  int ncols;              // TMEM columns of one M tile of one accumulator set: Nc (mrows 128) or Nc / 2 (mrows 64: the
+                          // pair MMA puts channels [0, Nc/2) on lanes 0-63 and [Nc/2, Nc) on lanes 64-127)
   int l_stride;           // 1, or 2 for the strided down-sampling conv
   int halo_lo;            // A box starts at l = l_stride * j0 - halo_lo
   int box_l;              // l positions in the A box
-  int Lt;                 // M positions (j) per l-tile; Lt * S is a multiple of 128
+  int Lt;                 // M positions (j) per l-tile; Lt * S is a multiple of mrows
   int n_ltiles;
-  int Mt;                 // 128-row MMA tiles per l-tile
+  int Mt;                 // MMA tiles (mrows rows per CTA) per l-tile
   int Lj;                 // number of valid M positions (Lout, or Lin for ConvTranspose)
   int Lout;               // output length
   int ntaps;
   ConvTap taps[kMaxTaps];
   int nphase;
-  int Nc;                 // output channels per CTA == MMA N
+  int Nc;                 // output channels per unit == MMA N; each CTA of the pair stages Nc / 2 rows of every weight tile
   int n_a_stages, n_w_stages;
   int a_stage_bytes, w_stage_bytes, a_plane_bytes, w_plane_bytes;
-  int a_tx_bytes, w_tx_bytes;
+  int a_tx_bytes, w_tx_bytes;   // bytes ONE CTA's loads deliver per stage (the leader's barrier expects twice that)
   int tmem_cols;
   int mma_mode;           // 0: warp A issues every MMA; 1: the two issuer warps split the k-steps of every tap, each
                           // with its own accumulator set (see mma_unit)

@@ -61,7 +61,7 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full, res_full;
-  uint64_t tile_ready;   // resident link: the previous layer's staged tile is complete (one arrival, by epilogue thread 0)
+  uint64_t tile_ready;   // resident link (leader CTA's copy is the live one): both CTAs' staged tiles are complete
   uint32_t tmem_slot;
   alignas(16) float par[5][256];        // bias, gamma, beta, time bias, auxiliary-conv bias of this unit's Nc channels
   alignas(16) unsigned char qgrp[64];   // GroupNorm group (within the unit) of every 4-channel quad
@@ -84,17 +84,23 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
   for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], 2); }
   mbar_init(&sh.acc_full, 2);
   mbar_init(&sh.res_full, 1);
-  mbar_init(&sh.tile_ready, 1);
+  mbar_init(&sh.tile_ready, 2);   // one arrival from each CTA of the pair (the peer's is remote)
   fence_barrier_init();
 }
 
-// ================================ TMA producer (one warp, one elected lane issues) =========================
+// ================================ TMA producer (one warp per CTA, one elected lane issues) ==================
+// Both CTAs of the pair run this loop: each loads ITS samples' activation rows and ITS half of every weight tile into
+// its own shared memory.  The bytes of both CTAs are counted on the LEADER's full barriers (the leader's MMA warps are
+// the only waiters): the leader arms them with arrive.expect_tx for twice its own byte count, the peer only issues its
+// loads.  Stage reuse is gated per CTA by its own empty barriers, which the MMA commits signal in both CTAs.
 template <bool TR>
 __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
-                                              const CUtensorMap* x_map, int g, int b0, int n0, uint32_t a_smem, uint32_t w_smem, ConvShared& sh,
-                                              RoleState& rs, unsigned long long* tr, uint32_t smem_base,
-                                              const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0) {
+                                              const CUtensorMap* x_map, int g, int b0, int n0, int rank, uint32_t a_smem,
+                                              uint32_t w_smem, ConvShared& sh, RoleState& rs, unsigned long long* tr,
+                                              uint32_t smem_base, const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0) {
   const bool leader = elect_one_sync();
+  const bool arm = leader && rank == 0;
+  const int wn0 = n0 + rank * (job.Nc >> 1);          // this CTA's rows of the weight tile
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
@@ -105,10 +111,9 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
       for (int ch = 0; ch < nch; ++ch) {
         if (!job.a_res) {
           mbar_wait(&sh.a_empty[as], ((rs.a_bits >> as) & 1) ^ 1, 0x100 + as);
-          if (leader) {
-            mbar_arrive_expect_tx(&sh.a_full[as], job.a_tx_bytes);
-            tma_load_5d(a_smem + as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
-          }
+          if (arm) mbar_arrive_expect_tx(&sh.a_full[as], 2u * job.a_tx_bytes);
+          if (leader)
+            tma_load_5d_pair(a_smem + as * job.a_stage_bytes, &a_maps[src], &sh.a_full[as], ch * job.Cc, b0, lstart, g, 0);
           rs.a_bits ^= 1u << as;
         }
         for (int t = 0; t < job.ntaps + job.aux; ++t) {   // the auxiliary 1x1 weights ride the same ring as one more tap
@@ -116,10 +121,10 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
             --rs.pre_w;            // issued during the previous layer's epilogue
           } else {
             mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
+            if (arm) mbar_arrive_expect_tx(&sh.w_full[ws], 2u * job.w_tx_bytes);
             if (leader) {
-              mbar_arrive_expect_tx(&sh.w_full[ws], job.w_tx_bytes);
-              tma_load_5d(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws], 0, n0,
-                          chunk0 + ch, t < job.ntaps ? job.taps[t].wtap : 0, 0);
+              tma_load_5d_pair(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws], 0, wn0,
+                               chunk0 + ch, t < job.ntaps ? job.taps[t].wtap : 0, 0);
 #ifdef DM_TRACE_WLOADS
               if (tr && wi < 24) trace_mark<TR>(tr, 16 + 2 * wi);
 #endif
@@ -135,21 +140,21 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
     }
   }
   if (leader) trace_mark<TR>(tr, 4);
-  // Weight prefetch across the layer boundary: weights do not depend on activations.  Once this unit's MMAs
-  // have all completed (its operand stages are dead), the first weight tiles of the next layer are loaded into
-  // that layer's ring slots that lie beyond this layer's staged output tile; they land during the epilogue.
   // A resident link has no block barrier behind it (the roles run ahead, see sample_loop_kernel): this warp may only
   // touch the next layer's ring once this layer's MMAs have completed, whether or not it prefetches.
   if (job.next_res && !(nj != nullptr && job.pre_next > 0)) mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x710);
+  // Weight prefetch across the layer boundary: weights do not depend on activations.  Once this unit's MMAs
+  // have all completed (its operand stages are dead), the first weight tiles of the next layer are loaded into
+  // that layer's ring slots that lie beyond this layer's staged output tile; they land during the epilogue.
   if (nj != nullptr && job.pre_next > 0) {
     mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x700);
     const uint32_t nw_smem = smem_base + (uint32_t)(nj->a_res ? nj->w_off_res : nj->n_a_stages * nj->a_stage_bytes);
     for (int i = 0; i < job.pre_next; ++i) {
       mbar_wait(&sh.w_empty[i], ((rs.w_bits >> i) & 1) ^ 1, 0x780 + i);
-      if (leader) {
-        mbar_arrive_expect_tx(&sh.w_full[i], nj->w_tx_bytes);
-        tma_load_5d(nw_smem + i * nj->w_stage_bytes, n_w_map, &sh.w_full[i], 0, n_n0, 0, nj->taps[i].wtap, 0);
-      }
+      if (arm) mbar_arrive_expect_tx(&sh.w_full[i], 2u * nj->w_tx_bytes);
+      if (leader)
+        tma_load_5d_pair(nw_smem + i * nj->w_stage_bytes, n_w_map, &sh.w_full[i], 0, n_n0 + rank * (nj->Nc >> 1), 0,
+                         nj->taps[i].wtap, 0);
       rs.w_bits ^= 1u << i;
     }
     rs.pre_w = job.pre_next;
@@ -158,17 +163,22 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
   __syncwarp();
 }
 
-// ================================ MMA issuers (two warps, one elected lane each) ===========================
+// ================================ MMA issuers (leader CTA only: two warps, one elected lane each) =============
+// The MMAs are CTA-pair instructions (tcgen05.mma.cta_group::2): one instruction multiplies both CTAs' activation rows
+// (M = 2 * mrows; each CTA's rows come from its own shared memory and accumulate in its own TMEM) by a weight tile of
+// which each CTA staged half the N rows.  Per SM an MMA then reads its A rows plus HALF of B from shared memory -- the
+// single-CTA form reads all of B and is bound by the 128 B/clk shared-memory port, which the TMA writes also use.
+//
 // A single thread cannot keep the tensor pipe busy: every mbarrier poll or descriptor recomputation between two
 // taps shows up as a pipe bubble (measured: 86-110 cycles per N=128 MMA from one thread against the 64-cycle MAC
-// floor; two threads reach 64.4).  So two warps issue.  job.mma_mode:
+// floor; two threads reach 64.4).  So two warps of the leader issue.  job.mma_mode:
 //   0  warp A issues everything (B only keeps the ring bookkeeping in step);
 //   1  every tap is shared: A issues the first half of its k-steps, B the second half, each into its OWN
 //      accumulator set (B's at column job.acc2_off); the epilogue adds the two.  Every accumulator sees one
 //      thread's MMAs in program order, so results stay bit-reproducible.  The auxiliary tap (one accumulator
 //      set) is B's alone.
-// A weight stage is released (w_empty, two arrivals) by both warps; A stages and the unit's acc_full take one
-// commit from each warp as well.
+// A weight stage is released (w_empty, two arrivals, in BOTH CTAs) by both warps; A stages and the unit's acc_full
+// take one commit from each warp as well.
 template <bool TR>
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr,
@@ -176,18 +186,19 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const bool leader = elect_one_sync();
   if (which != 0) tr = nullptr;
   if (leader) trace_mark<TR>(tr, 20);
-  const int S = job.S, Nc = job.Nc;
+  const int S = job.S, Nc = job.Nc, ncols = job.ncols;
   const int MT = job.n_ltiles * job.Mt;
   const int mode = job.mma_mode;
-  const uint32_t idesc = umma_idesc_f16(128, Nc);
+  const uint32_t idesc = umma_idesc_f16(2 * job.mrows, Nc);
   const int ksteps = job.ksteps;   // 16-channel k-steps per chunk that hold real input channels (zero padding skipped)
-  const int pos_per_mt = 128 / S;
+  const int pos_per_mt = job.mrows / S;
   // descriptor high words are per-layer constants; only the 14-bit start address changes per MMA
   const uint64_t hi_a = umma_smem_desc(0, job.l_stride * 8 * job.row_bytes, job.swz);
   const uint64_t hi_w = umma_smem_desc(0, 8 * job.row_bytes, job.swz);
   const uint32_t a_plane16 = (uint32_t)(job.a_res ? job.a_res_plane : job.a_plane_bytes) >> 4;
   const uint32_t w_plane16 = job.w_plane_bytes >> 4;
   const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
+  const uint32_t peer_w_empty = mapa_u32(smem_u32(&sh.w_empty[0]), 1);   // the peer CTA's copy of the ring's empty barriers
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 21);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
@@ -196,14 +207,14 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
       const int nch = job.src_chunks[src];
       for (int ch = 0; ch < nch; ++ch, ++cidx) {
         if (!job.a_res) {
-          mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
+          mbar_wait_cluster(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
           rs.a_bits ^= 1u << as;
           tc_fence_after();
         } else if (lt == 0 && cidx == 0) {
           // resident link: this warp ran ahead of the previous layer's epilogue (descriptors and loop state are set up,
-          // the first weight tiles were prefetched); the tile it reads in place -- and the TMEM columns it overwrites --
-          // are handed over by ONE mbarrier arrival instead of a block barrier
-          mbar_wait(&sh.tile_ready, rs.tile_count & 1, 0x310);
+          // the first weight tiles were prefetched); the tiles it reads in place -- and the TMEM columns it overwrites,
+          // in both CTAs -- are handed over by one mbarrier arrival per CTA instead of a barrier
+          mbar_wait_cluster(&sh.tile_ready, rs.tile_count & 1, 0x310);
           rs.tile_count++;
           tc_fence_after();
         }
@@ -224,9 +235,12 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
           // Both warps observe every fill of every stage, in order, and the stage is not refilled before both have:
           // a parity wait may only be one phase behind the barrier, so a warp without work on a tap still waits
           // for its fill and then releases its half of w_empty (otherwise its half is the tcgen05.commit).
-          mbar_wait(&sh.w_full[ws], w_par, 0x400 + ws);
+          mbar_wait_cluster(&sh.w_full[ws], w_par, 0x400 + ws);
           if (!mine) {
-            if (leader) mbar_arrive(&sh.w_empty[ws]);
+            if (leader) {
+              mbar_arrive(&sh.w_empty[ws]);
+              mbar_arrive_remote(peer_w_empty + 8u * (uint32_t)ws);
+            }
           } else {
             tc_fence_after();
             if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark<TR>(tr, 6);
@@ -238,37 +252,37 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
             const bool first = cidx == 0 && (is_aux || job.taps[t].first != 0);
             const int k_mid = (ksteps + 1) >> 1;
             const int k0 = both && which ? k_mid : 0, k1 = both && !which ? k_mid : ksteps;
-            uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * Nc) +
+            uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * ncols) +
                          (is_aux ? (uint32_t)job.aux_col0 : which ? (uint32_t)job.acc2_off : 0u);
             uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
-            for (int mt = 0; mt < job.Mt; ++mt, d += Nc, a16 += mt_step16) {
+            for (int mt = 0; mt < job.Mt; ++mt, d += ncols, a16 += mt_step16) {
               if (leader) {
                 for (int k = k0; k < k1; ++k) {
                   const uint64_t a_hi = hi_a | ((a16 + 2 * k) & 0x3FFF);
                   const uint64_t a_lo = hi_a | ((a16 + a_plane16 + 2 * k) & 0x3FFF);
                   const uint64_t w_hi = hi_w | ((w16 + 2 * k) & 0x3FFF);
                   const uint64_t w_lo = hi_w | ((w16 + w_plane16 + 2 * k) & 0x3FFF);
-                  umma_f16(d, a_lo, w_hi, idesc, !(first && k == k0));
-                  umma_f16(d, a_hi, w_lo, idesc, 1);
-                  umma_f16(d, a_hi, w_hi, idesc, 1);
+                  umma_f16_pair(d, a_lo, w_hi, idesc, !(first && k == k0));
+                  umma_f16_pair(d, a_hi, w_lo, idesc, 1);
+                  umma_f16_pair(d, a_hi, w_hi, idesc, 1);
                 }
               }
             }
             __syncwarp();
-            if (leader) umma_commit(&sh.w_empty[ws]);
+            if (leader) umma_commit_pair(&sh.w_empty[ws]);
           }
           ++wi;
           if (++ws == job.n_w_stages) ws = 0;
         }
         if (!job.a_res) {
-          if (leader) umma_commit(&sh.a_empty[as]);
+          if (leader) umma_commit_pair(&sh.a_empty[as]);
           if (++as == job.n_a_stages) as = 0;
         }
       }
     }
   }
   if (leader) {
-    umma_commit(&sh.acc_full);
+    umma_commit_pair(&sh.acc_full);
     trace_mark<TR>(tr, 7);
   }
   __syncwarp();
@@ -375,15 +389,19 @@ __device__ __forceinline__ void staged_write(const ConvJob& job, uint32_t stg_da
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
 template <bool TR>
 __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps* maps, int warp, int g, int b0, int n0,
-                                              const float* tbias, int tbias_stride, uint32_t stg, ConvShared& sh,
+                                              int rank, const float* tbias, int tbias_stride, uint32_t stg, ConvShared& sh,
                                               uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
   const int lane = threadIdx.x & 31;
   const int tid = threadIdx.x;                 // 0..511
   if (tid != 0) tr = nullptr;
   const int S = job.S, Nc = job.Nc;
-  const int s_shift = S == 8 ? 3 : 4;
+  const int s_shift = 3;                         // S == 8
+  const int mrows = job.mrows, ncols = job.ncols;
+  // mrows 128: TMEM lane == row of the CTA's 128-row tile, all Nc channels in columns [0, Nc).  mrows 64 (M = 128 pair
+  // MMA): lanes 0-63 hold the CTA's 64 rows for channels [0, Nc/2), lanes 64-127 the same rows for channels [Nc/2, Nc).
+  const int cbase = mrows == 64 ? ((warp & 3) >> 1) * ncols : 0;   // first channel (within the unit) this warp's lanes hold
   const int MT = job.n_ltiles * job.Mt;
-  const int row = (warp & 3) * 32 + lane;      // row inside a 128-row tile == TMEM lane
+  const int row = (mrows == 64 ? (warp & 1) : (warp & 3)) * 32 + lane;      // row inside the CTA's tile
   const int slice = warp >> 2;
   const int b = row & (S - 1);
   const bool gn = job.epi == EPI_GN_MISH;
@@ -430,24 +448,24 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     __syncwarp();
   }
   const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-  const int nchunks = Nc >> 5;
+  const int nchunks = ncols >> 5;               // 32-column units per tile in this warp's lanes
   float v[32];
 
   if (job.aux) {
     // ---- auxiliary 1x1 conv (the block's residual_conv): bias only, staged and stored first; its TMA store
     //      drains while pass 1 runs, and the staging buffer is reclaimed before pass 2 writes it ----
     for (int T = 0; T < MT; ++T) {
-      const int jrow = (T * 128 + row) >> s_shift;
+      const int jrow = (T * mrows + row) >> s_shift;
       for (int cc = (slice - T * nchunks) & 3; cc < nchunks; cc += 4) {
-        tmem_ld32(trow + (uint32_t)(job.aux_col0 + T * Nc + cc * 32), v);
+        tmem_ld32(trow + (uint32_t)(job.aux_col0 + T * ncols + cc * 32), v);
         tmem_ld_wait();
         if (jrow >= job.Lj) continue;
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
-          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[4][cc * 32 + r * 4]);
+          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[4][cbase + cc * 32 + r * 4]);
           v[r * 4] += bi.x; v[r * 4 + 1] += bi.y; v[r * 4 + 2] += bi.z; v[r * 4 + 3] += bi.w;
         }
-        staged_write(job, stg_data, jrow * S + b, cc * 32, v, false);
+        staged_write(job, stg_data, jrow * S + b, cbase + cc * 32, v, false);
       }
     }
     fence_proxy_async_smem();
@@ -465,21 +483,21 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   if (gn) {
     // ---- pass 1: GroupNorm statistics over (channels of group) x (all L positions), per sample ----
     for (int T = 0; T < MT; ++T) {
-      const bool ok = ((T * 128 + row) >> s_shift) < job.Lj;
+      const bool ok = ((T * mrows + row) >> s_shift) < job.Lj;
       for (int cc = (slice - T * nchunks) & 3; cc < nchunks; cc += 4) {   // units u = T * nchunks + cc with u % 4 == slice
-        tmem_ld32(trow + (uint32_t)(T * Nc + cc * 32), v);
+        tmem_ld32(trow + (uint32_t)(T * ncols + cc * 32), v);
         tmem_ld_wait();
-        if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * Nc + cc * 32), v);
+        if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * ncols + cc * 32), v);
         float s[8], q[8];
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
-          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cc * 32 + r * 4]);
+          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cbase + cc * 32 + r * 4]);
           const float x0 = v[r * 4] + bi.x, x1 = v[r * 4 + 1] + bi.y, x2 = v[r * 4 + 2] + bi.z, x3 = v[r * 4 + 3] + bi.w;
           s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
           q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
         }
         float* pw = &sh.part[warp * 256];
-        const unsigned char* qg = &sh.qgrp[cc * 8];
+        const unsigned char* qg = &sh.qgrp[(cbase >> 2) + cc * 8];
         if (job.cg_pow2) {
           // fold 4-channel quads of the same GroupNorm group inside the thread, then recursive halving across lanes
           if (job.cg < 8) {
@@ -580,15 +598,15 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   for (int pt = 0; pt < PT; ++pt) {
     const int ph = pt >= MT ? 1 : 0;
     const int T = pt - ph * MT;
-    const int j = (T * 128 + row) >> s_shift;
+    const int j = (T * mrows + row) >> s_shift;
     const bool ok = j < job.Lj;
     const int lrow = job.nphase == 2 ? 2 * j + ph : j;
     const size_t rowoff = ((size_t)g * job.Lout + lrow) * kGroupSamples + b0 + b;
     for (int cc = (slice - pt * nchunks) & 3; cc < nchunks; cc += 4) {
-      const int cb = cc * 32;
-      tmem_ld32(trow + (uint32_t)(pt * Nc + cc * 32), v);
+      const int cb = cbase + cc * 32;
+      tmem_ld32(trow + (uint32_t)(pt * ncols + cc * 32), v);
       tmem_ld_wait();
-      if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + pt * Nc + cc * 32), v);
+      if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + pt * ncols + cc * 32), v);
       if (!ok) continue;
       if (gn) {
         const float* trow_tab = &sh.part[b * (2 * Nc + 4) + 2 * cb];
@@ -695,7 +713,10 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine / next MMAs
     tc_fence_before();                    // this thread's TMEM reads are complete before the hand-over below
     named_bar_sync(1, kEpiThreads);
-    if (job.next_res && threadIdx.x == 0) mbar_arrive(&sh.tile_ready);   // releases the MMA warps waiting in the next layer
+    if (job.next_res && threadIdx.x == 0) {   // releases the leader's MMA warps waiting in the next layer (one arrival per CTA)
+      if (rank == 0) mbar_arrive(&sh.tile_ready);
+      else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), 0));
+    }
     trace_mark<TR>(tr, 15);
     if (tid == 0 && !job.no_store) {
       for (int p = 0; p < 2; ++p)
@@ -714,21 +735,42 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
 }
 
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
+// rank = this CTA's rank in its pair: it owns samples b0 = 8 * rank .. of group g.
 template <bool TR>
-__device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp,
-                                         int g, int b0, int n0, const float* tbias, int tbias_stride, uint32_t smem,
+__device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp, int rank,
+                                         int g, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
                                          unsigned long long* tr = nullptr, const ConvJob* nj = nullptr,
                                          const CUtensorMap* n_w_map = nullptr, int n_n0 = 0) {
   const uint32_t a_smem = smem;
   const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
+  const int b0 = rank * 8;
   if (warp == kProducerWarp) {
-    producer_unit<TR>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
+    producer_unit<TR>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, rank, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
   } else if (warp == kMmaWarp || warp == kMmaWarpB) {
-    mma_unit<TR>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);
+    if (rank == 0) mma_unit<TR>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
   } else {
-    epilogue_unit<TR>(job, maps, warp, g, b0, n0, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
+    epilogue_unit<TR>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
+}
+
+// Pair set-up / tear-down shared by both kernels: barriers of both CTAs exist before any remote arrival or pair TMA can
+// target them, and nobody frees TMEM or leaves while the leader's MMAs may still read the peer's shared memory.
+__device__ __forceinline__ uint32_t pair_begin(ConvShared& sh, int warp, uint32_t tmem_cols) {
+  if (threadIdx.x == 0) init_shared(sh);
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_alloc_pair(&sh.tmem_slot, tmem_cols);
+  tc_fence_before();
+  __syncwarp();
+  cluster_sync_all();
+  tc_fence_after();
+  return sh.tmem_slot;
+}
+__device__ __forceinline__ void pair_end(int warp, uint32_t tmem_base, uint32_t tmem_cols) {
+  tc_fence_before();
+  __syncwarp();
+  cluster_sync_all();
+  if (warp == kMmaWarp) tmem_dealloc_pair(tmem_base, tmem_cols);
 }
 
 // 1024-byte aligned start of the dynamic shared memory, as a shared-window address (warp-uniform)
@@ -738,31 +780,24 @@ __device__ __forceinline__ uint32_t aligned_dyn_smem() {
 }
 
 // ------------------------------------------------------------------------------------------------
-// per-layer launch: grid = (groups * 16/S, N slices)
+// per-layer launch: grid = (2 CTAs per 16-sample group, N slices), clusters of 2 along x (the CTA pair)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvJob job) {
   const uint32_t smem = aligned_dyn_smem();
   __shared__ ConvShared sh;
   const int warp = warp_idx_sync();
-  const int subs = kGroupSamples / job.S;
-  if (threadIdx.x == 0) init_shared(sh);
+  const int rank = (int)cluster_ctarank();
   if (warp == kProducerWarp && elect_one_sync()) {
     tma_prefetch_desc(&maps.a_map[0]);
     if (job.nsrc > 1) tma_prefetch_desc(&maps.a_map[1]);
     tma_prefetch_desc(&maps.w_map);
   }
-  if (warp == kMmaWarp) tmem_alloc(&sh.tmem_slot, job.tmem_cols);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = sh.tmem_slot;
+  const uint32_t tmem_base = pair_begin(sh, warp, job.tmem_cols);
   RoleState rs;
-  run_unit<false>(job, &maps, warp, blockIdx.x / subs, (blockIdx.x % subs) * job.S, blockIdx.y * job.Nc,
-           job.tbias, job.tbias_stride, smem, sh, tmem_base, rs);
-  tc_fence_before();
-  __syncthreads();
-  if (warp == kMmaWarp) tmem_dealloc(tmem_base, job.tmem_cols);
+  run_unit<false>(job, &maps, warp, rank, (int)(blockIdx.x >> 1), blockIdx.y * job.Nc, job.tbias, job.tbias_stride, smem, sh,
+                  tmem_base, rs);
+  pair_end(warp, tmem_base, job.tmem_cols);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -796,12 +831,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   const int warp = warp_idx_sync();
   const int rank = (int)cluster_ctarank();
   const int g = (int)cluster_id_x();
-  if (threadIdx.x == 0) init_shared(sh);
-  if (warp == kMmaWarp) tmem_alloc(&sh.tmem_slot, 512);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = sh.tmem_slot;
+  const uint32_t tmem_base = pair_begin(sh, warp, 512);
   RoleState rs;
 
   const long long ht4 = ((long long)lp.H * lp.T) >> 2;           // float4 per sample
@@ -828,20 +858,17 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
           tma_prefetch_desc(&lp.maps[ji + 1].a_map[0]);
           tma_prefetch_desc(&lp.maps[ji + 1].w_map);
         }
-        const int first = job.S == 8 ? 0 : rank, stride = job.S == 8 ? 1 : 2;
-        const int b0 = job.S == 8 ? rank * 8 : 0;
         // the unit after this job's last one: first unit of the next job (next step's first job after the last)
         const int nji = ji + 1 < lp.n_jobs ? ji + 1 : 0;
         const ConvJob& njob = lp.jobs[nji];
-        const bool has_next = (ji + 1 < lp.n_jobs || k < lp.n_steps) && (njob.S == 8 || rank < njob.slices);
-        const int n_n0 = njob.S == 8 ? 0 : rank * njob.Nc;
-        for (int sl = first; sl < slices; sl += stride) {
-          const bool last_unit = sl + stride >= slices;
-          if (TR && threadIdx.x == kMmaWarp * 32 && tr && sl == first) trace_mark<TR>(tr, 23);
-          run_unit<TR>(job, maps, warp, g, b0, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == first ? tr : nullptr,
-                   last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, n_n0);
-          if (sl + stride < slices) {   // TMEM / staging smem are reused by the next unit
-            tc_fence_before();
+        const bool has_next = ji + 1 < lp.n_jobs || k < lp.n_steps;
+        for (int sl = 0; sl < slices; ++sl) {      // N slices of the layer, one after the other, by the whole pair
+          const bool last_unit = sl + 1 >= slices;
+          if (TR && threadIdx.x == kMmaWarp * 32 && tr && sl == 0) trace_mark<TR>(tr, 23);
+          run_unit<TR>(job, maps, warp, rank, g, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == 0 ? tr : nullptr,
+                       last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, 0);
+          if (sl + 1 < slices) {   // TMEM / staging smem are reused by the next unit (the peer's side of the pair is
+            tc_fence_before();     // protected through the full barriers: its loads for the next unit follow its barrier)
             __syncthreads();
             tc_fence_after();
           }
@@ -876,9 +903,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
     else job_sync(warp < kEpiWarps, warp == kProducerWarp);
   }
   if (threadIdx.x == 0) tma_store_wait_all();
-  tc_fence_before();
-  __syncthreads();
-  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+  pair_end(warp, tmem_base, 512);
 }
 
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device (context): done once for each device this process
@@ -902,7 +927,7 @@ cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_grou
                             cudaStream_t stream) {
   cudaError_t e = ensure_smem_attr();
   if (e != cudaSuccess) return e;
-  dim3 grid(n_groups * (kGroupSamples / job.S), n_slices);
+  dim3 grid(2 * n_groups, n_slices);   // one CTA pair (cluster of 2 along x) per 16-sample group
   conv_gemm_kernel<<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
   return cudaGetLastError();
 }

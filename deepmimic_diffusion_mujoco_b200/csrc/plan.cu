@@ -187,10 +187,17 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (sp.nsrc == 1 && j.src_chunks[0] == 1 && sp.src_real_c[0] < j.Cc)   // e.g. the 35 qpos channels padded to 64
     j.ksteps = (sp.src_real_c[0] + 15) / 16;
 
-  // tile shape
+  // tile shape.  A CTA always owns 8 samples of its group (GEMM row = l * 8 + b); the two CTAs of a cluster form a CTA
+  // pair whose MMAs (tcgen05.mma.cta_group::2) span both CTAs' rows: M = 256 (128 rows per CTA), or M = 128 (64 rows per
+  // CTA) for the layers with L <= 8.  Each CTA stages half of every weight tile (N / 2 rows); the pair shares them.
+  const bool gn = !sp.gnkey.empty();
+  const int cout_pad = round_up(sp.Cout, 32);
+  const int cg = gn ? sp.Cout / 8 : 32;
+  if (gn && (sp.Cout % 32 != 0)) return fail(DM_ERR_ARG, "%s: GroupNorm layers need Cout %% 32 == 0", sp.name.c_str());
   j.l_stride = sp.kind == CONV_DOWN ? 2 : 1;
-  j.S = (sp.kind == CONV_DOWN || Lj * 8 >= 128) ? 8 : 16;
-  const int pos_per_mt = 128 / j.S;
+  j.S = 8;
+  j.mrows = (Lj * 8 <= 64 && cout_pad % 64 == 0) ? 64 : 128;
+  const int pos_per_mt = j.mrows / j.S;
   int maxshift;
   if (sp.kind == CONV_K5) { j.halo_lo = 2; maxshift = 4; }
   else if (sp.kind == CONV_DOWN) { j.halo_lo = 1; maxshift = 2; }
@@ -228,39 +235,36 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     for (int t = 0; t < ktaps; ++t) j.taps[t] = {(signed char)t, (signed char)t, 0, (signed char)(t == 0 ? 1 : 0)};
   }
 
-  // N split and TMEM budget
-  const bool gn = !sp.gnkey.empty();
-  const int cout_pad = round_up(sp.Cout, 32);
-  const int cg = gn ? sp.Cout / 8 : 32;
-  if (gn && (sp.Cout % 32 != 0)) return fail(DM_ERR_ARG, "%s: GroupNorm layers need Cout %% 32 == 0", sp.name.c_str());
-  int Nc = cout_pad < 128 ? cout_pad : 128;
-  while (cout_pad % Nc) Nc -= 32;
-  // 16-sample units are split over the two CTAs of a cluster by N slice: prefer an even slice count
-  if (j.S == 16 && (cout_pad / Nc) % 2 == 1 && Nc % 64 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
+  // N split and TMEM budget.  N = 256 for the 64-row layers (M = 128 pair MMA: the widest N reads A least often), else 128.
+  const int n_step = j.mrows == 64 ? 64 : 32;                  // mrows 64: each lane half holds Nc / 2 columns (32-column units)
+  int Nc = cout_pad < (j.mrows == 64 ? 256 : 128) ? cout_pad : (j.mrows == 64 ? 256 : 128);
+  while (cout_pad % Nc || (gn && Nc % cg)) Nc -= n_step;
   const int mt_all = j.n_ltiles * j.Mt;
+  auto tile_cols = [&](int n) { return j.mrows == 64 ? n / 2 : n; };
   int acc_sets = j.nphase + (sp.aux_wkey.empty() ? 0 : 1);   // the auxiliary conv has its own accumulators
-  if (!sp.aux_wkey.empty() && acc_sets * mt_all * Nc > 512)
+  if (!sp.aux_wkey.empty() && acc_sets * mt_all * tile_cols(Nc) > 512)
     return fail(DM_ERR_STATE, "%s: no TMEM room for the fused residual conv", sp.name.c_str());   // caller falls back
-  while (j.nphase * mt_all * Nc > 512 && Nc > 32 && (Nc / 2) % 32 == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
-  if (j.nphase * mt_all * Nc > 512)
+  while (j.nphase * mt_all * tile_cols(Nc) > 512 && Nc > n_step && (Nc / 2) % n_step == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
+  if (j.nphase * mt_all * tile_cols(Nc) > 512)
     return fail(DM_ERR_ARG, "%s: horizon too long for the TMEM-resident GroupNorm design (H <= 256)", sp.name.c_str());
-  if (gn && Nc % cg) return fail(DM_ERR_ARG, "%s: N slice does not hold whole GroupNorm groups", sp.name.c_str());
+  if (Nc < 16 || (gn && Nc % cg)) return fail(DM_ERR_ARG, "%s: N slice does not hold whole GroupNorm groups", sp.name.c_str());
   j.Nc = Nc;
+  j.ncols = tile_cols(Nc);
   // two MMA issuer warps with one accumulator set each (conv_kernel.cu, mma_unit) when TMEM has room for it
   j.acc2 = 0;
   j.acc2_off = 0;
-  if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_all * Nc <= 512) {
+  if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_all * j.ncols <= 512) {
     j.acc2 = 1;
-    j.acc2_off = j.nphase * mt_all * Nc;
+    j.acc2_off = j.nphase * mt_all * j.ncols;
     acc_sets += j.nphase;
   }
   ly.slices = cout_pad / Nc;
   j.slices = ly.slices;
   j.tb_off = sp.tb_off;
   int cols = 32;
-  while (cols < acc_sets * mt_all * Nc) cols *= 2;
+  while (cols < acc_sets * mt_all * j.ncols) cols *= 2;
   j.tmem_cols = cols;
-  j.w_plane_bytes = Nc * j.row_bytes;
+  j.w_plane_bytes = (Nc / 2) * j.row_bytes;                     // this CTA's half of the weight tile
   j.w_tx_bytes = 2 * j.w_plane_bytes;
   j.w_stage_bytes = round_up(j.w_tx_bytes, 1024);
 
@@ -321,7 +325,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     const uint64_t dims[5] = {(uint64_t)j.Cc, (uint64_t)cout_pad, (uint64_t)n_chunks_tot, (uint64_t)ktaps, 2};
     const uint64_t str[4] = {(uint64_t)j.Cc * 2, (uint64_t)cout_pad * j.Cc * 2, (uint64_t)cin_tot * cout_pad * 2,
                              (uint64_t)wplane * 2};
-    const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 1, 2};
+    const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)(Nc / 2), 1, 1, 2};   // per CTA: half of the tile's N rows
     if ((rc = encode_map(&ly.maps.w_map, wdev, 5, dims, str, box, j.swz))) return rc;
   }
   for (int s = 0; s < sp.nsrc; ++s) {
@@ -386,7 +390,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   j.st_cw = 0;
   size_t st_bytes = 0;
   if (sp.want_act_out) {
-    const int rows = j.nphase * mt_all * 128;
+    const int rows = j.nphase * mt_all * j.mrows;
     const int lbox = rows / j.S;
     const int cw = Nc % 64 == 0 ? 64 : 32;
     const int blk_stride = rows * cw * 2 + 2 * kStageGap;
@@ -447,7 +451,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
       const uint64_t dims[5] = {(uint64_t)j.Cc, (uint64_t)cout_pad, (uint64_t)n_chunks_tot, 1, 2};
       const uint64_t str[4] = {(uint64_t)j.Cc * 2, (uint64_t)cout_pad * j.Cc * 2, (uint64_t)cin_tot * cout_pad * 2,
                                (uint64_t)xplane * 2};
-      const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)Nc, 1, 1, 2};
+      const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)(Nc / 2), 1, 1, 2};
       if ((rc = encode_map(&ly.maps.x_map, xdev, 5, dims, str, box, j.swz))) return rc;
     }
     std::vector<float> hxb(cout_pad, 0.f);
@@ -466,7 +470,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     }
     j.aux = 1;
     j.aux_shift = j.halo_lo;
-    j.aux_col0 = j.nphase * (1 + j.acc2) * mt_all * Nc;
+    j.aux_col0 = j.nphase * (1 + j.acc2) * mt_all * j.ncols;
     j.aux_bias = dxb;
     ly.aux_act = xi;
     if (aux_idx) *aux_idx = xi;
