@@ -125,7 +125,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
             if (leader) {
               tma_load_5d_pair(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws], 0, wn0,
                                chunk0 + ch, t < job.ntaps ? job.taps[t].wtap : 0, 0);
-#ifdef DM_TRACE_WLOADS
+#if defined(DM_TRACE_WLOADS) && !defined(DM_TRACE_MMA)
               if (tr && wi < 24) trace_mark<TR>(tr, 16 + 2 * wi);
 #endif
             }
@@ -203,11 +203,12 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   if (leader) trace_mark<TR>(tr, 21);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     int cidx = 0;
+    uint32_t started = 0;   // mode 2: accumulator sets (phase 0, phase 1, auxiliary) this warp has written in this l-tile
     for (int src = 0; src < job.nsrc; ++src) {
       const int nch = job.src_chunks[src];
       for (int ch = 0; ch < nch; ++ch, ++cidx) {
         if (!job.a_res) {
-          mbar_wait_cluster(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
+          mbar_wait(&sh.a_full[as], (rs.a_bits >> as) & 1, 0x300 + as);
           rs.a_bits ^= 1u << as;
           tc_fence_after();
         } else if (lt == 0 && cidx == 0) {
@@ -227,15 +228,26 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
         for (int t = 0; t < job.ntaps + job.aux; ++t) {
           const bool is_aux = t >= job.ntaps;
           // mode 1: both warps work on every tap, A on the first half of its k-steps and B on the second half;
-          // the auxiliary tap (single accumulator set) is B's alone.  mode 0: everything is A's.
+          // the auxiliary tap (single accumulator set) is B's alone.  mode 2: whole taps alternate between the warps
+          // (a warp's per-tap bookkeeping -- commit, ring step, barrier poll, descriptors -- then overlaps the other
+          // warp's issue: the layers with little MMA work per tap are bound by that bookkeeping).  mode 0: all A's.
           const bool both = mode == 1 && !is_aux;
-          const bool mine = both || which == mode;
+          const bool mine = mode == 2 ? (wi & 1) == which : (both || which == mode);
           const uint32_t w_par = (rs.w_bits >> ws) & 1;
           rs.w_bits ^= 1u << ws;
-          // Both warps observe every fill of every stage, in order, and the stage is not refilled before both have:
-          // a parity wait may only be one phase behind the barrier, so a warp without work on a tap still waits
-          // for its fill and then releases its half of w_empty (otherwise its half is the tcgen05.commit).
-          mbar_wait_cluster(&sh.w_full[ws], w_par, 0x400 + ws);
+          if (mode == 2) {
+            // Whole taps alternate.  The ring depth is even, so a stage always serves the same warp: the other warp
+            // neither waits for its fills nor releases it (the owner releases it twice); it only keeps its parity
+            // bookkeeping in step.  Its next wait on that stage happens in a later layer, behind a hand-over that
+            // implies every fill of this layer has completed (a parity wait may only be one phase behind the barrier).
+            if (!mine) { ++wi; if (++ws == job.n_w_stages) ws = 0; continue; }
+            mbar_wait(&sh.w_full[ws], w_par, 0x400 + ws);
+          } else {
+            // Both warps observe every fill of every stage, in order, and the stage is not refilled before both have:
+            // a warp without work on a tap still waits for its fill and then releases its half of w_empty
+            // (otherwise its half is the tcgen05.commit).
+            mbar_wait(&sh.w_full[ws], w_par, 0x400 + ws);
+          }
           if (!mine) {
             if (leader) {
               mbar_arrive(&sh.w_empty[ws]);
@@ -244,12 +256,19 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
           } else {
             tc_fence_after();
             if (leader && lt == 0 && cidx == 0 && t == 0) trace_mark<TR>(tr, 6);
-#ifdef DM_TRACE_WLOADS
+#ifdef DM_TRACE_MMA
+            if (leader && tr && wi < 24) tr[17 + 2 * wi] = (unsigned long long)clock64();
+#elif defined(DM_TRACE_WLOADS)
             if (leader && tr && wi < 24) trace_mark<TR>(tr, 17 + 2 * wi);
 #endif
             const uint32_t w16 = (w_smem + ws * job.w_stage_bytes) >> 4;
             const int shift = is_aux ? job.aux_shift : job.taps[t].shift, phase = is_aux ? 0 : job.taps[t].phase;
-            const bool first = cidx == 0 && (is_aux || job.taps[t].first != 0);
+            bool first = cidx == 0 && (is_aux || job.taps[t].first != 0);
+            if (mode == 2) {          // this warp's first product into (its accumulator set of) this phase clears it
+              const uint32_t bit = is_aux ? 4u : 1u << phase;
+              first = (started & bit) == 0;
+              started |= bit;
+            }
             const int k_mid = (ksteps + 1) >> 1;
             const int k0 = both && which ? k_mid : 0, k1 = both && !which ? k_mid : ksteps;
             uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * ncols) +
@@ -268,8 +287,14 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
                 }
               }
             }
+#ifdef DM_TRACE_MMA   // debug: when this warp finished ISSUING the tap's MMAs (slot pairs: issue done / fill seen)
+            if (leader && tr && wi < 24) tr[16 + 2 * wi] = (unsigned long long)clock64();
+#endif
             __syncwarp();
-            if (leader) umma_commit_pair(&sh.w_empty[ws]);
+            if (leader) {
+              umma_commit_pair(&sh.w_empty[ws]);
+              if (mode == 2) umma_commit_pair(&sh.w_empty[ws]);   // the owner's release counts for both warps
+            }
           }
           ++wi;
           if (++ws == job.n_w_stages) ws = 0;
@@ -345,6 +370,60 @@ __device__ __forceinline__ void gn_reduce_rows(float* s, float* q, int lane, flo
       q[0] += __shfl_xor_sync(0xffffffffu, q[0], 8);
     }
     if (lane < (S8 ? 8 : 16)) rmw(lane, 0, s[0], q[0]);
+  }
+}
+
+// GroupNorm statistics of one 32-column unit held in v[] (bias not yet added): adds this thread's row to the per-warp
+// partial sums of its sample (Sigma x, Sigma x^2 per group).  bias32 / qg: the unit's 32 bias values and the group of each
+// 4-channel quad.  Rows beyond the layer's length contribute nothing (ok == false).
+__device__ __forceinline__ void gn_accumulate_unit(const ConvJob& job, const float* v, const float* bias32, bool ok, int lane,
+                                             float* pw, const unsigned char* qg) {
+  constexpr int S = 8;
+  float s[8], q[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const float4 bi = *reinterpret_cast<const float4*>(bias32 + r * 4);
+    const float x0 = v[r * 4] + bi.x, x1 = v[r * 4 + 1] + bi.y, x2 = v[r * 4 + 2] + bi.z, x3 = v[r * 4 + 3] + bi.w;
+    s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
+    q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
+  }
+  if (job.cg_pow2) {
+    // fold 4-channel quads of the same GroupNorm group inside the thread, then recursive halving across lanes
+    if (job.cg < 8) {
+      if (S == 8) gn_reduce_rows<8, true>(s, q, lane, pw, qg); else gn_reduce_rows<8, false>(s, q, lane, pw, qg);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { s[i] = s[2 * i] + s[2 * i + 1]; q[i] = q[2 * i] + q[2 * i + 1]; }
+      if (job.cg < 16) {
+        if (S == 8) gn_reduce_rows<4, true>(s, q, lane, pw, qg); else gn_reduce_rows<4, false>(s, q, lane, pw, qg);
+      } else {
+        s[0] += s[1]; q[0] += q[1]; s[1] = s[2] + s[3]; q[1] = q[2] + q[3];
+        if (job.cg < 32) {
+          if (S == 8) gn_reduce_rows<2, true>(s, q, lane, pw, qg); else gn_reduce_rows<2, false>(s, q, lane, pw, qg);
+        } else {
+          s[0] += s[1]; q[0] += q[1];
+          if (S == 8) gn_reduce_rows<1, true>(s, q, lane, pw, qg); else gn_reduce_rows<1, false>(s, q, lane, pw, qg);
+        }
+      }
+    }
+  } else {
+    // arbitrary group width (a multiple of 4): several quads may share a group, one lane adds them in order
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
+      q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
+      if (S == 8) {
+        s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
+        q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
+      }
+      if (lane < S) {
+        float2* pp = reinterpret_cast<float2*>(&pw[(lane * 8 + qg[r]) * 2]);
+        float2 acc = *pp;
+        acc.x += s[r];
+        acc.y += q[r];
+        *pp = acc;
+      }
+    }
   }
 }
 
@@ -488,54 +567,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         tmem_ld32(trow + (uint32_t)(T * ncols + cc * 32), v);
         tmem_ld_wait();
         if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * ncols + cc * 32), v);
-        float s[8], q[8];
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cbase + cc * 32 + r * 4]);
-          const float x0 = v[r * 4] + bi.x, x1 = v[r * 4 + 1] + bi.y, x2 = v[r * 4 + 2] + bi.z, x3 = v[r * 4 + 3] + bi.w;
-          s[r] = ok ? (x0 + x1) + (x2 + x3) : 0.f;
-          q[r] = ok ? fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, x3 * x3))) : 0.f;
-        }
-        float* pw = &sh.part[warp * 256];
-        const unsigned char* qg = &sh.qgrp[(cbase >> 2) + cc * 8];
-        if (job.cg_pow2) {
-          // fold 4-channel quads of the same GroupNorm group inside the thread, then recursive halving across lanes
-          if (job.cg < 8) {
-            if (S == 8) gn_reduce_rows<8, true>(s, q, lane, pw, qg); else gn_reduce_rows<8, false>(s, q, lane, pw, qg);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) { s[i] = s[2 * i] + s[2 * i + 1]; q[i] = q[2 * i] + q[2 * i + 1]; }
-            if (job.cg < 16) {
-              if (S == 8) gn_reduce_rows<4, true>(s, q, lane, pw, qg); else gn_reduce_rows<4, false>(s, q, lane, pw, qg);
-            } else {
-              s[0] += s[1]; q[0] += q[1]; s[1] = s[2] + s[3]; q[1] = q[2] + q[3];
-              if (job.cg < 32) {
-                if (S == 8) gn_reduce_rows<2, true>(s, q, lane, pw, qg); else gn_reduce_rows<2, false>(s, q, lane, pw, qg);
-              } else {
-                s[0] += s[1]; q[0] += q[1];
-                if (S == 8) gn_reduce_rows<1, true>(s, q, lane, pw, qg); else gn_reduce_rows<1, false>(s, q, lane, pw, qg);
-              }
-            }
-          }
-        } else {
-          // arbitrary group width (a multiple of 4): several quads may share a group, one lane adds them in order
-#pragma unroll
-          for (int r = 0; r < 8; ++r) {
-            s[r] += __shfl_xor_sync(0xffffffffu, s[r], 16);
-            q[r] += __shfl_xor_sync(0xffffffffu, q[r], 16);
-            if (S == 8) {
-              s[r] += __shfl_xor_sync(0xffffffffu, s[r], 8);
-              q[r] += __shfl_xor_sync(0xffffffffu, q[r], 8);
-            }
-            if (lane < S) {
-              float2* pp = reinterpret_cast<float2*>(&pw[(lane * 8 + qg[r]) * 2]);
-              float2 acc = *pp;
-              acc.x += s[r];
-              acc.y += q[r];
-              *pp = acc;
-            }
-          }
-        }
+        gn_accumulate_unit(job, v, &sh.par[0][cbase + cc * 32], ok, lane, &sh.part[warp * 256], &sh.qgrp[(cbase >> 2) + cc * 8]);
       }
     }
     trace_mark<TR>(tr, 40);

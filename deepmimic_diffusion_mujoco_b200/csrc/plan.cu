@@ -475,7 +475,16 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     ly.aux_act = xi;
     if (aux_idx) *aux_idx = xi;
   }
-  j.mma_mode = j.acc2;   // 1: both issuer warps share every tap (conv_kernel.cu, mma_unit)
+  // 1: both issuer warps share every tap (k-steps split); 2: whole taps alternate between them (conv_kernel.cu, mma_unit)
+  j.mma_mode = j.acc2;
+#ifndef DM_MODE2
+#define DM_MODE2 2
+#endif
+  if (j.acc2 && j.ntaps >= 2) {
+    // pipe time of one tap's MMAs (cycles, MAC floor of the pair MMA) against the issuing warp's per-tap bookkeeping
+    const int mma_cycles = j.Mt * j.ksteps * 3 * ((j.mrows * Nc) / 256);
+    if (DM_MODE2 == 1 || (DM_MODE2 == 2 && mma_cycles < 600)) j.mma_mode = 2;
+  }
   // ---- resident link: read the previous layer's staged tile in place (fused loop only) ----
   if (!P->layers.empty()) {
     Layer& pv = P->layers.back();
@@ -501,6 +510,10 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
         if (ly.smem < need) ly.smem = need;
       }
     }
+  }
+  if (j.mma_mode == 2) {   // alternating taps need an even ring: a stage then always serves the same issuer warp
+    if (j.n_w_stages % 2) j.n_w_stages -= 1;
+    if (j.n_w_stages < 2) { j.n_w_stages = 1; j.mma_mode = 1; }
   }
   if (!P->layers.empty()) P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, j);
   P->layers.push_back(ly);

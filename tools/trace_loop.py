@@ -51,3 +51,13 @@ if detail:
             print("  " + "  ".join(f"{(r[16+2*w]-r[0])/1e3:.2f}/{(r[17+2*w]-r[0])/1e3:.2f}" for w in range(24) if r[17+2*w] > 0))
 print("effective SM clock MHz over the traced step:", (t[-1, 1] - t[0, 1]) / ((t[-1, 0] - t[0, 0]) / 1e3))
 print("sum of layers us", tot / 1e3, " step span us", (t[-1, 13] - t[0, 0]) / 1e3)
+if os.environ.get("TRACE_MMA_CLOCKS"):
+    # DM_TRACE_MMA build: slots 17+2i / 16+2i hold clock64 when issuer warp A passed tap i's weight wait / finished issuing it
+    for i, (n, C, L) in enumerate(names):
+        if any(d in n for d in os.environ["TRACE_MMA_CLOCKS"].split(",")):
+            r = tr.cpu().numpy()[i].astype("int64")
+            seen = [int(r[17 + 2 * w]) for w in range(20) if r[17 + 2 * w] > 0]
+            done = [int(r[16 + 2 * w]) for w in range(20) if r[16 + 2 * w] > 0]
+            m = min(len(seen), len(done))
+            print(n, "cycles: [wait passed -> issue loop done | issue done -> next wait passed]")
+            print("  " + "  ".join(f"{done[w]-seen[w]}|{(seen[w+1]-done[w]) if w + 1 < m else 0}" for w in range(m)))
