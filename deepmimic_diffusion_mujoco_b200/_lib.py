@@ -13,7 +13,7 @@ CSRC = os.path.join(_HERE, "csrc")
 
 EXPORTS = [
     "dm_last_error", "dm_plan_create", "dm_plan_free", "dm_plan_set_schedule", "dm_unet_forward", "dm_ddpm_step",
-    "dm_sample_loop", "dm_fk_reward", "dm_fid_moments", "dm_window_moments", "dm_mocap_to_qpos", "dm_mocap_to_qvel", "dm_motion_dataset", "dm_plan_set_sample_offset", "dm_plan_num_layers", "dm_plan_layer_info",
+    "dm_sample_loop", "dm_fk_reward", "dm_fk_reward_noalloc", "dm_fid_moments", "dm_window_moments", "dm_mocap_to_qpos", "dm_mocap_to_qvel", "dm_motion_dataset", "dm_plan_set_sample_offset", "dm_plan_num_layers", "dm_plan_layer_info",
     "dm_plan_read_layer", "dm_plan_last_launch_count", "dm_device_error_code", "dm_plan_set_trace",
 ]
 
@@ -72,6 +72,7 @@ def lib():
     L.dm_ddpm_step.argtypes = [vp, vp, vp, vp, u64, ci, ci, ci, ctypes.POINTER(DmCond), vp]
     L.dm_sample_loop.argtypes = [vp, vp, ci, vp, u64, ci, ci, ci, ctypes.POINTER(DmCond), vp, ci, vp]
     L.dm_fk_reward.argtypes = [vp, vp, ci, ci, ctypes.c_float, vp, vp, vp, vp]
+    L.dm_fk_reward_noalloc.argtypes = [vp, vp, ci, ci, ctypes.c_float, vp, vp, vp, vp]
     L.dm_fid_moments.argtypes = [vp, ci, ci, vp, vp, vp]
     L.dm_window_moments.argtypes = [vp, ci, ci, ci, ci, ci, vp, vp, vp]
     L.dm_mocap_to_qpos.argtypes = [vp, ci, vp, vp]

@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "../../include/dm_b200.h"
 #include "fk_math.cuh"
 
@@ -219,6 +221,79 @@ extern "C" int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, 
   if (body) e = feat_in_smem ? launch(fk_reward_kernel<true, true>) : launch(fk_reward_kernel<true, false>);
   else e = feat_in_smem ? launch(fk_reward_kernel<false, true>) : launch(fk_reward_kernel<false, false>);
   cudaFreeAsync(feat, s);
+  if (e != cudaSuccess) return fail(DM_ERR_CUDA, "fk_reward launch: %s", cudaGetErrorString(e));
+  return DM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// dm_fk_reward_noalloc: the same kernels as dm_fk_reward with the reference-feature scratch in a file-scope device
+// array instead of a pool allocation -- for callers that must not allocate (CUDA graph capture, serving loops).
+// No counterpart in the reference.
+//   * kNoAllocMaxH frames of kFeatStride floats = 376 832 bytes, held by every GPU that loads the library until exit.
+//   * In HOST code `g_fk_noalloc_feat` is only a stand-in for the symbol: the device address comes from
+//     cudaGetSymbolAddress, fetched once per device with that device current (never pass the name to a kernel).
+//   * Every call shares the array and it keeps the previous call's contents.  Nothing has to start at zero:
+//     ref_features_kernel rewrites all kFeatStride floats of the H rows a call uses (padding included) before
+//     fk_reward_kernel reads them, in stream order.  Calls that overlap on the GPU (different streams, or graph
+//     branches without a dependency) race on the array: serialise them.
+// ------------------------------------------------------------------------------------------------
+constexpr int kNoAllocMaxH = DM_FK_NOALLOC_MAX_H;
+static __device__ __align__(256) float g_fk_noalloc_feat[kNoAllocMaxH * dm::fk::kFeatStride];
+
+static int fk_noalloc_scratch(float** out) {
+  static std::mutex mu;
+  static float* addr[64] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(DM_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= 64) return fail(DM_ERR_ARG, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_fk_noalloc_feat);   // this device's copy of the array (device `dev` is current)
+    if (e != cudaSuccess || !p) return fail(DM_ERR_CUDA, "cudaGetSymbolAddress(g_fk_noalloc_feat): %s", cudaGetErrorString(e));
+    addr[dev] = static_cast<float*>(p);
+  }
+  *out = addr[dev];
+  return DM_OK;
+}
+
+extern "C" int dm_fk_reward_noalloc(const float* qpos_dev, const float* ref_dev, int N, int H, float dt, float* body_pos_dev,
+                                    float* reward_dev, double* sums_dev, dm_stream_t st) {
+  if (!qpos_dev || !ref_dev || !reward_dev || !sums_dev) return fail(DM_ERR_ARG, "null argument");
+  if (N < 1 || H < 1 || !(dt > 0.f)) return fail(DM_ERR_ARG, "need N >= 1, H >= 1, dt > 0");
+  if (H > kNoAllocMaxH)
+    return fail(DM_ERR_ARG, "dm_fk_reward_noalloc: horizon %d exceeds the static scratch (DM_FK_NOALLOC_MAX_H = %d frames); "
+                            "use dm_fk_reward", H, kNoAllocMaxH);
+  int rc = check_device();
+  if (rc) return rc;
+  float* feat = nullptr;
+  if ((rc = fk_noalloc_scratch(&feat))) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  ref_features_kernel<<<(H + 31) / 32, 32, 0, s>>>(ref_dev, H, 1.f / dt, feat);
+  const long long nfr = (long long)N * H;
+  const long long tiles = (nfr + kFkThreads - 1) / kFkThreads;
+  const bool body = body_pos_dev != nullptr;
+  const size_t base_smem = (size_t)(kFkThreads * 35 + 36 + (body ? kFkThreads * fk::kBodies * 3 : 0)) * sizeof(float);
+  const size_t feat_smem = (size_t)H * fk::kFeatStride * sizeof(float);
+  const bool feat_in_smem = base_smem + feat_smem <= 200 * 1024;
+  const size_t smem = base_smem + (feat_in_smem ? feat_smem : 0);
+  int blocks_per_sm = kFkBlocksPerSm;
+  while (blocks_per_sm > 1 && (smem + 1024) * blocks_per_sm > 227 * 1024) --blocks_per_sm;
+  const unsigned grid = (unsigned)(tiles < 148LL * blocks_per_sm ? tiles : 148LL * blocks_per_sm);
+  const int vec_ok = (reinterpret_cast<uintptr_t>(qpos_dev) & 15) == 0;
+  const int body_vec_ok = (reinterpret_cast<uintptr_t>(body_pos_dev) & 15) == 0;
+  auto launch = [&](auto kern) -> cudaError_t {
+    if (smem > 48 * 1024) {
+      cudaError_t le = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (le != cudaSuccess) return le;
+    }
+    kern<<<grid, kFkThreads, smem, s>>>(qpos_dev, feat, nfr, H, 1.f / dt, vec_ok, body_vec_ok, body_pos_dev, reward_dev, sums_dev);
+    return cudaGetLastError();
+  };
+  cudaError_t e;
+  if (body) e = feat_in_smem ? launch(fk_reward_kernel<true, true>) : launch(fk_reward_kernel<true, false>);
+  else e = feat_in_smem ? launch(fk_reward_kernel<false, true>) : launch(fk_reward_kernel<false, false>);
   if (e != cudaSuccess) return fail(DM_ERR_CUDA, "fk_reward launch: %s", cudaGetErrorString(e));
   return DM_OK;
 }

@@ -108,6 +108,17 @@ int dm_sample_loop(dm_plan_t* plan, float* x_dev, int have_start, const float* n
 int dm_fk_reward(const float* qpos_dev, const float* ref_dev, int N, int H, float dt, float* body_pos_dev,
                  float* reward_dev, double* sums_dev, dm_stream_t stream);
 
+/* dm_fk_reward without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same arguments, kernels and results as dm_fk_reward; the reference-clip feature scratch lives in a static device array
+ * of DM_FK_NOALLOC_MAX_H frames x 92 floats (376 832 bytes, held by every GPU that loads the library until exit), so
+ * H > DM_FK_NOALLOC_MAX_H is rejected with DM_ERR_ARG.  The call issues no cudaMalloc / cudaFree / pool operation.  All
+ * calls share that array and it keeps the previous call's contents (each call rewrites the rows it uses before reading
+ * them): calls that overlap on the GPU -- different streams, unordered graph branches -- race; serialise them. */
+#define DM_FK_NOALLOC_MAX_H 1024
+int dm_fk_reward_noalloc(const float* qpos_dev, const float* ref_dev, int N, int H, float dt, float* body_pos_dev,
+                         float* reward_dev, double* sums_dev, dm_stream_t stream);
+
 /* MotionFID.calculate_activation_statistics moments (metrics/fid_score.py:24-43): sum_dev double[D] += sum_n X,
  * sxx_dev double[D,D] += X^T X over X_dev fp32 [N,D].  Buffers accumulate (zero them first); sums are what
  * ranks all-reduce. */
