@@ -69,6 +69,13 @@ struct ConvJob {
   int n_a_stages, n_w_stages;
   int a_stage_bytes, w_stage_bytes, a_plane_bytes, w_plane_bytes;
   int a_tx_bytes, w_tx_bytes;   // bytes ONE CTA's loads deliver per stage (the leader's barrier expects twice that)
+  // TMEM rounds.  The whole per-sample conv output normally stays in TMEM until the GroupNorm statistics are known; when
+  // its tiles exceed the 512 columns (horizons above 256) the l-tiles are processed lt_round at a time: the epilogue drains
+  // each round (statistics + raw fp32 values to `raw`), the MMAs reuse the columns, and pass 2 reads `raw` back.
+  int lt_round;           // l-tiles per round (== n_ltiles when everything fits)
+  int n_rounds;           // ceil(n_ltiles / lt_round)
+  float* raw;             // [G][Lj][16][raw_C] fp32 scratch of the pre-normalisation conv output (rounds only)
+  int raw_C;
   int tmem_cols;
   int mma_mode;           // 0: warp A issues every MMA; 1: the two issuer warps split the k-steps of every tap, each
                           // with its own accumulator set (see mma_unit)

@@ -147,7 +147,8 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
   // have all completed (its operand stages are dead), the first weight tiles of the next layer are loaded into
   // that layer's ring slots that lie beyond this layer's staged output tile; they land during the epilogue.
   if (nj != nullptr && job.pre_next > 0) {
-    mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x700);
+    for (int r = 0; r < job.n_rounds; ++r)   // one accumulator phase per TMEM round, observed in order
+      mbar_wait(&sh.acc_full, (rs.acc_count + r) & 1, 0x700);
     const uint32_t nw_smem = smem_base + (uint32_t)(nj->a_res ? nj->w_off_res : nj->n_a_stages * nj->a_stage_bytes);
     for (int i = 0; i < job.pre_next; ++i) {
       mbar_wait(&sh.w_empty[i], ((rs.w_bits >> i) & 1) ^ 1, 0x780 + i);
@@ -159,7 +160,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
     }
     rs.pre_w = job.pre_next;
   }
-  rs.acc_count++;
+  rs.acc_count += job.n_rounds;
   __syncwarp();
 }
 
@@ -187,7 +188,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   if (which != 0) tr = nullptr;
   if (leader) trace_mark<TR>(tr, 20);
   const int S = job.S, Nc = job.Nc, ncols = job.ncols;
-  const int MT = job.n_ltiles * job.Mt;
+  const int MT = job.lt_round * job.Mt;      // tiles per phase of one TMEM round (all of them when n_rounds == 1)
   const int mode = job.mma_mode;
   const uint32_t idesc = umma_idesc_f16(2 * job.mrows, Nc);
   const int ksteps = job.ksteps;   // 16-channel k-steps per chunk that hold real input channels (zero padding skipped)
@@ -201,6 +202,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const uint32_t peer_w_empty = mapa_u32(smem_u32(&sh.w_empty[0]), 1);   // the peer CTA's copy of the ring's empty barriers
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 21);
+  int lt_in = 0;            // l-tile index inside the current TMEM round
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
     int cidx = 0;
     uint32_t started = 0;   // mode 2: accumulator sets (phase 0, phase 1, auxiliary) this warp has written in this l-tile
@@ -271,7 +273,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
             }
             const int k_mid = (ksteps + 1) >> 1;
             const int k0 = both && which ? k_mid : 0, k1 = both && !which ? k_mid : ksteps;
-            uint32_t d = tmem_base + (uint32_t)((phase * MT + lt * job.Mt) * ncols) +
+            uint32_t d = tmem_base + (uint32_t)((phase * MT + lt_in * job.Mt) * ncols) +
                          (is_aux ? (uint32_t)job.aux_col0 : which ? (uint32_t)job.acc2_off : 0u);
             uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
             for (int mt = 0; mt < job.Mt; ++mt, d += ncols, a16 += mt_step16) {
@@ -305,11 +307,18 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
         }
       }
     }
+    if (++lt_in == job.lt_round || lt + 1 == job.n_ltiles) {   // end of a TMEM round: hand the accumulators to the epilogues
+      lt_in = 0;
+      if (leader) umma_commit_pair(&sh.acc_full);
+      if (lt + 1 < job.n_ltiles) {
+        // the next round overwrites these columns in BOTH CTAs: wait until both epilogues have drained them
+        mbar_wait_cluster(&sh.tile_ready, rs.tile_count & 1, 0x320);
+        rs.tile_count++;
+        tc_fence_after();
+      }
+    }
   }
-  if (leader) {
-    umma_commit_pair(&sh.acc_full);
-    trace_mark<TR>(tr, 7);
-  }
+  if (leader) trace_mark<TR>(tr, 7);
   __syncwarp();
 }
 
@@ -425,6 +434,56 @@ __device__ __forceinline__ void gn_accumulate_unit(const ConvJob& job, const flo
       }
     }
   }
+}
+
+// GroupNorm statistics -> per-(sample, channel) scale / shift table.  Called by all epilogue threads once every warp has
+// accumulated its partial sums: fixed-order combination over the warps (deterministic), then
+//   y = x * sc + sf,  sc = rstd * gamma,  sf = (bias - mean) * sc + beta      (table rows of 2 * Nc + 4 floats in sh.part)
+__device__ __forceinline__ void gn_finalize(const ConvJob& job, ConvShared& sh, int tid, int Nc) {
+  constexpr int S = 8;
+  named_bar_sync(1, kEpiThreads);
+  if (tid < 128) {                       // one thread per (sample, group): fixed-order sum over the warps
+    float a = 0.f, q2 = 0.f;
+#pragma unroll
+    for (int w = 0; w < kEpiWarps; ++w) {
+      const float2 pv = *reinterpret_cast<const float2*>(&sh.part[(w * 128 + tid) * 2]);
+      a += pv.x;
+      q2 += pv.y;
+    }
+    const float inv_n = 1.f / (float)(job.cg * job.Lj);
+    const float mean = a * inv_n;
+    const float var = fmaxf(q2 * inv_n - mean * mean, 0.f);
+    (&sh.stat[0][0][0])[tid * 2] = mean;
+    (&sh.stat[0][0][0])[tid * 2 + 1] = rsqrtf(var + 1e-5f);
+  }
+  named_bar_sync(1, kEpiThreads);
+  // scale/shift table: y = x * sc + sf with sc = rstd * gamma, sf = (bias - mean) * sc + beta
+  const int tab_stride = 2 * Nc + 4;
+  if (kEpiThreads % Nc == 0) {           // Nc in {32, 64, 128, ...}: no integer division in the loop
+    const int c = tid % Nc;
+    const int gi = sh.qgrp[c >> 2];
+    const float ga = sh.par[1][c], be = sh.par[2][c], bi = sh.par[0][c];
+    for (int bb = tid / Nc; bb < S; bb += kEpiThreads / Nc) {
+      const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
+      const float sc = st.y * ga;
+      float2 o;
+      o.x = sc;
+      o.y = fmaf(bi - st.x, sc, be);
+      *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
+    }
+  } else {
+    for (int e = tid; e < S * Nc; e += kEpiThreads) {
+      const int bb = e / Nc, c = e - bb * Nc;
+      const int gi = sh.qgrp[c >> 2];
+      const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
+      const float sc = st.y * sh.par[1][c];
+      float2 o;
+      o.x = sc;
+      o.y = fmaf(sh.par[0][c] - st.x, sc, sh.par[2][c]);
+      *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
+    }
+  }
+  named_bar_sync(1, kEpiThreads);
 }
 
 // Writes (optionally after adding the staged residual) 32 consecutive channels [cb, cb+32) of staged row `srow` as
@@ -572,51 +631,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     }
     trace_mark<TR>(tr, 40);
     if (job.aux && tid == 0) tma_store_wait_read();   // the auxiliary tile has left the staging buffer
-    named_bar_sync(1, kEpiThreads);
-    trace_mark<TR>(tr, 41);
-    if (tid < 128) {                       // one thread per (sample, group): fixed-order sum over the warps
-      float a = 0.f, q2 = 0.f;
-#pragma unroll
-      for (int w = 0; w < kEpiWarps; ++w) {
-        const float2 pv = *reinterpret_cast<const float2*>(&sh.part[(w * 128 + tid) * 2]);
-        a += pv.x;
-        q2 += pv.y;
-      }
-      const float inv_n = 1.f / (float)(job.cg * job.Lj);
-      const float mean = a * inv_n;
-      const float var = fmaxf(q2 * inv_n - mean * mean, 0.f);
-      (&sh.stat[0][0][0])[tid * 2] = mean;
-      (&sh.stat[0][0][0])[tid * 2 + 1] = rsqrtf(var + 1e-5f);
-    }
-    named_bar_sync(1, kEpiThreads);
-    trace_mark<TR>(tr, 42);
-    // scale/shift table: y = x * sc + sf with sc = rstd * gamma, sf = (bias - mean) * sc + beta
-    const int tab_stride = 2 * Nc + 4;
-    if (kEpiThreads % Nc == 0) {           // Nc in {32, 64, 128, ...}: no integer division in the loop
-      const int c = tid % Nc;
-      const int gi = sh.qgrp[c >> 2];
-      const float ga = sh.par[1][c], be = sh.par[2][c], bi = sh.par[0][c];
-      for (int bb = tid / Nc; bb < S; bb += kEpiThreads / Nc) {
-        const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
-        const float sc = st.y * ga;
-        float2 o;
-        o.x = sc;
-        o.y = fmaf(bi - st.x, sc, be);
-        *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
-      }
-    } else {
-      for (int e = tid; e < S * Nc; e += kEpiThreads) {
-        const int bb = e / Nc, c = e - bb * Nc;
-        const int gi = sh.qgrp[c >> 2];
-        const float2 st = *reinterpret_cast<const float2*>(&sh.stat[bb][gi][0]);
-        const float sc = st.y * sh.par[1][c];
-        float2 o;
-        o.x = sc;
-        o.y = fmaf(sh.par[0][c] - st.x, sc, sh.par[2][c]);
-        *reinterpret_cast<float2*>(&sh.part[bb * tab_stride + 2 * c]) = o;
-      }
-    }
-    named_bar_sync(1, kEpiThreads);
+    gn_finalize(job, sh, tid, Nc);
   }
   trace_mark<TR>(tr, 10);
 

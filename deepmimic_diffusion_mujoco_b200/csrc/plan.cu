@@ -245,24 +245,34 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (!sp.aux_wkey.empty() && acc_sets * mt_all * tile_cols(Nc) > 512)
     return fail(DM_ERR_STATE, "%s: no TMEM room for the fused residual conv", sp.name.c_str());   // caller falls back
   while (j.nphase * mt_all * tile_cols(Nc) > 512 && Nc > n_step && (Nc / 2) % n_step == 0 && (!gn || (Nc / 2) % cg == 0)) Nc /= 2;
-  if (j.nphase * mt_all * tile_cols(Nc) > 512)
-    return fail(DM_ERR_ARG, "%s: horizon too long for the TMEM-resident GroupNorm design (H <= 256)", sp.name.c_str());
   if (Nc < 16 || (gn && Nc % cg)) return fail(DM_ERR_ARG, "%s: N slice does not hold whole GroupNorm groups", sp.name.c_str());
   j.Nc = Nc;
   j.ncols = tile_cols(Nc);
+  // TMEM rounds (horizons above 256): when even the narrowest N slice does not fit, the l-tiles go through TMEM
+  // lt_round at a time and the GroupNorm epilogue keeps the raw conv output in a global scratch between its two passes
+  j.lt_round = j.n_ltiles;
+  if (j.nphase * mt_all * j.ncols > 512) {
+    j.lt_round = 512 / (j.nphase * j.Mt * j.ncols);
+    if (j.lt_round < 1)
+      return fail(DM_ERR_ARG, "%s: one l-tile does not fit the 512 TMEM columns", sp.name.c_str());
+    if (!sp.aux_wkey.empty())
+      return fail(DM_ERR_STATE, "%s: no TMEM room for the fused residual conv", sp.name.c_str());   // caller falls back
+  }
+  j.n_rounds = (j.n_ltiles + j.lt_round - 1) / j.lt_round;
+  const int mt_acc = j.lt_round * j.Mt;                        // M tiles per phase resident in TMEM at a time
   // two MMA issuer warps with one accumulator set each (conv_kernel.cu, mma_unit) when TMEM has room for it
   j.acc2 = 0;
   j.acc2_off = 0;
-  if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_all * j.ncols <= 512) {
+  if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_acc * j.ncols <= 512) {
     j.acc2 = 1;
-    j.acc2_off = j.nphase * mt_all * j.ncols;
+    j.acc2_off = j.nphase * mt_acc * j.ncols;
     acc_sets += j.nphase;
   }
   ly.slices = cout_pad / Nc;
   j.slices = ly.slices;
   j.tb_off = sp.tb_off;
   int cols = 32;
-  while (cols < acc_sets * mt_all * j.ncols) cols *= 2;
+  while (cols < acc_sets * mt_acc * j.ncols) cols *= 2;
   j.tmem_cols = cols;
   j.w_plane_bytes = (Nc / 2) * j.row_bytes;                     // this CTA's half of the weight tile
   j.w_tx_bytes = 2 * j.w_plane_bytes;
@@ -380,7 +390,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     j.out_f32 = P->model_out;
     j.out_f32_C = sp.Cout;
     const int per_sample = Lout * sp.Cout;
-    if (per_sample % 4 == 0 && ly.slices == 1 && (size_t)j.S * (per_sample + 4) * 4 <= (size_t)budget) {
+    if (per_sample % 4 == 0 && ly.slices == 1 && j.n_rounds == 1 && (size_t)j.S * (per_sample + 4) * 4 <= (size_t)budget) {
       j.f32_stride = per_sample + 4;
       const size_t need = (size_t)j.S * j.f32_stride * 4 + 1024;
       if (ly.smem < need) ly.smem = need;
@@ -395,7 +405,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     const int cw = Nc % 64 == 0 ? 64 : 32;
     const int blk_stride = rows * cw * 2 + 2 * kStageGap;
     st_bytes = (size_t)2 * (Nc / cw) * blk_stride;
-    if (lbox <= 256 && st_bytes <= (size_t)budget) {
+    if (lbox <= 256 && st_bytes <= (size_t)budget && j.n_rounds == 1) {
       j.st_cw = cw;
       j.st_nq = Nc / cw;
       j.st_rows = rows;
@@ -470,7 +480,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     }
     j.aux = 1;
     j.aux_shift = j.halo_lo;
-    j.aux_col0 = j.nphase * (1 + j.acc2) * mt_all * j.ncols;
+    j.aux_col0 = j.nphase * (1 + j.acc2) * mt_acc * j.ncols;
     j.aux_bias = dxb;
     ly.aux_act = xi;
     if (aux_idx) *aux_idx = xi;
@@ -775,6 +785,24 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
   for (size_t i = 0; i + 1 < P->layers.size(); ++i)
       P->layers[i].job.sync_local = P->layers[i].job.S == 8 && P->layers[i + 1].job.S == 8;
   if (tb != P->TB) return fail(DM_ERR_ARG, "internal: time-bias layout mismatch (%d vs %d)", tb, P->TB);
+  // Scratch for the GroupNorm layers that run in TMEM rounds: [G][Lj][16][cout_pad] fp32, shared by all of them.
+  {
+    size_t need = 0;
+    for (Layer& ly : P->layers)
+      if (ly.kind == 0 && ly.job.n_rounds > 1 && ly.job.epi == EPI_GN_MISH) {
+        const size_t n = (size_t)P->G * ly.job.Lj * kGroupSamples * round_up(ly.job.Cout, 32);
+        if (n > need) need = n;
+      }
+    if (need) {
+      float* raw = nullptr;
+      if ((rc = dev_alloc(P, reinterpret_cast<void**>(&raw), need * sizeof(float), false))) return rc;
+      for (Layer& ly : P->layers)
+        if (ly.kind == 0 && ly.job.n_rounds > 1 && ly.job.epi == EPI_GN_MISH) {
+          ly.job.raw = raw;
+          ly.job.raw_C = round_up(ly.job.Cout, 32);
+        }
+    }
+  }
   // An output tile whose only reader is the next layer's in-place (resident) read never has to reach global memory.
   for (size_t i = 0; i + 1 < P->layers.size(); ++i) {
     Layer& ly = P->layers[i];
