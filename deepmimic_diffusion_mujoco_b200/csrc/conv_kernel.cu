@@ -138,6 +138,13 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
       }
       chunk0 += nch;
     }
+    // TMEM rounds: this warp observes EVERY accumulator phase in order (a parity wait is only valid one phase behind the
+    // barrier), so it does not run ahead of a round boundary -- the MMA warps stop there anyway until the epilogues have
+    // drained the round
+    if (job.n_rounds > 1 && lt + 1 < job.n_ltiles && (lt + 1) % job.lt_round == 0) {
+      mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x720);
+      rs.acc_count++;
+    }
   }
   if (leader) trace_mark<TR>(tr, 4);
   // A resident link has no block barrier behind it (the roles run ahead, see sample_loop_kernel): this warp may only
@@ -147,8 +154,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
   // have all completed (its operand stages are dead), the first weight tiles of the next layer are loaded into
   // that layer's ring slots that lie beyond this layer's staged output tile; they land during the epilogue.
   if (nj != nullptr && job.pre_next > 0) {
-    for (int r = 0; r < job.n_rounds; ++r)   // one accumulator phase per TMEM round, observed in order
-      mbar_wait(&sh.acc_full, (rs.acc_count + r) & 1, 0x700);
+    mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x700);   // (the last round's phase; earlier ones were observed above)
     const uint32_t nw_smem = smem_base + (uint32_t)(nj->a_res ? nj->w_off_res : nj->n_a_stages * nj->a_stage_bytes);
     for (int i = 0; i < job.pre_next; ++i) {
       mbar_wait(&sh.w_empty[i], ((rs.w_bits >> i) & 1) ^ 1, 0x780 + i);
@@ -160,7 +166,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
     }
     rs.pre_w = job.pre_next;
   }
-  rs.acc_count += job.n_rounds;
+  rs.acc_count++;
   __syncwarp();
 }
 
@@ -180,7 +186,9 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
 //      set) is B's alone.
 // A weight stage is released (w_empty, two arrivals, in BOTH CTAs) by both warps; A stages and the unit's acc_full
 // take one commit from each warp as well.
-template <bool TR>
+// RD = false: the kernel variant for plans whose every layer fits TMEM at once (all horizons <= 256): the round logic
+// compiles away.  RD = true: layers may pass through TMEM in rounds (job.n_rounds > 1).
+template <bool TR, bool RD>
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr,
                                          const int which) {
@@ -188,7 +196,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   if (which != 0) tr = nullptr;
   if (leader) trace_mark<TR>(tr, 20);
   const int S = job.S, Nc = job.Nc, ncols = job.ncols;
-  const int MT = job.lt_round * job.Mt;      // tiles per phase of one TMEM round (all of them when n_rounds == 1)
+  const int MT = (RD ? job.lt_round : job.n_ltiles) * job.Mt;      // tiles per phase resident in TMEM (one round's worth)
   const int mode = job.mma_mode;
   const uint32_t idesc = umma_idesc_f16(2 * job.mrows, Nc);
   const int ksteps = job.ksteps;   // 16-channel k-steps per chunk that hold real input channels (zero padding skipped)
@@ -273,7 +281,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
             }
             const int k_mid = (ksteps + 1) >> 1;
             const int k0 = both && which ? k_mid : 0, k1 = both && !which ? k_mid : ksteps;
-            uint32_t d = tmem_base + (uint32_t)((phase * MT + lt_in * job.Mt) * ncols) +
+            uint32_t d = tmem_base + (uint32_t)((phase * MT + (RD ? lt_in : lt) * job.Mt) * ncols) +
                          (is_aux ? (uint32_t)job.aux_col0 : which ? (uint32_t)job.acc2_off : 0u);
             uint32_t a16 = a_base16 + ((uint32_t)(shift * S * job.row_bytes) >> 4);
             for (int mt = 0; mt < job.Mt; ++mt, d += ncols, a16 += mt_step16) {
@@ -307,7 +315,9 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
         }
       }
     }
-    if (++lt_in == job.lt_round || lt + 1 == job.n_ltiles) {   // end of a TMEM round: hand the accumulators to the epilogues
+    if (!RD) {
+      if (lt + 1 == job.n_ltiles && leader) umma_commit_pair(&sh.acc_full);
+    } else if (++lt_in == job.lt_round || lt + 1 == job.n_ltiles) {   // end of a TMEM round: hand the accumulators to the epilogues
       lt_in = 0;
       if (leader) umma_commit_pair(&sh.acc_full);
       if (lt + 1 < job.n_ltiles) {
@@ -519,6 +529,179 @@ __device__ __forceinline__ void staged_write(const ConvJob& job, uint32_t stg_da
     for (int w = 0; w < 4; ++w) split_half2(v[q4 * 8 + w * 2], v[q4 * 8 + w * 2 + 1], hh[w], ll[w]);
     sts128(a_hi, hv);
     sts128(a_lo, lv);
+  }
+}
+
+// ================================ epilogue, TMEM rounds (horizons above 256) ================================
+// The layer's l-tiles pass through TMEM job.lt_round at a time (mma_unit): after every round the accumulators are drained
+// and handed back to the leader's MMA warps (sh.tile_ready, one arrival per CTA).  GroupNorm layers accumulate the
+// statistics round by round and park the raw conv output in job.raw (fp32, written and later re-read by the SAME thread);
+// after the last round the table is built and pass 2 streams the raw values back.  Bias-only layers (down / up-sampling,
+// 1x1) finish each round directly.  Outputs go straight to global memory (these tiles exceed the staged epilogue).
+// Only the RD = true kernel variants contain it: the H <= 256 kernels carry neither its registers nor its instructions.
+template <bool TR>
+__device__ __forceinline__ void epilogue_rounds(const ConvJob& job, int warp, int g, int b0, int n0, int rank,
+                                             const float* tbias, int tbias_stride, ConvShared& sh, uint32_t tmem_base,
+                                             uint32_t acc_count0) {
+  constexpr int S = 8;
+  const int lane = threadIdx.x & 31, tid = threadIdx.x;
+  const int Nc = job.Nc, mrows = job.mrows, ncols = job.ncols;
+  const int cbase = mrows == 64 ? ((warp & 3) >> 1) * ncols : 0;
+  const int row = (mrows == 64 ? (warp & 1) : (warp & 3)) * 32 + lane;
+  const int slice = warp >> 2, b = row & (S - 1);
+  const bool gn = job.epi == EPI_GN_MISH;
+  const bool tb_uniform = tbias != nullptr && tbias_stride == 0;
+  for (int i = tid; i < Nc; i += kEpiThreads) {
+    sh.par[0][i] = __ldg(job.bias + n0 + i);
+    sh.par[1][i] = gn ? __ldg(job.gamma + n0 + i) : 1.f;
+    sh.par[2][i] = gn ? __ldg(job.beta + n0 + i) : 0.f;
+    sh.par[3][i] = tb_uniform ? __ldg(tbias + n0 + i) : 0.f;
+  }
+  if (tid < (Nc >> 2)) sh.qgrp[tid] = (unsigned char)((tid * 4) / job.cg);
+  if (gn)
+    for (int i = tid; i < kEpiWarps * 256; i += kEpiThreads) sh.part[i] = 0.f;
+  if (tid == 0) tma_store_wait_read();
+  const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+  const int nchunks = ncols >> 5;
+  const int MTr = job.lt_round * job.Mt;              // tiles per phase held in TMEM during one round
+  const int MT_all = job.n_ltiles * job.Mt;
+  const int bg = g * kGroupSamples + b0 + b;
+  float v[32];
+
+  // one 32-channel piece of one output row: bias / normalise + Mish + time bias, + residual, stores
+  auto finish = [&](int lrow, int cb) {
+    if (gn) {
+      const float* tab = &sh.part[b * (2 * Nc + 4) + 2 * cb];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const float4 s01 = *reinterpret_cast<const float4*>(tab + r * 8);
+        const float4 s23 = *reinterpret_cast<const float4*>(tab + r * 8 + 4);
+        const float4 tb = *reinterpret_cast<const float4*>(&sh.par[3][cb + r * 4]);
+        v[r * 4] = mish_f(fmaf(v[r * 4], s01.x, s01.y)) + tb.x;
+        v[r * 4 + 1] = mish_f(fmaf(v[r * 4 + 1], s01.z, s01.w)) + tb.y;
+        v[r * 4 + 2] = mish_f(fmaf(v[r * 4 + 2], s23.x, s23.y)) + tb.z;
+        v[r * 4 + 3] = mish_f(fmaf(v[r * 4 + 3], s23.z, s23.w)) + tb.w;
+      }
+      if (tbias != nullptr && tbias_stride != 0) {
+        const float4* tb = reinterpret_cast<const float4*>(tbias + (size_t)bg * tbias_stride + n0 + cb);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float4 t4 = __ldg(tb + e);
+          v[e * 4] += t4.x; v[e * 4 + 1] += t4.y; v[e * 4 + 2] += t4.z; v[e * 4 + 3] += t4.w;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
+        v[r * 4] += bi.x; v[r * 4 + 1] += bi.y; v[r * 4 + 2] += bi.z; v[r * 4 + 3] += bi.w;
+      }
+    }
+    const size_t rowoff = ((size_t)g * job.Lout + lrow) * kGroupSamples + b0 + b;
+    if (job.res) {
+      const uint4* rh = reinterpret_cast<const uint4*>(job.res + rowoff * job.res_C + n0 + cb);
+      const uint4* rl = reinterpret_cast<const uint4*>(job.res + job.res_plane_stride + rowoff * job.res_C + n0 + cb);
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        const uint4 hv = __ldcg(rh + q4), lv = __ldcg(rl + q4);
+        const __half2* hh = reinterpret_cast<const __half2*>(&hv);
+        const __half2* ll = reinterpret_cast<const __half2*>(&lv);
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
+          v[q4 * 8 + w * 2] += fh.x + fl.x;
+          v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
+        }
+      }
+    }
+    if (job.out) {
+      uint4* oh = reinterpret_cast<uint4*>(job.out + rowoff * job.out_C + n0 + cb);
+      uint4* ol = reinterpret_cast<uint4*>(job.out + job.out_plane_stride + rowoff * job.out_C + n0 + cb);
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        uint4 hv, lv;
+        __half2* hh = reinterpret_cast<__half2*>(&hv);
+        __half2* ll = reinterpret_cast<__half2*>(&lv);
+#pragma unroll
+        for (int w = 0; w < 4; ++w) split_half2(v[q4 * 8 + w * 2], v[q4 * 8 + w * 2 + 1], hh[w], ll[w]);
+        oh[q4] = hv;
+        ol[q4] = lv;
+      }
+    }
+    if (job.out_f32 && bg < job.B) {
+      float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
+#pragma unroll
+      for (int e = 0; e < 32; ++e)
+        if (n0 + cb + e < job.Cout) of[n0 + cb + e] = v[e];
+    }
+  };
+
+  for (int rd = 0; rd < job.n_rounds; ++rd) {
+    if (warp == kPollWarp) mbar_wait(&sh.acc_full, (acc_count0 + rd) & 1, 0x520);
+    named_bar_sync(1, kEpiThreads);      // (also orders the parameter loads above before their first use)
+    tc_fence_after();
+    const int t0 = rd * MTr;
+    const int nt = min(MTr, MT_all - t0);
+    if (gn) {
+      // pass 1 of this round: statistics, and the raw accumulators (bias not yet added) out to the scratch
+      for (int Tl = 0; Tl < nt; ++Tl) {
+        const int j = ((t0 + Tl) * mrows + row) >> 3;
+        const bool ok = j < job.Lj;
+        for (int cc = (slice - Tl * nchunks) & 3; cc < nchunks; cc += 4) {
+          tmem_ld32(trow + (uint32_t)(Tl * ncols + cc * 32), v);
+          tmem_ld_wait();
+          if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + Tl * ncols + cc * 32), v);
+          const int cb = cbase + cc * 32;
+          gn_accumulate_unit(job, v, &sh.par[0][cb], ok, lane, &sh.part[warp * 256], &sh.qgrp[cb >> 2]);
+          if (ok) {
+            float4* dst = reinterpret_cast<float4*>(job.raw + (((size_t)g * job.Lj + j) * kGroupSamples + b0 + b) * job.raw_C + n0 + cb);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) dst[e] = make_float4(v[e * 4], v[e * 4 + 1], v[e * 4 + 2], v[e * 4 + 3]);
+          }
+        }
+      }
+    } else {
+      // bias-only layers finish the round's tiles (both phases of a transposed conv) here
+      for (int ph = 0; ph < job.nphase; ++ph)
+        for (int Tl = 0; Tl < nt; ++Tl) {
+          const int j = ((t0 + Tl) * mrows + row) >> 3;
+          const int lrow = job.nphase == 2 ? 2 * j + ph : j;
+          const int pt = ph * MTr + Tl;
+          for (int cc = (slice - pt * nchunks) & 3; cc < nchunks; cc += 4) {
+            tmem_ld32(trow + (uint32_t)(pt * ncols + cc * 32), v);
+            tmem_ld_wait();
+            if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + pt * ncols + cc * 32), v);
+            if (j < job.Lj) finish(lrow, cbase + cc * 32);
+          }
+        }
+    }
+    if (rd + 1 < job.n_rounds) {           // give the TMEM columns back: the next round's MMAs overwrite them in both CTAs
+      tc_fence_before();
+      named_bar_sync(1, kEpiThreads);
+      if (tid == 0) {
+        if (rank == 0) mbar_arrive(&sh.tile_ready);
+        else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), 0));
+      }
+    }
+  }
+  if (gn) {
+    gn_finalize(job, sh, tid, Nc);          // (starts with a barrier: every warp's partial sums are complete)
+    // pass 2: every thread streams back the raw values it parked (same thread, same addresses: no fence needed)
+    for (int T = 0; T < MT_all; ++T) {
+      const int j = (T * mrows + row) >> 3;
+      if (j >= job.Lj) continue;
+      const int Tl = T % MTr;               // the unit -> warp assignment used when the tile was drained
+      for (int cc = (slice - Tl * nchunks) & 3; cc < nchunks; cc += 4) {
+        const int cb = cbase + cc * 32;
+        const float4* src = reinterpret_cast<const float4*>(job.raw + (((size_t)g * job.Lj + j) * kGroupSamples + b0 + b) * job.raw_C + n0 + cb);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float4 t4 = __ldcg(src + e);
+          v[e * 4] = t4.x; v[e * 4 + 1] = t4.y; v[e * 4 + 2] = t4.z; v[e * 4 + 3] = t4.w;
+        }
+        finish(j, cb);
+      }
+    }
   }
 }
 
@@ -783,7 +966,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
 
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
 // rank = this CTA's rank in its pair: it owns samples b0 = 8 * rank .. of group g.
-template <bool TR>
+template <bool TR, bool RD>
 __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp, int rank,
                                          int g, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
@@ -795,7 +978,10 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
   if (warp == kProducerWarp) {
     producer_unit<TR>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, rank, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
   } else if (warp == kMmaWarp || warp == kMmaWarpB) {
-    if (rank == 0) mma_unit<TR>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
+    if (rank == 0) mma_unit<TR, RD>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
+  } else if (RD && job.n_rounds > 1) {
+    epilogue_rounds<TR>(job, warp, g, b0, n0, rank, tbias, tbias_stride, sh, tmem_base, rs.acc_count);
+    rs.acc_count += job.n_rounds;
   } else {
     epilogue_unit<TR>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
@@ -829,6 +1015,7 @@ __device__ __forceinline__ uint32_t aligned_dyn_smem() {
 // ------------------------------------------------------------------------------------------------
 // per-layer launch: grid = (2 CTAs per 16-sample group, N slices), clusters of 2 along x (the CTA pair)
 // ------------------------------------------------------------------------------------------------
+template <bool RD>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvJob job) {
   const uint32_t smem = aligned_dyn_smem();
@@ -842,7 +1029,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   }
   const uint32_t tmem_base = pair_begin(sh, warp, job.tmem_cols);
   RoleState rs;
-  run_unit<false>(job, &maps, warp, rank, (int)(blockIdx.x >> 1), blockIdx.y * job.Nc, job.tbias, job.tbias_stride, smem, sh,
+  run_unit<false, RD>(job, &maps, warp, rank, (int)(blockIdx.x >> 1), blockIdx.y * job.Nc, job.tbias, job.tbias_stride, smem, sh,
                   tmem_base, rs);
   pair_end(warp, tmem_base, job.tmem_cols);
 }
@@ -869,7 +1056,7 @@ __device__ __forceinline__ void local_sync(bool wrote_global, bool issues_tma) {
   if (issues_tma) fence_proxy_async_global();
 }
 
-template <bool TR>
+template <bool TR, bool RD>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   const uint32_t smem = aligned_dyn_smem();
@@ -912,7 +1099,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         for (int sl = 0; sl < slices; ++sl) {      // N slices of the layer, one after the other, by the whole pair
           const bool last_unit = sl + 1 >= slices;
           if (TR && threadIdx.x == kMmaWarp * 32 && tr && sl == 0) trace_mark<TR>(tr, 23);
-          run_unit<TR>(job, maps, warp, rank, g, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == 0 ? tr : nullptr,
+          run_unit<TR, RD>(job, maps, warp, rank, g, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == 0 ? tr : nullptr,
                        last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, 0);
           if (sl + 1 < slices) {   // TMEM / staging smem are reused by the next unit (the peer's side of the pair is
             tc_fence_before();     // protected through the full barriers: its loads for the next unit follow its barrier)
@@ -963,9 +1150,13 @@ static cudaError_t ensure_smem_attr() {
   if (e != cudaSuccess) return e;
   std::lock_guard<std::mutex> lock(mu);
   if (dev >= 0 && dev < 64 && done[dev]) return cudaSuccess;
-  e = cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(sample_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(sample_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  const void* kernels[] = {(const void*)conv_gemm_kernel<false>, (const void*)conv_gemm_kernel<true>,
+                           (const void*)sample_loop_kernel<false, false>, (const void*)sample_loop_kernel<false, true>,
+                           (const void*)sample_loop_kernel<true, false>, (const void*)sample_loop_kernel<true, true>};
+  for (const void* k : kernels) {
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+    if (e != cudaSuccess) break;
+  }
   if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev] = true;
   return e;
 }
@@ -975,15 +1166,23 @@ cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_grou
   cudaError_t e = ensure_smem_attr();
   if (e != cudaSuccess) return e;
   dim3 grid(2 * n_groups, n_slices);   // one CTA pair (cluster of 2 along x) per 16-sample group
-  conv_gemm_kernel<<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+  if (job.n_rounds > 1) conv_gemm_kernel<true><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+  else conv_gemm_kernel<false><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
   return cudaGetLastError();
 }
 
 cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStream_t stream) {
   cudaError_t e = ensure_smem_attr();
   if (e != cudaSuccess) return e;
-  if (lp.trace) sample_loop_kernel<true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
-  else sample_loop_kernel<false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+  bool rounds = false;   // any layer that passes through TMEM in rounds (horizons above 256) selects the RD = true variant
+  for (int i = 0; i < lp.n_jobs; ++i) rounds = rounds || lp.jobs[i].n_rounds > 1;
+  if (lp.trace) {
+    if (rounds) sample_loop_kernel<true, true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+    else sample_loop_kernel<true, false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+  } else {
+    if (rounds) sample_loop_kernel<false, true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+    else sample_loop_kernel<false, false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+  }
   return cudaGetLastError();
 }
 

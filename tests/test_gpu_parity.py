@@ -278,6 +278,45 @@ def test_full_batch_rows_match_oracle(dm):
     assert torch.equal(chain[:, -1][m], ref[:, -1][m])
 
 
+@pytest.mark.parametrize("B,H,n", [(2, 480, 3), (1, 512, 2), (1, 1024, 1)])
+def test_horizons_beyond_256_layers_and_chain(dm, B, H, n):
+    """The reference samples at any horizon that is a multiple of 8 (diffusion.py:186-205 takes an arbitrary shape;
+    archive/3_5_long_projection.ipynb cell 19 samples [1, 480, 35] from a model trained at 160).  Above H = 256 a layer's
+    conv output no longer fits the 512 TMEM columns: the l-tiles go through TMEM in rounds and the GroupNorm epilogue
+    parks the raw values in a scratch between its two passes.  Every layer, and a short chain, against the oracle."""
+    sd = O.seeded_state_dict(H=H, seed=7)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    g = torch.Generator().manual_seed(H)
+    x = torch.randn(B, H, 35, generator=g)
+    t = torch.randint(0, 100, (B,), generator=g)
+    rec = {}
+    y_ref = O.unet_forward(sd, x, t, record=rec)
+    y = net(x.cuda(), {}, t.cuda()).cpu()
+    plan = net.plan_for(B, H)
+    for i, (name, C, L) in enumerate(plan.layer_names()):
+        if C == 0:
+            continue
+        got = plan.read_layer(i, C, L).cpu()
+        assert rel(got, rec[name]) < 1e-4, (name, rel(got, rec[name]))
+    assert rel(y, y_ref) < 1e-4
+    if n == 0:
+        return
+    noise = torch.randn(n + 1, B, H, 35, generator=g)
+    mask, value = box_cond(H)
+    ref = O.p_sample_loop(sd, O.make_schedule(n), noise, mask=mask, value=value)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    for fused in (True, False):
+        out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=dm.InjectedNoise(noise),
+                                 conditioning_fn=box_holding, fused=fused)
+        chain = out.chains.cpu()
+        for k in range(n + 1):
+            assert rel(chain[:, k], ref[:, k]) < REL_STEP, (fused, k)
+        m = mask.expand(B, H, 35)
+        assert torch.equal(chain[:, -1][m], ref[:, -1][m])
+        assert tuple(out.trajectories.shape) == (B, H, 35)
+
+
 def test_ddpm_step_kernel_matches_oracle(dm):
     """K4 alone through dm_ddpm_step, both parameterisations, with clamp and a per-sample mask."""
     import ctypes
