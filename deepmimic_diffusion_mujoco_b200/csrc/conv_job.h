@@ -119,6 +119,8 @@ struct ConvJob {
   int sync_local;         // the next layer only reads what THIS CTA wrote (both layers S = 8): block barrier, no cluster barrier
   int pre_next;           // weight loads of the NEXT layer's first chunk the producer may issue during this epilogue
   int next_res;           // the next layer reads this layer's staged tile in place (zero the gaps, defer the store wait)
+  int gaps_clean;         // resident producer whose staging area was last written by an identically laid-out tile (the previous
+                          // layer's, which this layer read in place): the zero halo gaps are still zero, skip re-zeroing them
   int no_store;           // fused loop only: the resident consumer is the ONLY reader of this layer's output, so the tile
                           // never leaves shared memory (no TMA store to the global activation planes)
   // auxiliary 1x1 conv sharing this layer's A operand (ResidualTemporalBlock.residual_conv, temporal.py:34-35,46):

@@ -930,7 +930,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   }
   trace_mark<TR>(tr, 14);
   if (staged) {
-    if (job.next_res) {
+    if (job.next_res && !job.gaps_clean) {
       // zero the halo gaps of every block (other layers' operand stages alias this memory)
       const uint4 z = make_uint4(0u, 0u, 0u, 0u);
       const int per_blk = 2 * kStageGap / 16;

@@ -263,7 +263,11 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   // two MMA issuer warps with one accumulator set each (conv_kernel.cu, mma_unit) when TMEM has room for it
   j.acc2 = 0;
   j.acc2_off = 0;
+#ifdef DM_SINGLE_ISSUER
+  if (false) {
+#else
   if (j.ksteps >= 2 && (acc_sets + j.nphase) * mt_acc * j.ncols <= 512) {
+#endif
     j.acc2 = 1;
     j.acc2_off = j.nphase * mt_acc * j.ncols;
     acc_sets += j.nphase;
@@ -803,6 +807,17 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
         }
     }
   }
+  // Halo gaps of a staged tile stay zero when the bytes were last written by the previous layer's tile of the same geometry
+  // (this layer read that tile in place, its weights ring lies beyond it, residual / auxiliary tiles only touch data rows).
+  for (size_t i = 1; i < P->layers.size(); ++i) {
+    ConvJob& j = P->layers[i].job;
+    const ConvJob& pj = P->layers[i - 1].job;
+    if (P->layers[i].kind != 0 || P->layers[i - 1].kind != 0) continue;
+#ifndef DM_NO_GAPS_CLEAN
+    j.gaps_clean = j.next_res && j.a_res && pj.next_res && pj.st_cw == j.st_cw && pj.st_nq == j.st_nq &&
+                   pj.st_blk_stride == j.st_blk_stride && pj.st_rows == j.st_rows && j.f32_stride == 0;
+#endif
+  }
   // An output tile whose only reader is the next layer's in-place (resident) read never has to reach global memory.
   for (size_t i = 0; i + 1 < P->layers.size(); ++i) {
     Layer& ly = P->layers[i];
@@ -867,6 +882,7 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
     j.a_res = 0;       // per-layer launches always go through global memory
     j.next_res = 0;
     j.no_store = 0;
+    j.gaps_clean = 0;
     j.pre_next = 0;
     j.sync_local = 0;
     DM_CUDA(launch_conv_job(ly.maps, j, P->G, ly.slices, ly.smem, s));
