@@ -401,7 +401,10 @@ def main():
                                  f"{B * H} frames x 420 B; at this size (9 MB) the launch is latency-sized -- inside the "
                                  "fused loop K4 is part of sample_loop_kernel"))
         ms = timed(lambda: scoring.fk_reward(x, ref, 0.016666))
-        kernels.append(hbm_entry("K5 fk_reward_kernel (reward only)", ms, frames * 144, f"{frames} frames x (140 B read + 4 B written)"))
+        k5_note = ("; the kernel is FP32-issue bound, not HBM bound: 1 983 warp instructions per frame, issue slots 70 % busy, FMA pipe "
+                   "56 %, DRAM traffic = algorithmic bytes (ncu, profiles/r1f_ncu_full_summary.md); `frac` is still quoted against HBM")
+        kernels.append(hbm_entry("K5 fk_reward_kernel (reward only)", ms, frames * 144, f"{frames} frames x (140 B read + 4 B written)" + k5_note))
+        kernels[-1]["limiter"] = "fp32-issue"
         ms = timed(lambda: scoring.fk_reward(x, ref, 0.016666, return_body_pos=True))
         kernels.append(hbm_entry("K5 fk_reward_kernel (+ body positions)", ms, frames * 324, f"{frames} frames x (140 + 4 + 180 B)"))
         ms = timed(lambda: scoring.fid_moments(x, s, sxx))
