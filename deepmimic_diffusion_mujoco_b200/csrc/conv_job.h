@@ -108,6 +108,8 @@ struct ConvJob {
   int st_rows;            // rows (l, b) per block = nphase * n_ltiles * Mt * 128
   int st_lbox;            // l extent of the store box = st_rows / S
   int st_blk_stride;      // bytes between staged blocks: kStageGap zero rows | st_rows data rows | kStageGap zero rows
+  int st_wave;            // 1: the tile exceeds the staging budget as a whole; it is staged and stored in waves of four
+                          // (tile, 32-channel) units through two buffers of 2 * st_nq * st_blk_stride bytes (st_rows = rows per wave)
   // resident links (fused loop only): when the next layer's only input is this CTA's staged output tile, the
   // tile stays in shared memory (zero halo gaps around each block) and is read in place by the next layer's
   // MMAs: no TMA round trip through L2, no cluster barrier, and the TMA store of the tile is not waited for.

@@ -32,9 +32,13 @@ namespace dm {
 __device__ __forceinline__ float mish_f(float x) {
   // x * tanh(softplus(x)) == x * a / (a + 2), a = n (n + 2), n = e^x.  torch switches softplus to the identity
   // above 20; here the ratio already rounds to 1 there (a > 2^57), and the clamp keeps n finite.
-  const float n = __expf(fminf(x, 30.f));
+  // Raw MUFU ops: __expf / __fdividef wrap ex2 / rcp in range fix-ups (3 extra instructions each) that cannot trigger
+  // here: a + 2 >= 2, and an e^x that underflows (x < -87) gives mish = 0 where the exact value is below 1e-36.
+  float n, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(n) : "f"(fminf(x, 30.f) * 1.4426950408889634f));
   const float a = n * (n + 2.f);
-  return x * __fdividef(a, a + 2.f);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a + 2.f));
+  return x * (a * r);
 }
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -708,7 +712,8 @@ __device__ __forceinline__ void epilogue_rounds(const ConvJob& job, int warp, in
 // ================================ epilogue (warps 0..15) ===================================
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
-template <bool TR>
+// RD: the "big tile" kernel variants (see mma_unit) also carry the wave-staged pass 2.
+template <bool TR, bool RD>
 __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps* maps, int warp, int g, int b0, int n0,
                                               int rank, const float* tbias, int tbias_stride, uint32_t stg, ConvShared& sh,
                                               uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
@@ -752,7 +757,8 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   // assembled there.  The residual tile (temporal.py:46) is TMA-loaded into the same buffer now; it lands
   // while pass 1 runs.  Block (plane p, channel block q) = kStageGap zero bytes | st_rows rows | kStageGap zero
   // bytes at stg + (p * st_nq + q) * st_blk_stride; the gaps are the conv halo of a resident consumer.
-  const bool staged = job.st_cw != 0;
+  const bool wave = RD && job.st_wave != 0;    // big tiles: staged and stored wave by wave (see pass 2)
+  const bool staged = job.st_cw != 0 && !wave;
   const bool res_staged = staged && job.res != nullptr;
   const uint32_t blk_bytes = (uint32_t)(job.st_rows * job.st_cw * 2);
   const uint32_t blk_stride = (uint32_t)job.st_blk_stride;
@@ -825,6 +831,94 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     mbar_wait(&sh.res_full, rs.res_count & 1, 0x600);
     rs.res_count++;
   }
+  // normalise + Mish + time bias (GroupNorm layers) or bias (others) of the 32 channels [cb, cb + 32) held in v[]
+  auto norm_unit = [&](int cb) {
+    if (gn) {
+      const float* trow_tab = &sh.part[b * (2 * Nc + 4) + 2 * cb];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const float4 s01 = *reinterpret_cast<const float4*>(trow_tab + r * 8);
+        const float4 s23 = *reinterpret_cast<const float4*>(trow_tab + r * 8 + 4);
+        const float4 tb = *reinterpret_cast<const float4*>(&sh.par[3][cb + r * 4]);
+        v[r * 4] = mish_f(fmaf(v[r * 4], s01.x, s01.y)) + tb.x;
+        v[r * 4 + 1] = mish_f(fmaf(v[r * 4 + 1], s01.z, s01.w)) + tb.y;
+        v[r * 4 + 2] = mish_f(fmaf(v[r * 4 + 2], s23.x, s23.y)) + tb.z;
+        v[r * 4 + 3] = mish_f(fmaf(v[r * 4 + 3], s23.z, s23.w)) + tb.w;
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
+        v[r * 4] += bi.x; v[r * 4 + 1] += bi.y; v[r * 4 + 2] += bi.z; v[r * 4 + 3] += bi.w;
+      }
+    }
+    if (gn && tbias != nullptr && tbias_stride != 0) {
+      const float4* tb = reinterpret_cast<const float4*>(tbias + (size_t)bg * tbias_stride + n0 + cb);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float4 t4 = __ldg(tb + e);
+        v[e * 4] += t4.x; v[e * 4 + 1] += t4.y; v[e * 4 + 2] += t4.z; v[e * 4 + 3] += t4.w;
+      }
+    }
+  };
+  if (RD && wave) {
+    // ---- big tiles (they exceed the staging budget as a whole): the (tile, 32-channel) units go out in WAVES of four,
+    //      one unit per slice group = 512 rows x 32 | 256 x 64 | 128 x 128 channels = 64 KB of hi/lo planes, assembled in one
+    //      of two staging buffers in the TMA box layout and written with TMA stores while the next wave is computed.
+    //      The residual arrives the same way: the wave's box is TMA-loaded into the buffer before the wave is computed. ----
+    const uint32_t wave_bytes = 2u * (uint32_t)job.st_nq * blk_stride;
+    const int n_units = MT * nchunks;
+    const int n_waves = (n_units + 3) >> 2;
+    const int tiles_per_wave = 4 / nchunks;          // nchunks in {1, 2, 4}
+    auto load_res = [&](int w) {                      // tid 0: residual boxes of wave w into buffer w & 1
+      const uint32_t buf = stg + (uint32_t)(w & 1) * wave_bytes;
+      mbar_arrive_expect_tx(&sh.res_full, wave_bytes);
+      for (int p = 0; p < 2; ++p)
+        for (int q = 0; q < job.st_nq; ++q)
+          tma_load_5d(buf + (uint32_t)(p * job.st_nq + q) * blk_stride, &maps->r_map, &sh.res_full, n0 + q * job.st_cw, b0,
+                      w * tiles_per_wave * (mrows >> 3), g, p);
+    };
+    const bool wres = job.res != nullptr;
+    if (wres && tid == 0) { tma_store_wait_all(); load_res(0); }
+    for (int w = 0; w < n_waves; ++w) {
+      const uint32_t buf = stg + (uint32_t)(w & 1) * wave_bytes;
+      const int u = 4 * w + slice;
+      const int T = u / nchunks, cc = u - T * nchunks;
+      const int T0 = w * tiles_per_wave;
+      const int j = (T * mrows + row) >> s_shift;
+      if (wres) {
+        mbar_wait(&sh.res_full, rs.res_count & 1, 0x610);
+        rs.res_count++;
+      }
+      if (u < n_units) {
+        const int cb = cbase + cc * 32;
+        tmem_ld32(trow + (uint32_t)(T * ncols + cc * 32), v);
+        tmem_ld_wait();
+        if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * ncols + cc * 32), v);
+        if (j < job.Lj) {
+          norm_unit(cb);
+          staged_write(job, buf, (T - T0) * mrows + row, cb, v, wres);
+        }
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, kEpiThreads);
+      if (tid == 0) {
+        for (int p = 0; p < 2; ++p)
+          for (int q = 0; q < job.st_nq; ++q)
+            tma_store_5d(&maps->o_map, buf + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0,
+                         T0 * (mrows >> 3), g, p);
+        tma_store_commit();
+        if (w + 1 < n_waves) {
+          // buffer (w + 1) & 1 was last read by the store of wave w - 1: at most this wave's group may still be reading
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          if (wres) load_res(w + 1);
+        }
+      }
+      if (w + 1 < n_waves && !wres) named_bar_sync(1, kEpiThreads);   // (with a residual the res_full wait orders the reuse)
+    }
+    if (tid == 0) tma_store_wait_all();   // consumers TMA-load this tile from global memory
+    __syncwarp();
+  } else
   for (int pt = 0; pt < PT; ++pt) {
     const int ph = pt >= MT ? 1 : 0;
     const int T = pt - ph * MT;
@@ -838,33 +932,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       tmem_ld_wait();
       if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + pt * ncols + cc * 32), v);
       if (!ok) continue;
-      if (gn) {
-        const float* trow_tab = &sh.part[b * (2 * Nc + 4) + 2 * cb];
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          const float4 s01 = *reinterpret_cast<const float4*>(trow_tab + r * 8);
-          const float4 s23 = *reinterpret_cast<const float4*>(trow_tab + r * 8 + 4);
-          const float4 tb = *reinterpret_cast<const float4*>(&sh.par[3][cb + r * 4]);
-          v[r * 4] = mish_f(fmaf(v[r * 4], s01.x, s01.y)) + tb.x;
-          v[r * 4 + 1] = mish_f(fmaf(v[r * 4 + 1], s01.z, s01.w)) + tb.y;
-          v[r * 4 + 2] = mish_f(fmaf(v[r * 4 + 2], s23.x, s23.y)) + tb.z;
-          v[r * 4 + 3] = mish_f(fmaf(v[r * 4 + 3], s23.z, s23.w)) + tb.w;
-        }
-      } else {
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          const float4 bi = *reinterpret_cast<const float4*>(&sh.par[0][cb + r * 4]);
-          v[r * 4] += bi.x; v[r * 4 + 1] += bi.y; v[r * 4 + 2] += bi.z; v[r * 4 + 3] += bi.w;
-        }
-      }
-      if (gn && tbias != nullptr && tbias_stride != 0) {
-        const float4* tb = reinterpret_cast<const float4*>(tbias + (size_t)bg * tbias_stride + n0 + cb);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float4 t4 = __ldg(tb + e);
-          v[e * 4] += t4.x; v[e * 4 + 1] += t4.y; v[e * 4 + 2] += t4.z; v[e * 4 + 3] += t4.w;
-        }
-      }
+      norm_unit(cb);
       if (staged) {
         staged_write(job, stg_data, lrow * S + b, cb, v, res_staged);
       } else {
@@ -983,7 +1051,7 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
     epilogue_rounds<TR>(job, warp, g, b0, n0, rank, tbias, tbias_stride, sh, tmem_base, rs.acc_count);
     rs.acc_count += job.n_rounds;
   } else {
-    epilogue_unit<TR>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
+    epilogue_unit<TR, RD>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
 }
 
@@ -1166,7 +1234,7 @@ cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_grou
   cudaError_t e = ensure_smem_attr();
   if (e != cudaSuccess) return e;
   dim3 grid(2 * n_groups, n_slices);   // one CTA pair (cluster of 2 along x) per 16-sample group
-  if (job.n_rounds > 1) conv_gemm_kernel<true><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+  if (job.n_rounds > 1 || job.st_wave) conv_gemm_kernel<true><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
   else conv_gemm_kernel<false><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
   return cudaGetLastError();
 }
@@ -1175,7 +1243,7 @@ cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStre
   cudaError_t e = ensure_smem_attr();
   if (e != cudaSuccess) return e;
   bool rounds = false;   // any layer that passes through TMEM in rounds (horizons above 256) selects the RD = true variant
-  for (int i = 0; i < lp.n_jobs; ++i) rounds = rounds || lp.jobs[i].n_rounds > 1;
+  for (int i = 0; i < lp.n_jobs; ++i) rounds = rounds || lp.jobs[i].n_rounds > 1 || lp.jobs[i].st_wave;
   if (lp.trace) {
     if (rounds) sample_loop_kernel<true, true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
     else sample_loop_kernel<true, false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);

@@ -124,7 +124,7 @@ static int find_w(const WeightMap& W, const std::string& name, std::vector<int64
 // Weight loads of `nx`'s first channel chunk that may be issued while `cur`'s epilogue runs: ring slots of nx
 // that lie beyond cur's staged output tile (cur's operand stages are dead by then).
 static int prefetchable_w_loads(const ConvJob& cur, const ConvJob& nx) {
-  int cur_st = cur.st_cw ? 2 * cur.st_nq * cur.st_blk_stride : 0;
+  int cur_st = cur.st_cw ? (cur.st_wave ? 2 : 1) * 2 * cur.st_nq * cur.st_blk_stride : 0;
   if (cur.f32_stride && cur.S * cur.f32_stride * 4 > cur_st) cur_st = cur.S * cur.f32_stride * 4;
   const int w_off = nx.a_res ? nx.w_off_res : nx.n_a_stages * nx.a_stage_bytes;
   const int lim = nx.ntaps < nx.n_w_stages ? nx.ntaps : nx.n_w_stages;
@@ -432,13 +432,41 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
                                  (uint64_t)r.C * 2 * kGroupSamples * r.L, (uint64_t)r.plane * 2};
         if ((rc = encode_map(&ly.maps.r_map, r.p, 5, dims, str, box, st_swz))) return rc;
       }
+    } else if (j.n_rounds == 1 && j.nphase == 1 && j.mrows == 128 && (Nc == 32 || Nc == 64 || Nc == 128)) {
+      // big tile: wave-staged epilogue (conv_kernel.cu, pass 2).  One wave = 4 units of 128 rows x 32 channels.
+      const int nchunks = Nc / 32;
+      const int rows_w = 512 / nchunks;
+      j.st_wave = 1;
+      j.st_cw = cw;
+      j.st_nq = Nc / cw;
+      j.st_rows = rows_w;
+      j.st_lbox = rows_w / j.S;
+      j.st_blk_stride = rows_w * cw * 2;
+      st_bytes = (size_t)2 * 2 * j.st_nq * j.st_blk_stride;        // two wave buffers
+      if (ly.smem < st_bytes + 1024) ly.smem = st_bytes + 1024;
+      const int st_swz = cw == 64 ? 2 : 4;
+      const uint32_t box[5] = {(uint32_t)cw, (uint32_t)j.S, (uint32_t)j.st_lbox, 1, 1};
+      {
+        const Act& o = P->acts[ly.out_act];
+        const uint64_t dims[5] = {(uint64_t)o.C, kGroupSamples, (uint64_t)o.L, (uint64_t)P->G, 2};
+        const uint64_t str[4] = {(uint64_t)o.C * 2, (uint64_t)o.C * 2 * kGroupSamples,
+                                 (uint64_t)o.C * 2 * kGroupSamples * o.L, (uint64_t)o.plane * 2};
+        if ((rc = encode_map(&ly.maps.o_map, o.p, 5, dims, str, box, st_swz))) return rc;
+      }
+      if (sp.res >= 0) {
+        const Act& r = P->acts[sp.res];
+        const uint64_t dims[5] = {(uint64_t)r.C, kGroupSamples, (uint64_t)r.L, (uint64_t)P->G, 2};
+        const uint64_t str[4] = {(uint64_t)r.C * 2, (uint64_t)r.C * 2 * kGroupSamples,
+                                 (uint64_t)r.C * 2 * kGroupSamples * r.L, (uint64_t)r.plane * 2};
+        if ((rc = encode_map(&ly.maps.r_map, r.p, 5, dims, str, box, st_swz))) return rc;
+      }
     } else {
       st_bytes = 0;
     }
   }
   // ---- fused auxiliary 1x1 conv (ResidualTemporalBlock.residual_conv): weights, bias, output act + store map ----
   if (!sp.aux_wkey.empty()) {
-    if (!gn || sp.kind != CONV_K5 || sp.res >= 0 || j.st_cw == 0)
+    if (!gn || sp.kind != CONV_K5 || sp.res >= 0 || j.st_cw == 0 || j.st_wave)
       return fail(DM_ERR_STATE, "%s: this layer cannot carry a fused residual conv", sp.name.c_str());
     const float *xw = nullptr, *xb = nullptr;
     if ((rc = find_w(W, sp.aux_wkey + ".weight", {sp.Cout, cin_real, 1}, &xw))) return rc;
@@ -504,7 +532,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     Layer& pv = P->layers.back();
     const ConvJob& pj = pv.job;
     const int halo_hi_rows = (j.box_l - j.halo_lo - Lin) * j.S;
-    const bool ok = pj.st_cw != 0 && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
+    const bool ok = pj.st_cw != 0 && !pj.st_wave && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
                     ly.slices == 1 && pj.st_cw == j.Cc && j.src_chunks[0] == pj.st_nq && j.n_ltiles == 1 &&
                     pj.Lout * pj.S == pj.st_rows && j.halo_lo * j.S * j.row_bytes <= kStageGap &&
                     halo_hi_rows * j.row_bytes <= kStageGap;
