@@ -517,13 +517,12 @@ __device__ __forceinline__ void staged_write(const ConvJob& job, uint32_t stg_da
     const uint32_t a_lo = a_hi + plane_bytes;
     if (add_res) {
       const uint4 hv = lds128(a_hi), lv = lds128(a_lo);
-      const __half2* hh = reinterpret_cast<const __half2*>(&hv);
-      const __half2* ll = reinterpret_cast<const __half2*>(&lv);
+      const unsigned int* hh = reinterpret_cast<const unsigned int*>(&hv);
+      const unsigned int* ll = reinterpret_cast<const unsigned int*>(&lv);
 #pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        const float2 fh = __half22float2(hh[w]), fl = __half22float2(ll[w]);
-        v[q4 * 8 + w * 2] += fh.x + fl.x;
-        v[q4 * 8 + w * 2 + 1] += fh.y + fl.y;
+      for (int w = 0; w < 4; ++w) {   // (v + hi) + lo, one mixed-precision add each
+        v[q4 * 8 + w * 2] = add_f32_h(add_f32_h(v[q4 * 8 + w * 2], (unsigned short)(hh[w] & 0xFFFFu)), (unsigned short)(ll[w] & 0xFFFFu));
+        v[q4 * 8 + w * 2 + 1] = add_f32_h(add_f32_h(v[q4 * 8 + w * 2 + 1], (unsigned short)(hh[w] >> 16)), (unsigned short)(ll[w] >> 16));
       }
     }
     uint4 hv, lv;

@@ -337,12 +337,25 @@ __device__ __forceinline__ void split_half(float v, __half& hi, __half& lo) {
   lo = __float2half_rn(v - __half2float(hi));
 }
 
+// Mixed-precision ALU ops of sm_100 (one instruction instead of convert + add): d = c + float(h) and d = c - float(h).
+__device__ __forceinline__ float add_f32_h(float c, unsigned short h) {
+  float d;
+  asm("add.rn.f32.f16 %0, %1, %2;" : "=f"(d) : "h"(h), "f"(c));
+  return d;
+}
+__device__ __forceinline__ float sub_f32_h(float c, unsigned short h) {   // c - float(h) == fma(h, -1, c), exact for a split
+  float d;
+  asm("fma.rn.f32.f16 %0, %1, %2, %3;" : "=f"(d) : "h"(h), "h"((unsigned short)0xBC00), "f"(c));
+  return d;
+}
+
 // two values at once with the packed converter (cvt.rn.f16x2.f32 is a full-rate ALU op; the scalar
-// cvt.rn.f16.f32 goes through the XU pipe that Mish's ex2/rcp already saturate).  Same rounding as split_half.
+// cvt.rn.f16.f32 goes through the XU pipe that Mish's ex2/rcp already saturate).  Same rounding as split_half:
+// a - float(hi) is exact, here computed by one mixed-precision FMA per value instead of convert + subtract.
 __device__ __forceinline__ void split_half2(float a, float b, __half2& hi, __half2& lo) {
   hi = __floats2half2_rn(a, b);
-  const float2 hf = __half22float2(hi);
-  lo = __floats2half2_rn(a - hf.x, b - hf.y);
+  const unsigned int hb = *reinterpret_cast<const unsigned int*>(&hi);
+  lo = __floats2half2_rn(sub_f32_h(a, (unsigned short)(hb & 0xFFFFu)), sub_f32_h(b, (unsigned short)(hb >> 16)));
 }
 
 }  // namespace dm
