@@ -814,9 +814,13 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         tmem_ld32(trow + (uint32_t)(T * ncols + cc * 32), v);
         tmem_ld_wait();
         if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * ncols + cc * 32), v);
+        // the two issuer warps' accumulator sets are folded ONCE: the sum goes back into set 0 (tcgen05.st), and pass 2
+        // (same thread, same unit) needs a single TMEM load
+        if (job.acc2) tmem_st32(trow + (uint32_t)(T * ncols + cc * 32), v);
         gn_accumulate_unit(job, v, &sh.par[0][cbase + cc * 32], ok, lane, &sh.part[warp * 256], &sh.qgrp[(cbase >> 2) + cc * 8]);
       }
     }
+    if (job.acc2) tmem_st_wait();
     trace_mark<TR>(tr, 40);
     if (job.aux && tid == 0) tma_store_wait_read();   // the auxiliary tile has left the staging buffer
     gn_finalize(job, sh, tid, Nc);
@@ -893,7 +897,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         const int cb = cbase + cc * 32;
         tmem_ld32(trow + (uint32_t)(T * ncols + cc * 32), v);
         tmem_ld_wait();
-        if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * ncols + cc * 32), v);
+        if (job.acc2 && !gn) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + T * ncols + cc * 32), v);
         if (j < job.Lj) {
           norm_unit(cb);
           staged_write(job, buf, (T - T0) * mrows + row, cb, v, wres);
@@ -929,7 +933,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       const int cb = cbase + cc * 32;
       tmem_ld32(trow + (uint32_t)(pt * ncols + cc * 32), v);
       tmem_ld_wait();
-      if (job.acc2) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + pt * ncols + cc * 32), v);
+      if (job.acc2 && !gn) tmem_ld32_add(trow + (uint32_t)(job.acc2_off + pt * ncols + cc * 32), v);   // (GroupNorm layers: folded in pass 1)
       if (!ok) continue;
       norm_unit(cb);
       if (staged) {
