@@ -56,6 +56,13 @@ DM_HD void sincos_half(float th, float& s, float& c) {
   float t = fmaf(k, -6.2831854820251465f, th);
   t = fmaf(k, 1.7484555e-7f, t);
   const float r = 0.5f * t;
+#if defined(__CUDA_ARCH__)
+  // device: the SFU's sin / cos on the reduced half angle (|r| <= pi/2; absolute error ~4e-7 each): 4 instructions instead of
+  // the 13 of the two polynomials.  FK positions stay within 3e-6 m of the float64 oracle (bar: 1e-5 m).
+  s = __sinf(r);
+  c = __cosf(r);
+  return;
+#endif
   const float z = r * r;
   float ps = 2.6052249021813675e-06f;
   ps = fmaf(ps, z, -0.00019809075284523637f);
