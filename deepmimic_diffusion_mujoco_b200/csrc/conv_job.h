@@ -61,7 +61,14 @@ struct ConvJob {
   int n_ltiles;
   int Mt;                 // MMA tiles (mrows rows per CTA) per l-tile
   int Lj;                 // number of valid M positions (Lout, or Lin for ConvTranspose)
-  int Lout;               // output length
+  int Lout;               // output length (of this CTA pair's share, see `ls`)
+  // L-split (ls = 1; small batches at long horizons): a cluster of FOUR CTAs = two pairs owns the group, pair h works on
+  // positions [h * L / 2, (h + 1) * L / 2) of every layer.  Lj / Lout / tiles describe ONE half; the kernel adds the offsets:
+  // (flag `ls` in the byte block at the end)
+  int ls_in;              // input positions between the halves' A boxes  (l_stride * Lj)
+  int ls_out;             // output positions between the halves' rows    (Lout)
+  int Lfull_out;          // length of the whole output activation (row addressing); == Lout when ls == 0
+  int gn_L;               // positions one GroupNorm statistic covers (both halves); == Lj when ls == 0
   int ntaps;
   ConvTap taps[kMaxTaps];
   int nphase;
@@ -79,13 +86,11 @@ struct ConvJob {
   int tmem_cols;
   int mma_mode;           // 0: warp A issues every MMA; 1: the two issuer warps split the k-steps of every tap, each
                           // with its own accumulator set (see mma_unit)
-  int acc2;               // 1: a second accumulator set at TMEM column acc2_off is added by the epilogue
   int acc2_off;
   // epilogue
   int epi;
   int Cout;               // real output channels
   int cg;                 // channels per GroupNorm group
-  int cg_pow2;            // cg is a power of two (lets the epilogue fold partial sums by shifts)
   int B;                  // real batch (masks the fp32 output)
   const float* bias;      // [CoutPad]
   const float* gamma;     // [CoutPad]
@@ -108,29 +113,33 @@ struct ConvJob {
   int st_rows;            // rows (l, b) per block = nphase * n_ltiles * Mt * 128
   int st_lbox;            // l extent of the store box = st_rows / S
   int st_blk_stride;      // bytes between staged blocks: kStageGap zero rows | st_rows data rows | kStageGap zero rows
-  int st_wave;            // 1: the tile exceeds the staging budget as a whole; it is staged and stored in waves of four
-                          // (tile, 32-channel) units through two buffers of 2 * st_nq * st_blk_stride bytes (st_rows = rows per wave)
   // resident links (fused loop only): when the next layer's only input is this CTA's staged output tile, the
   // tile stays in shared memory (zero halo gaps around each block) and is read in place by the next layer's
   // MMAs: no TMA round trip through L2, no cluster barrier, and the TMA store of the tile is not waited for.
-  int a_res;              // this layer's A operand is the previous layer's staged tile
   int a_res_off;          // byte offset (from the smem base) of chunk 0 / plane 0 of the A view (row l = -halo_lo)
   int a_res_chunk;        // bytes between channel chunks of the resident tile
   int a_res_plane;        // bytes between the hi and lo planes of the resident tile
   int w_off_res;          // weight ring offset when a_res (beyond every staged tile)
-  int sync_local;         // the next layer only reads what THIS CTA wrote (both layers S = 8): block barrier, no cluster barrier
   int pre_next;           // weight loads of the NEXT layer's first chunk the producer may issue during this epilogue
-  int next_res;           // the next layer reads this layer's staged tile in place (zero the gaps, defer the store wait)
-  int gaps_clean;         // resident producer whose staging area was last written by an identically laid-out tile (the previous
-                          // layer's, which this layer read in place): the zero halo gaps are still zero, skip re-zeroing them
-  int no_store;           // fused loop only: the resident consumer is the ONLY reader of this layer's output, so the tile
-                          // never leaves shared memory (no TMA store to the global activation planes)
   // auxiliary 1x1 conv sharing this layer's A operand (ResidualTemporalBlock.residual_conv, temporal.py:34-35,46):
   // one extra weight tile per channel chunk, accumulated into its own TMEM columns, bias-only epilogue
-  int aux;                // 1 if present
   int aux_shift;          // l offset of the 1x1 tap inside the A box (= halo_lo)
   int aux_col0;           // first TMEM column of the auxiliary accumulators
   const float* aux_bias;  // [CoutPad]
+  // one-byte flags, kept together (80 descriptors share the 32 KB kernel-parameter block)
+  unsigned char ls;                 // 1: L-split job (see ls_in / ls_out above)
+  unsigned char cg_pow2;            // cg is a power of two (lets the epilogue fold partial sums by shifts)
+  unsigned char a_res;              // this layer's A operand is the previous layer's staged tile
+  unsigned char sync_local;         // the next layer only reads what THIS CTA wrote (both layers S = 8): block barrier, no cluster barrier
+  unsigned char next_res;           // the next layer reads this layer's staged tile in place (zero the gaps, defer the store wait)
+  unsigned char gaps_clean;         // resident producer whose staging area was last written by an identically laid-out tile (the previous
+                          // layer's, which this layer read in place): the zero halo gaps are still zero, skip re-zeroing them
+  unsigned char no_store;           // fused loop only: the resident consumer is the ONLY reader of this layer's output, so the tile
+                          // never leaves shared memory (no TMA store to the global activation planes)
+  unsigned char aux;                // 1: the unit carries the auxiliary 1x1 conv (aux_* above)
+  unsigned char st_wave;            // 1: the tile exceeds the staging budget as a whole; it is staged and stored in waves of four
+                          // (tile, 32-channel) units through two buffers of 2 * st_nq * st_blk_stride bytes (st_rows = rows per wave)
+  unsigned char acc2;               // 1: a second accumulator set at TMEM column acc2_off is added by the epilogue
   // fused-loop bookkeeping
   int slices;             // number of N slices (units per sample sub-group)
   int tb_off;             // offset of the layer's time bias inside a time-bias table row, or -1

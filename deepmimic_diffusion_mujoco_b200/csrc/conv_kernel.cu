@@ -66,7 +66,9 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full, res_full;
   uint64_t tile_ready;   // resident link (leader CTA's copy is the live one): both CTAs' staged tiles are complete
+  uint64_t xstat_full;   // L-split: the twin CTA (other half of L, same samples) has delivered its GroupNorm partial sums
   uint32_t tmem_slot;
+  alignas(8) float xstat[2][128][2];    // L-split: the twin's (sum, sum of squares) per (sample, group), double-buffered by use
   alignas(16) float par[5][256];        // bias, gamma, beta, time bias, auxiliary-conv bias of this unit's Nc channels
   alignas(16) unsigned char qgrp[64];   // GroupNorm group (within the unit) of every 4-channel quad
   float stat[16][8][2];                 // per (sample, group): mean, rstd
@@ -79,8 +81,10 @@ struct ConvShared {
 // used; producer and MMA issuer walk the same stage sequence, so their private copies stay in step even
 // though ring depths change from layer to layer inside the persistent kernel.
 struct RoleState {
-  uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0, tile_count = 0;
+  uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0, tile_count = 0, x_count = 0;
   int pre_w = 0;   // producer: weight loads of the current unit that were already issued during the previous epilogue
+  int lhalf = 0;       // L-split: which half of the positions this CTA's pair works on (0 when the job is not split)
+  int pair_base = 0;   // rank of the pair's leader inside the cluster (0, or 2 for the second pair of a cluster of four)
 };
 
 __device__ __forceinline__ void init_shared(ConvShared& sh) {
@@ -89,6 +93,7 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
   mbar_init(&sh.acc_full, 2);
   mbar_init(&sh.res_full, 1);
   mbar_init(&sh.tile_ready, 2);   // one arrival from each CTA of the pair (the peer's is remote)
+  mbar_init(&sh.xstat_full, 128);  // one remote arrival per (sample, group) value pair the twin writes
   fence_barrier_init();
 }
 
@@ -108,7 +113,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
-    const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo;
+    const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo + rs.lhalf * job.ls_in;
     int chunk0 = 0;   // index of the source's first channel chunk inside the concatenated input (weights are chunk-major)
     for (int src = 0; src < job.nsrc; ++src) {
       const int nch = job.src_chunks[src];
@@ -211,7 +216,8 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const uint32_t a_plane16 = (uint32_t)(job.a_res ? job.a_res_plane : job.a_plane_bytes) >> 4;
   const uint32_t w_plane16 = job.w_plane_bytes >> 4;
   const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
-  const uint32_t peer_w_empty = mapa_u32(smem_u32(&sh.w_empty[0]), 1);   // the peer CTA's copy of the ring's empty barriers
+  const uint32_t peer_w_empty = mapa_u32(smem_u32(&sh.w_empty[0]), (uint32_t)rs.pair_base + 1);   // the peer CTA's copy of the ring's empty barriers
+  const unsigned short cmask = (unsigned short)(3u << rs.pair_base);     // the pair's ranks, for the multicast commits
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 21);
   int lt_in = 0;            // l-tile index inside the current TMEM round
@@ -306,24 +312,24 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
 #endif
             __syncwarp();
             if (leader) {
-              umma_commit_pair(&sh.w_empty[ws]);
-              if (mode == 2) umma_commit_pair(&sh.w_empty[ws]);   // the owner's release counts for both warps
+              umma_commit_pair(&sh.w_empty[ws], cmask);
+              if (mode == 2) umma_commit_pair(&sh.w_empty[ws], cmask);   // the owner's release counts for both warps
             }
           }
           ++wi;
           if (++ws == job.n_w_stages) ws = 0;
         }
         if (!job.a_res) {
-          if (leader) umma_commit_pair(&sh.a_empty[as]);
+          if (leader) umma_commit_pair(&sh.a_empty[as], cmask);
           if (++as == job.n_a_stages) as = 0;
         }
       }
     }
     if (!RD) {
-      if (lt + 1 == job.n_ltiles && leader) umma_commit_pair(&sh.acc_full);
+      if (lt + 1 == job.n_ltiles && leader) umma_commit_pair(&sh.acc_full, cmask);
     } else if (++lt_in == job.lt_round || lt + 1 == job.n_ltiles) {   // end of a TMEM round: hand the accumulators to the epilogues
       lt_in = 0;
-      if (leader) umma_commit_pair(&sh.acc_full);
+      if (leader) umma_commit_pair(&sh.acc_full, cmask);
       if (lt + 1 < job.n_ltiles) {
         // the next round overwrites these columns in BOTH CTAs: wait until both epilogues have drained them
         mbar_wait_cluster(&sh.tile_ready, rs.tile_count & 1, 0x320);
@@ -453,7 +459,11 @@ __device__ __forceinline__ void gn_accumulate_unit(const ConvJob& job, const flo
 // GroupNorm statistics -> per-(sample, channel) scale / shift table.  Called by all epilogue threads once every warp has
 // accumulated its partial sums: fixed-order combination over the warps (deterministic), then
 //   y = x * sc + sf,  sc = rstd * gamma,  sf = (bias - mean) * sc + beta      (table rows of 2 * Nc + 4 floats in sh.part)
-__device__ __forceinline__ void gn_finalize(const ConvJob& job, ConvShared& sh, int tid, int Nc) {
+// L-split: the twin CTA (same samples, other half of the positions) holds the other half of every sum: the 128 combining
+// threads write theirs into the twin's sh.xstat (st.shared::cluster + remote mbarrier arrive), wait for the twin's, and add
+// the two in a fixed order (half 0 first), so both CTAs normalise with bit-identical statistics.
+__device__ __forceinline__ void gn_finalize(const ConvJob& job, ConvShared& sh, int tid, int Nc, int lhalf = 0,
+                                            int pair_base = 0, int rank = 0, uint32_t x_parity = 0) {
   constexpr int S = 8;
   named_bar_sync(1, kEpiThreads);
   if (tid < 128) {                       // one thread per (sample, group): fixed-order sum over the warps
@@ -464,7 +474,16 @@ __device__ __forceinline__ void gn_finalize(const ConvJob& job, ConvShared& sh, 
       a += pv.x;
       q2 += pv.y;
     }
-    const float inv_n = 1.f / (float)(job.cg * job.Lj);
+    if (job.ls) {
+      const uint32_t twin = (uint32_t)((pair_base ^ 2) + rank);
+      st_remote_f32x2(mapa_u32(smem_u32(&sh.xstat[x_parity][tid][0]), twin), a, q2);
+      mbar_arrive_remote(mapa_u32(smem_u32(&sh.xstat_full), twin));          // release.cluster: orders the store before it
+      mbar_wait_cluster(&sh.xstat_full, x_parity, 0x530);
+      const float2 o = *reinterpret_cast<const float2*>(&sh.xstat[x_parity][tid][0]);
+      a = lhalf == 0 ? a + o.x : o.x + a;
+      q2 = lhalf == 0 ? q2 + o.y : o.y + q2;
+    }
+    const float inv_n = 1.f / (float)(job.cg * job.gn_L);
     const float mean = a * inv_n;
     const float var = fmaxf(q2 * inv_n - mean * mean, 0.f);
     (&sh.stat[0][0][0])[tid * 2] = mean;
@@ -731,6 +750,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   const int b = row & (S - 1);
   const bool gn = job.epi == EPI_GN_MISH;
   const bool tb_uniform = tbias != nullptr && tbias_stride == 0;
+  const int loff = rs.lhalf * job.ls_out;        // L-split: first output position of this pair's half (0 otherwise)
 
   for (int i = tid; i < Nc; i += kEpiThreads) {
     sh.par[0][i] = __ldg(job.bias + n0 + i);
@@ -769,7 +789,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
           tma_load_5d(stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, &maps->r_map, &sh.res_full,
-                      n0 + q * job.st_cw, b0, 0, g, p);
+                      n0 + q * job.st_cw, b0, loff, g, p);
     }
     __syncwarp();
   }
@@ -799,7 +819,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     if (tid == 0) {
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
-          tma_store_5d(&maps->p_map, stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0, 0,
+          tma_store_5d(&maps->p_map, stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0, loff,
                        g, p);
       tma_store_commit();
     }
@@ -823,7 +843,8 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     if (job.acc2) tmem_st_wait();
     trace_mark<TR>(tr, 40);
     if (job.aux && tid == 0) tma_store_wait_read();   // the auxiliary tile has left the staging buffer
-    gn_finalize(job, sh, tid, Nc);
+    gn_finalize(job, sh, tid, Nc, rs.lhalf, rs.pair_base, rank, rs.x_count & 1);
+    if (job.ls) rs.x_count++;
   }
   trace_mark<TR>(tr, 10);
 
@@ -879,7 +900,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
           tma_load_5d(buf + (uint32_t)(p * job.st_nq + q) * blk_stride, &maps->r_map, &sh.res_full, n0 + q * job.st_cw, b0,
-                      w * tiles_per_wave * (mrows >> 3), g, p);
+                      loff + w * tiles_per_wave * (mrows >> 3), g, p);
     };
     const bool wres = job.res != nullptr;
     if (wres && tid == 0) { tma_store_wait_all(); load_res(0); }
@@ -909,7 +930,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         for (int p = 0; p < 2; ++p)
           for (int q = 0; q < job.st_nq; ++q)
             tma_store_5d(&maps->o_map, buf + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0,
-                         T0 * (mrows >> 3), g, p);
+                         loff + T0 * (mrows >> 3), g, p);
         tma_store_commit();
         if (w + 1 < n_waves) {
           // buffer (w + 1) & 1 was last read by the store of wave w - 1: at most this wave's group may still be reading
@@ -928,7 +949,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     const int j = (T * mrows + row) >> s_shift;
     const bool ok = j < job.Lj;
     const int lrow = job.nphase == 2 ? 2 * j + ph : j;
-    const size_t rowoff = ((size_t)g * job.Lout + lrow) * kGroupSamples + b0 + b;
+    const size_t rowoff = ((size_t)g * job.Lfull_out + loff + lrow) * kGroupSamples + b0 + b;
     for (int cc = (slice - pt * nchunks) & 3; cc < nchunks; cc += 4) {
       const int cb = cbase + cc * 32;
       tmem_ld32(trow + (uint32_t)(pt * ncols + cc * 32), v);
@@ -979,7 +1000,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
         for (int e = 0; e < 32; ++e)
           if (n0 + cb + e < job.Cout) sts32(so + 4u * e, v[e]);
       } else if (job.out_f32 && bg < job.B) {
-        float* of = job.out_f32 + ((size_t)bg * job.Lout + lrow) * job.out_f32_C;
+        float* of = job.out_f32 + ((size_t)bg * job.Lfull_out + loff + lrow) * job.out_f32_C;
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
           const int c = n0 + cb + e;
@@ -995,7 +1016,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       const int bb = i / per, o = i - bb * per;
       const int sg = g * kGroupSamples + b0 + bb;
       if (sg < job.B)
-        reinterpret_cast<float4*>(job.out_f32 + (size_t)sg * job.Lout * job.out_f32_C)[o] =
+        reinterpret_cast<float4*>(job.out_f32 + ((size_t)sg * job.Lfull_out + loff) * job.out_f32_C)[o] =
             lds128f(stg + 4u * (uint32_t)(bb * job.f32_stride) + 16u * (uint32_t)o);
     }
   }
@@ -1016,13 +1037,13 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     named_bar_sync(1, kEpiThreads);
     if (job.next_res && threadIdx.x == 0) {   // releases the leader's MMA warps waiting in the next layer (one arrival per CTA)
       if (rank == 0) mbar_arrive(&sh.tile_ready);
-      else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), 0));
+      else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)rs.pair_base));
     }
     trace_mark<TR>(tr, 15);
     if (tid == 0 && !job.no_store) {
       for (int p = 0; p < 2; ++p)
         for (int q = 0; q < job.st_nq; ++q)
-          tma_store_5d(&maps->o_map, stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0, 0,
+          tma_store_5d(&maps->o_map, stg_data + (uint32_t)(p * job.st_nq + q) * blk_stride, n0 + q * job.st_cw, b0, loff,
                        g, p);
       tma_store_commit();
       // a non-resident consumer TMA-loads this tile from global, and the staging is reused by the next unit's
@@ -1086,13 +1107,15 @@ __device__ __forceinline__ uint32_t aligned_dyn_smem() {
 // ------------------------------------------------------------------------------------------------
 // per-layer launch: grid = (2 CTAs per 16-sample group, N slices), clusters of 2 along x (the CTA pair)
 // ------------------------------------------------------------------------------------------------
-template <bool RD>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
+// LS: L-split launch (conv_job.h): clusters of 4 = two pairs per group, pair h = cluster rank / 2 owns half h of the positions.
+template <bool RD, bool LS>
+__global__ void __cluster_dims__(LS ? 4 : 2, 1, 1) __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvJob job) {
   const uint32_t smem = aligned_dyn_smem();
   __shared__ ConvShared sh;
   const int warp = warp_idx_sync();
-  const int rank = (int)cluster_ctarank();
+  const int crank = (int)cluster_ctarank();
+  const int rank = crank & 1;
   if (warp == kProducerWarp && elect_one_sync()) {
     tma_prefetch_desc(&maps.a_map[0]);
     if (job.nsrc > 1) tma_prefetch_desc(&maps.a_map[1]);
@@ -1100,8 +1123,10 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   }
   const uint32_t tmem_base = pair_begin(sh, warp, job.tmem_cols);
   RoleState rs;
-  run_unit<false, RD>(job, &maps, warp, rank, (int)(blockIdx.x >> 1), blockIdx.y * job.Nc, job.tbias, job.tbias_stride, smem, sh,
-                  tmem_base, rs);
+  rs.lhalf = LS ? crank >> 1 : 0;
+  rs.pair_base = crank & ~1;
+  run_unit<false, RD>(job, &maps, warp, rank, (int)(blockIdx.x >> (LS ? 2 : 1)), blockIdx.y * job.Nc, job.tbias, job.tbias_stride,
+                      smem, sh, tmem_base, rs);
   pair_end(warp, tmem_base, job.tmem_cols);
 }
 
@@ -1127,28 +1152,33 @@ __device__ __forceinline__ void local_sync(bool wrote_global, bool issues_tma) {
   if (issues_tma) fence_proxy_async_global();
 }
 
-template <bool TR, bool RD>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
+template <bool TR, bool RD, bool LS>
+__global__ void __cluster_dims__(LS ? 4 : 2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   const uint32_t smem = aligned_dyn_smem();
   __shared__ ConvShared sh;
   __shared__ StepParams sstep;
   const int warp = warp_idx_sync();
-  const int rank = (int)cluster_ctarank();
+  const int crank = (int)cluster_ctarank();
+  const int rank = crank & 1;
   const int g = (int)cluster_id_x();
   const uint32_t tmem_base = pair_begin(sh, warp, 512);
   RoleState rs;
+  rs.lhalf = LS ? crank >> 1 : 0;
+  rs.pair_base = crank & ~1;
 
+  // K4 works on whole samples: 8 per CTA, or 4 per CTA of an L-split cluster (every CTA of the group takes a share)
   const long long ht4 = ((long long)lp.H * lp.T) >> 2;           // float4 per sample
-  const int s_lo = g * kGroupSamples + rank * 8;
-  const int s_hi = min(lp.B, s_lo + 8);
+  const int k4_n = LS ? 4 : 8;
+  const int s_lo = g * kGroupSamples + crank * k4_n;
+  const int s_hi = min(lp.B, s_lo + k4_n);
 
   for (int k = 0; k <= lp.n_steps; ++k) {
     if (k > 0) {
       const int t_index = lp.steps[k].t_index;
       for (int ji = 0; ji < lp.n_jobs; ++ji) {
         const ConvJob& job = lp.jobs[ji];   // kernel-parameter (constant) space: warp-uniform
-        unsigned long long* tr = (TR && lp.trace && g == lp.trace_cluster && rank == 0 && k == lp.trace_step)
+        unsigned long long* tr = (TR && lp.trace && g == lp.trace_cluster && crank == 0 && k == lp.trace_step)
                                      ? lp.trace + (size_t)ji * kTraceSlots : nullptr;
         if (TR && threadIdx.x == 0 && tr) { trace_mark<TR>(tr, 0); tr[1] = (unsigned long long)clock64(); }   // slot 1: SM clock (effective MHz)
         if (TR && threadIdx.x == kMmaWarp * 32 && tr) trace_mark<TR>(tr, 22);
@@ -1174,7 +1204,8 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
                        last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, 0);
           if (sl + 1 < slices) {   // TMEM / staging smem are reused by the next unit (the peer's side of the pair is
             tc_fence_before();     // protected through the full barriers: its loads for the next unit follow its barrier)
-            __syncthreads();
+            if (LS) cluster_sync_all();   // (L-split: also keeps the twin's next statistics exchange one use behind at most)
+            else __syncthreads();
             tc_fence_after();
           }
         }
@@ -1221,9 +1252,12 @@ static cudaError_t ensure_smem_attr() {
   if (e != cudaSuccess) return e;
   std::lock_guard<std::mutex> lock(mu);
   if (dev >= 0 && dev < 64 && done[dev]) return cudaSuccess;
-  const void* kernels[] = {(const void*)conv_gemm_kernel<false>, (const void*)conv_gemm_kernel<true>,
-                           (const void*)sample_loop_kernel<false, false>, (const void*)sample_loop_kernel<false, true>,
-                           (const void*)sample_loop_kernel<true, false>, (const void*)sample_loop_kernel<true, true>};
+  const void* kernels[] = {(const void*)conv_gemm_kernel<false, false>, (const void*)conv_gemm_kernel<true, false>,
+                           (const void*)conv_gemm_kernel<false, true>, (const void*)conv_gemm_kernel<true, true>,
+                           (const void*)sample_loop_kernel<false, false, false>, (const void*)sample_loop_kernel<false, true, false>,
+                           (const void*)sample_loop_kernel<true, false, false>, (const void*)sample_loop_kernel<true, true, false>,
+                           (const void*)sample_loop_kernel<false, false, true>, (const void*)sample_loop_kernel<false, true, true>,
+                           (const void*)sample_loop_kernel<true, false, true>, (const void*)sample_loop_kernel<true, true, true>};
   for (const void* k : kernels) {
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) break;
@@ -1236,9 +1270,16 @@ cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_grou
                             cudaStream_t stream) {
   cudaError_t e = ensure_smem_attr();
   if (e != cudaSuccess) return e;
-  dim3 grid(2 * n_groups, n_slices);   // one CTA pair (cluster of 2 along x) per 16-sample group
-  if (job.n_rounds > 1 || job.st_wave) conv_gemm_kernel<true><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
-  else conv_gemm_kernel<false><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+  // one CTA pair (cluster of 2 along x) per 16-sample group; two pairs (cluster of 4) when the positions are split
+  dim3 grid((job.ls ? 4 : 2) * n_groups, n_slices);
+  const bool rd = job.n_rounds > 1 || job.st_wave;
+  if (job.ls) {
+    if (rd) conv_gemm_kernel<true, true><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+    else conv_gemm_kernel<false, true><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+  } else {
+    if (rd) conv_gemm_kernel<true, false><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+    else conv_gemm_kernel<false, false><<<grid, kConvThreads, smem_bytes, stream>>>(maps, job);
+  }
   return cudaGetLastError();
 }
 
@@ -1247,13 +1288,17 @@ cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStre
   if (e != cudaSuccess) return e;
   bool rounds = false;   // any layer that passes through TMEM in rounds (horizons above 256) selects the RD = true variant
   for (int i = 0; i < lp.n_jobs; ++i) rounds = rounds || lp.jobs[i].n_rounds > 1 || lp.jobs[i].st_wave;
-  if (lp.trace) {
-    if (rounds) sample_loop_kernel<true, true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
-    else sample_loop_kernel<true, false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+  const bool ls = lp.n_jobs > 0 && lp.jobs[0].ls;   // the plan splits every layer or none
+  const int grid = (ls ? 4 : 2) * lp.G;
+#define DM_LOOP(TR_, RD_, LS_) sample_loop_kernel<TR_, RD_, LS_><<<grid, kConvThreads, smem_bytes, stream>>>(lp)
+  if (ls) {
+    if (lp.trace) { if (rounds) DM_LOOP(true, true, true); else DM_LOOP(true, false, true); }
+    else { if (rounds) DM_LOOP(false, true, true); else DM_LOOP(false, false, true); }
   } else {
-    if (rounds) sample_loop_kernel<false, true><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
-    else sample_loop_kernel<false, false><<<2 * lp.G, kConvThreads, smem_bytes, stream>>>(lp);
+    if (lp.trace) { if (rounds) DM_LOOP(true, true, false); else DM_LOOP(true, false, false); }
+    else { if (rounds) DM_LOOP(false, true, false); else DM_LOOP(false, false, false); }
   }
+#undef DM_LOOP
   return cudaGetLastError();
 }
 

@@ -166,7 +166,12 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   const int Lin = a0.L;
   int ktaps = sp.kind == CONV_K5 ? 5 : sp.kind == CONV_DOWN ? 3 : sp.kind == CONV_K1 ? 1 : 4;
   const int Lout = sp.kind == CONV_DOWN ? Lin / 2 : sp.kind == CONV_T4 ? Lin * 2 : Lin;
-  const int Lj = sp.kind == CONV_T4 ? Lin : Lout;
+  // L-split: all tile geometry below describes ONE pair's half of the positions (Lj, Lo); activations keep their full length
+  const int ls = P->lsplit ? 1 : 0;
+  const int Lj_full = sp.kind == CONV_T4 ? Lin : Lout;
+  if (ls && (Lj_full % 2 || Lout % 2)) return fail(DM_ERR_STATE, "%s: odd length, cannot split the positions", sp.name.c_str());
+  const int Lj = Lj_full >> ls;
+  const int Lo = Lout >> ls;
 
   // channel chunking
   int cin_tot = 0, cin_real = 0;
@@ -215,7 +220,14 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   j.Lt = Mt * pos_per_mt;
   j.box_l = box_for(Mt);
   j.Lj = Lj;
-  j.Lout = Lout;
+  j.Lout = Lo;
+  j.ls = ls;
+  j.ls_in = ls ? j.l_stride * Lj : 0;
+  j.ls_out = ls ? Lo : 0;
+  j.Lfull_out = Lout;
+  j.gn_L = Lj_full;
+  if (ls && (Lj % pos_per_mt || j.n_ltiles * Mt * pos_per_mt != Lj))   // a padded tile's rows would land in the other half
+    return fail(DM_ERR_STATE, "%s: half of the positions is not a whole number of MMA tiles", sp.name.c_str());
   j.a_plane_bytes = j.box_l * j.S * j.row_bytes;
   j.a_tx_bytes = 2 * j.a_plane_bytes;
   j.a_stage_bytes = round_up(j.a_tx_bytes, 1024);
@@ -252,6 +264,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   // lt_round at a time and the GroupNorm epilogue keeps the raw conv output in a global scratch between its two passes
   j.lt_round = j.n_ltiles;
   if (j.nphase * mt_all * j.ncols > 512) {
+    if (ls) return fail(DM_ERR_STATE, "%s: TMEM rounds are not combined with the position split", sp.name.c_str());
     j.lt_round = 512 / (j.nphase * j.Mt * j.ncols);
     if (j.lt_round < 1)
       return fail(DM_ERR_ARG, "%s: one l-tile does not fit the 512 TMEM columns", sp.name.c_str());
@@ -393,7 +406,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (sp.f32_out) {
     j.out_f32 = P->model_out;
     j.out_f32_C = sp.Cout;
-    const int per_sample = Lout * sp.Cout;
+    const int per_sample = Lo * sp.Cout;
     if (per_sample % 4 == 0 && ly.slices == 1 && j.n_rounds == 1 && (size_t)j.S * (per_sample + 4) * 4 <= (size_t)budget) {
       j.f32_stride = per_sample + 4;
       const size_t need = (size_t)j.S * j.f32_stride * 4 + 1024;
@@ -436,6 +449,8 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
       // big tile: wave-staged epilogue (conv_kernel.cu, pass 2).  One wave = 4 units of 128 rows x 32 channels.
       const int nchunks = Nc / 32;
       const int rows_w = 512 / nchunks;
+      if (ls && (mt_all * nchunks) % 4)   // a partly filled last wave would store rows into the other half
+        return fail(DM_ERR_STATE, "%s: the half does not fill whole staging waves", sp.name.c_str());
       j.st_wave = 1;
       j.st_cw = cw;
       j.st_nq = Nc / cw;
@@ -532,7 +547,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     Layer& pv = P->layers.back();
     const ConvJob& pj = pv.job;
     const int halo_hi_rows = (j.box_l - j.halo_lo - Lin) * j.S;
-    const bool ok = pj.st_cw != 0 && !pj.st_wave && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
+    const bool ok = !ls && pj.st_cw != 0 && !pj.st_wave && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
                     ly.slices == 1 && pj.st_cw == j.Cc && j.src_chunks[0] == pj.st_nq && j.n_ltiles == 1 &&
                     pj.Lout * pj.S == pj.st_rows && j.halo_lo * j.S * j.row_bytes <= kStageGap &&
                     halo_hi_rows * j.row_bytes <= kStageGap;
@@ -815,7 +830,7 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
   }
   P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, P->layers.front().job);
   for (size_t i = 0; i + 1 < P->layers.size(); ++i)
-      P->layers[i].job.sync_local = P->layers[i].job.S == 8 && P->layers[i + 1].job.S == 8;
+      P->layers[i].job.sync_local = !P->lsplit && P->layers[i].job.S == 8 && P->layers[i + 1].job.S == 8;
   if (tb != P->TB) return fail(DM_ERR_ARG, "internal: time-bias layout mismatch (%d vs %d)", tb, P->TB);
   // Scratch for the GroupNorm layers that run in TMEM rounds: [G][Lj][16][cout_pad] fp32, shared by all of them.
   {
@@ -962,13 +977,35 @@ extern "C" int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, 
     t.shape.assign(weights[i].shape, weights[i].shape + weights[i].ndim);
     W[weights[i].name] = t;
   }
-  dm_plan* P = new dm_plan();
-  P->B = B; P->H = H; P->T = T; P->dim = dim;
-  P->G = (B + kGroupSamples - 1) / kGroupSamples;
-  P->mults.assign(dim_mults, dim_mults + n_mults);
-  cudaGetDevice(&P->device);
-  if (cudaEventCreateWithFlags(&P->steps_event, cudaEventDisableTiming) != cudaSuccess) { delete P; return fail(DM_ERR_CUDA, "event create failed"); }
-  rc = build_unet(P, W);
+  // L-split (conv_job.h): when the 16-sample groups would leave more than half of the SMs idle and the horizon is long
+  // enough for every level to split into whole MMA tiles, two CTA pairs share each group.  Layers that cannot be split
+  // (DM_ERR_STATE from add_conv) or an attention model send the build back to the unsplit layout.
+  const int G = (B + kGroupSamples - 1) / kGroupSamples;
+  int n_sm = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+#ifdef DM_NO_LSPLIT
+  bool try_split = false;
+#else
+  bool try_split = 4 * G <= n_sm && H >= 128 && (H >> (n_mults - 1)) % 16 == 0;
+#endif
+  dm_plan* P = nullptr;
+  for (;;) {
+    P = new dm_plan();
+    P->B = B; P->H = H; P->T = T; P->dim = dim;
+    P->G = G;
+    P->lsplit = try_split;
+    P->mults.assign(dim_mults, dim_mults + n_mults);
+    P->device = dev;
+    if (cudaEventCreateWithFlags(&P->steps_event, cudaEventDisableTiming) != cudaSuccess) { delete P; return fail(DM_ERR_CUDA, "event create failed"); }
+    rc = build_unet(P, W);
+    if (try_split && (rc == DM_ERR_STATE || (rc == DM_OK && P->has_attention))) {
+      dm_plan_free(P);
+      try_split = false;
+      continue;
+    }
+    break;
+  }
   if (rc) { dm_plan_free(P); return rc; }
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { dm_plan_free(P); return fail(DM_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); }
@@ -1213,7 +1250,7 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   lp.maps = P->maps_dev;
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
-  lp.k4_local = P->layers.front().job.S == 8 && P->layers.back().job.S == 8;
+  lp.k4_local = !P->lsplit && P->layers.front().job.S == 8 && P->layers.back().job.S == 8;
   lp.trace = P->trace_dev; lp.trace_cluster = P->trace_cluster; lp.trace_step = P->trace_step;
   DM_CUDA(launch_sample_loop(lp, P->loop_smem, s));
   P->last_launches = 1;
@@ -1227,7 +1264,7 @@ extern "C" int dm_plan_layer_info(const dm_plan_t* P, int i, char* name, int nam
   const Layer& ly = P->layers[i];
   if (name && name_cap > 0) snprintf(name, name_cap, "%s", ly.name.c_str());
   if (C) *C = ly.out_act >= 0 ? ly.job.Cout : 0;
-  if (L) *L = ly.job.Lout;
+  if (L) *L = ly.kind == 0 ? ly.job.Lfull_out : ly.job.Lout;
   return DM_OK;
 }
 

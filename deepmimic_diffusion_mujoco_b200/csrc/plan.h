@@ -59,6 +59,7 @@ struct dm_plan {
   std::vector<dm::Act> acts;
   std::vector<dm::Layer> layers;
   int xs_act = -1;
+  bool lsplit = false;             // L-split (conv_job.h): two CTA pairs per 16-sample group, half of the positions each
   bool has_attention = false;      // attention=True: per-layer launches only (the fused loop kernel has no attention stage)
   float* model_out = nullptr;      // fp32 [B,H,T] scratch for the sampling loop
   dm::TimeMlpParams tmlp{};

@@ -210,12 +210,17 @@ __device__ __forceinline__ void umma_f16_pair(uint32_t d_tmem, uint64_t adesc, u
       : "memory");
 }
 // Arrive on the barrier at this offset in BOTH CTAs of the pair once the issuing thread's earlier MMAs have completed.
-__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+// mask: the pair's two ranks inside the cluster (3 for a cluster of two, 3 << 2 for the second pair of a cluster of four).
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar, unsigned short mask = 3) {
   asm volatile(
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
           smem_u32(bar)),
-      "h"((unsigned short)3)
+      "h"(mask)
       : "memory");
+}
+// fp32 pair into another CTA's shared memory (shared::cluster address from mapa)
+__device__ __forceinline__ void st_remote_f32x2(uint32_t remote, float a, float b) {
+  asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(a), "f"(b) : "memory");
 }
 
 // D[tmem] (+)= A[smem] * B[smem], fp16 inputs, fp32 accumulate.  One thread issues.
