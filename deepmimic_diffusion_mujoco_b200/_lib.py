@@ -14,7 +14,7 @@ CSRC = os.path.join(_HERE, "csrc")
 EXPORTS = [
     "dm_last_error", "dm_plan_create", "dm_plan_free", "dm_plan_set_schedule", "dm_unet_forward", "dm_ddpm_step",
     "dm_sample_loop", "dm_fk_reward", "dm_fk_reward_noalloc", "dm_fid_moments", "dm_window_moments", "dm_mocap_to_qpos", "dm_mocap_to_qvel", "dm_motion_dataset", "dm_plan_set_sample_offset", "dm_plan_num_layers", "dm_plan_layer_info",
-    "dm_plan_read_layer", "dm_plan_last_launch_count", "dm_device_error_code", "dm_plan_set_trace",
+    "dm_plan_read_layer", "dm_plan_ctas_per_group", "dm_plan_last_launch_count", "dm_device_error_code", "dm_plan_set_trace",
 ]
 
 
@@ -83,6 +83,7 @@ def lib():
     L.dm_plan_layer_info.argtypes = [vp, ci, ctypes.c_char_p, ci, ctypes.POINTER(ci), ctypes.POINTER(ci)]
     L.dm_plan_read_layer.argtypes = [vp, ci, vp, vp]
     L.dm_plan_last_launch_count.argtypes = [vp]
+    L.dm_plan_ctas_per_group.argtypes = [vp]
     L.dm_plan_set_trace.argtypes = [vp, vp, ci, ci]
     L.dm_device_error_code.argtypes = [ctypes.POINTER(ctypes.c_uint)]
     _lib = L

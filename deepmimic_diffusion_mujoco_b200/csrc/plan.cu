@@ -1259,6 +1259,8 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
 
 extern "C" int dm_plan_num_layers(const dm_plan_t* P) { return P ? (int)P->layers.size() : 0; }
 
+extern "C" int dm_plan_ctas_per_group(const dm_plan_t* P) { return P ? (P->lsplit ? 4 : 2) : 0; }
+
 extern "C" int dm_plan_layer_info(const dm_plan_t* P, int i, char* name, int name_cap, int* C, int* L) {
   if (!P || i < 0 || i >= (int)P->layers.size()) return fail(DM_ERR_ARG, "layer index out of range");
   const Layer& ly = P->layers[i];

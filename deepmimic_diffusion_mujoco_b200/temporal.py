@@ -142,6 +142,10 @@ class UnetPlan:
         _lib.check(_lib.lib().dm_plan_read_layer(self.handle, i, out.data_ptr(), _lib.stream_ptr()))
         return out
 
+    def ctas_per_group(self):
+        """2 = one CTA pair per 16-sample group; 4 = the positions of every layer are split between two pairs."""
+        return _lib.lib().dm_plan_ctas_per_group(self.handle)
+
     def last_launch_count(self):
         return _lib.lib().dm_plan_last_launch_count(self.handle)
 

@@ -148,6 +148,9 @@ int dm_plan_set_sample_offset(dm_plan_t* plan, long long first_sample);
 int dm_plan_num_layers(const dm_plan_t* plan);
 int dm_plan_layer_info(const dm_plan_t* plan, int i, char* name, int name_cap, int* C, int* L);
 int dm_plan_read_layer(dm_plan_t* plan, int i, float* out_dev, dm_stream_t stream);
+/* Test / debug introspection: CTAs that share one 16-sample group -- 2 (one CTA pair), or 4 when the plan splits the
+ * positions of every layer between two pairs (small batches at horizons >= 128; DESIGN.md, "L-split").  0 for NULL. */
+int dm_plan_ctas_per_group(const dm_plan_t* plan);
 /* Debug: record %globaltimer stamps of the phases of every layer of one (cluster, step) of the fused loop into
  * trace_dev (uint64 [num_layers][16]); NULL switches tracing off. */
 int dm_plan_set_trace(dm_plan_t* plan, unsigned long long* trace_dev, int cluster, int step);

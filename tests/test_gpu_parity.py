@@ -278,6 +278,32 @@ def test_full_batch_rows_match_oracle(dm):
     assert torch.equal(chain[:, -1][m], ref[:, -1][m])
 
 
+@pytest.mark.parametrize("B,H,ctas,rows", [(592, 128, 4, [0, 3, 4, 9, 14, 300, 591]), (160, 256, 4, [1, 6, 11, 12, 159]),
+                                             (608, 128, 2, [0, 9, 300, 607]), (608, 256, 2, [0, 15, 607])])
+def test_split_and_unsplit_layouts_at_long_horizons(dm, B, H, ctas, rows):
+    """Small batches at H >= 128 run with FOUR CTAs per 16-sample group (two pairs, half of the positions each, GroupNorm
+    sums exchanged between them); from 4 * groups > SM count on the plan keeps one pair per group.  Both layouts, at the
+    largest split batch and the smallest unsplit one: rows from every CTA's share of the step kernel (samples 4r .. 4r+3
+    of a split group) against the oracle run on just those rows, fused and per-layer launches."""
+    n = 3
+    sd = O.seeded_state_dict(H=H, seed=8)
+    noise = torch.randn(n + 1, B, H, 35, generator=torch.Generator().manual_seed(B + H))
+    mask, value = box_cond(H)
+    ref = O.p_sample_loop(sd, O.make_schedule(n), noise[:, rows].contiguous(), mask=mask, value=value)
+    net = dm.TemporalUnet(H, 35, 35)
+    net.load_state_dict(sd)
+    diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=n, predict_epsilon=False).cuda()
+    for fused in (True, False):
+        out = diff.p_sample_loop((B, H, 35), {}, verbose=False, return_chain=True, sample_fn=dm.InjectedNoise(noise),
+                                 conditioning_fn=box_holding, fused=fused)
+        assert net.plan_for(B, H).ctas_per_group() == ctas
+        chain = out.chains[rows].cpu()
+        for k in range(n + 1):
+            assert rel(chain[:, k], ref[:, k]) < REL_STEP, (fused, k)
+        m = mask.expand(len(rows), H, 35)
+        assert torch.equal(chain[:, -1][m], ref[:, -1][m])
+
+
 @pytest.mark.parametrize("B,H,n", [(2, 480, 3), (1, 512, 2), (1, 1024, 1)])
 def test_horizons_beyond_256_layers_and_chain(dm, B, H, n):
     """The reference samples at any horizon that is a multiple of 8 (diffusion.py:186-205 takes an arbitrary shape;
