@@ -30,6 +30,9 @@ struct ConvTap {       // bytes: 80 of these descriptors travel as ONE kernel pa
 };
 
 enum { EPI_BIAS = 0, EPI_GN_MISH = 1 };
+// ConvJob::kind.  The attention stages (attn_stages.cuh) are jobs of the same list and reuse the descriptor's activation
+// fields; everything about tiles, taps and TMEM is meaningless for them.
+enum { JOB_CONV = 0, JOB_ATTN_NORM = 1, JOB_ATTN_CORE = 2 };
 
 // TMA descriptors of one layer; they live in global memory (or in a __grid_constant__ kernel parameter).
 struct ConvMaps {
@@ -127,6 +130,7 @@ struct ConvJob {
   int aux_col0;           // first TMEM column of the auxiliary accumulators
   const float* aux_bias;  // [CoutPad]
   // one-byte flags, kept together (80 descriptors share the 32 KB kernel-parameter block)
+  unsigned char kind;               // JOB_CONV, or one of the attention stages
   unsigned char ls;                 // 1: L-split job (see ls_in / ls_out above)
   unsigned char cg_pow2;            // cg is a power of two (lets the epilogue fold partial sums by shifts)
   unsigned char a_res;              // this layer's A operand is the previous layer's staged tile

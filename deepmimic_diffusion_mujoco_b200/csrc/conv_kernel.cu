@@ -21,6 +21,7 @@
 //
 // Reference: Conv1dBlock helpers.py:50-69; ResidualTemporalBlock temporal.py:37-46; Downsample1d/Upsample1d
 // helpers.py:32-47; p_sample_loop diffusion.py:186-228 (under /root/reference/diffusion/diffuser/models/).
+#include "attn_stages.cuh"
 #include "conv_job.h"
 #include "ptx.cuh"
 #include "step_device.cuh"
@@ -1152,7 +1153,15 @@ __device__ __forceinline__ void local_sync(bool wrote_global, bool issues_tma) {
   if (issues_tma) fence_proxy_async_global();
 }
 
-template <bool TR, bool RD, bool LS>
+// Out of line on purpose: the stages keep their own register allocation and the conv roles around the call keep theirs.
+__device__ __noinline__ void attn_stage_call(const ConvJob& job, int g, int b0, float* sm) {
+  if (job.kind == JOB_ATTN_NORM) attn_norm_stage(job, g, b0, threadIdx.x);
+  else attn_core_stage(job, g, b0, threadIdx.x, sm);
+}
+
+// AT: the layer list carries attention stages (attn_stages.cuh); a variant of its own so that the common kernels keep their
+// register allocation.
+template <bool TR, bool RD, bool LS, bool AT>
 __global__ void __cluster_dims__(LS ? 4 : 2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   const uint32_t smem = aligned_dyn_smem();
@@ -1185,6 +1194,18 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
 #ifdef DM_DEBUG_WAIT
         if (threadIdx.x == 0) g_dm_dbg_pos[blockIdx.x] = (unsigned)ji | ((unsigned)k << 7);
 #endif
+        if (AT && job.kind != JOB_CONV) {
+          // CUDA-core stage of an attention block: the epilogue warps work on this CTA's 8 samples, global -> global
+          if (warp < kEpiWarps) {
+            extern __shared__ uint8_t smem_raw[];
+            attn_stage_call(job, g, rank * 8, reinterpret_cast<float*>(smem_raw + (smem - smem_u32(smem_raw))));
+            fence_proxy_async_smem();   // the next layer's TMA loads overwrite this shared memory
+          }
+          if (threadIdx.x == 0) trace_mark<TR>(tr, 12);
+          local_sync(warp < kEpiWarps, warp == kProducerWarp);
+          if (threadIdx.x == 0) trace_mark<TR>(tr, 13);
+          continue;
+        }
         const int slices = job.slices;
         const int off = job.tb_off;
         const float* tb = off >= 0 ? lp.tb_table + (size_t)t_index * lp.TB + off : nullptr;
@@ -1254,10 +1275,12 @@ static cudaError_t ensure_smem_attr() {
   if (dev >= 0 && dev < 64 && done[dev]) return cudaSuccess;
   const void* kernels[] = {(const void*)conv_gemm_kernel<false, false>, (const void*)conv_gemm_kernel<true, false>,
                            (const void*)conv_gemm_kernel<false, true>, (const void*)conv_gemm_kernel<true, true>,
-                           (const void*)sample_loop_kernel<false, false, false>, (const void*)sample_loop_kernel<false, true, false>,
-                           (const void*)sample_loop_kernel<true, false, false>, (const void*)sample_loop_kernel<true, true, false>,
-                           (const void*)sample_loop_kernel<false, false, true>, (const void*)sample_loop_kernel<false, true, true>,
-                           (const void*)sample_loop_kernel<true, false, true>, (const void*)sample_loop_kernel<true, true, true>};
+                           (const void*)sample_loop_kernel<false, false, false, false>, (const void*)sample_loop_kernel<false, true, false, false>,
+                           (const void*)sample_loop_kernel<true, false, false, false>, (const void*)sample_loop_kernel<true, true, false, false>,
+                           (const void*)sample_loop_kernel<false, false, true, false>, (const void*)sample_loop_kernel<false, true, true, false>,
+                           (const void*)sample_loop_kernel<true, false, true, false>, (const void*)sample_loop_kernel<true, true, true, false>,
+                           (const void*)sample_loop_kernel<false, false, false, true>, (const void*)sample_loop_kernel<true, false, false, true>,
+                           (const void*)sample_loop_kernel<false, true, false, true>, (const void*)sample_loop_kernel<true, true, false, true>};
   for (const void* k : kernels) {
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) break;
@@ -1290,7 +1313,17 @@ cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStre
   for (int i = 0; i < lp.n_jobs; ++i) rounds = rounds || lp.jobs[i].n_rounds > 1 || lp.jobs[i].st_wave;
   const bool ls = lp.n_jobs > 0 && lp.jobs[0].ls;   // the plan splits every layer or none
   const int grid = (ls ? 4 : 2) * lp.G;
-#define DM_LOOP(TR_, RD_, LS_) sample_loop_kernel<TR_, RD_, LS_><<<grid, kConvThreads, smem_bytes, stream>>>(lp)
+  bool at = false;
+  for (int i = 0; i < lp.n_jobs; ++i) at = at || lp.jobs[i].kind != JOB_CONV;
+  if (at) {
+    if (ls) return cudaErrorInvalidValue;   // (dm_plan_create never splits the positions of an attention model)
+    if (lp.trace) { if (rounds) sample_loop_kernel<true, true, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp);
+                    else sample_loop_kernel<true, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp); }
+    else { if (rounds) sample_loop_kernel<false, true, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp);
+           else sample_loop_kernel<false, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp); }
+    return cudaGetLastError();
+  }
+#define DM_LOOP(TR_, RD_, LS_) sample_loop_kernel<TR_, RD_, LS_, false><<<grid, kConvThreads, smem_bytes, stream>>>(lp)
   if (ls) {
     if (lp.trace) { if (rounds) DM_LOOP(true, true, true); else DM_LOOP(true, false, true); }
     else { if (rounds) DM_LOOP(false, true, true); else DM_LOOP(false, false, true); }

@@ -10,6 +10,7 @@
 #include <string.h>
 
 #include "../../include/dm_b200.h"
+#include "attn_stages.cuh"
 
 namespace dm {
 
@@ -146,7 +147,10 @@ struct ConvSpec {
   int res = -1;          // residual act index
   bool want_act_out = true;
   bool f32_out = false;  // write plan->model_out style fp32 [B,L,Cout]
+  float* f32_dst = nullptr;   // with f32_out: the destination when it is not plan->model_out (attention: the q|k|v rows)
   std::string aux_wkey;  // fused auxiliary 1x1 conv over the same input ("<key>.weight/.bias"), or ""
+  bool no_bias = false;  // Conv1d(bias=False): LinearAttention.to_qkv (helpers.py:114)
+  bool hidden = false;   // intermediate of an attention block (no entry of its own in the oracle's per-layer record)
 };
 
 static int round_up(int a, int b) { return (a + b - 1) / b * b; }
@@ -158,6 +162,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   memset(&j, 0, sizeof(j));
   memset(&ly.maps, 0, sizeof(ly.maps));
   ly.name = sp.name;
+  ly.hidden = sp.hidden;
   ly.tb_off = sp.tb_off;
   for (int s = 0; s < sp.nsrc; ++s) ly.src_acts[s] = sp.src[s];
   ly.res_act = sp.res;
@@ -317,7 +322,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   else rc = find_w(W, sp.wkey + ".weight", {sp.Cout, cin_real, ktaps}, &wsrc);
   if (rc) return rc;
   const float* bsrc = nullptr;
-  if ((rc = find_w(W, sp.wkey + ".bias", {sp.Cout}, &bsrc))) return rc;
+  if (!sp.no_bias && (rc = find_w(W, sp.wkey + ".bias", {sp.Cout}, &bsrc))) return rc;
   const int n_chunks_tot = cin_tot / j.Cc;
   const size_t wplane = (size_t)ktaps * cout_pad * cin_tot;
   auto w_index = [&](int k, int co, int col) {   // col: channel position inside the concatenated, padded input
@@ -366,7 +371,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
 
   // ---- epilogue parameters ----
   std::vector<float> hb(cout_pad, 0.f), hg(cout_pad, 1.f), hbe(cout_pad, 0.f);
-  for (int c = 0; c < sp.Cout; ++c) hb[c] = bsrc[c];
+  for (int c = 0; c < sp.Cout && bsrc; ++c) hb[c] = bsrc[c];
   if (gn) {
     const float *gs = nullptr, *bs = nullptr;
     if ((rc = find_w(W, sp.gnkey + ".weight", {sp.Cout}, &gs))) return rc;
@@ -404,7 +409,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     *out_idx = oi;
   }
   if (sp.f32_out) {
-    j.out_f32 = P->model_out;
+    j.out_f32 = sp.f32_dst ? sp.f32_dst : P->model_out;
     j.out_f32_C = sp.Cout;
     const int per_sample = Lo * sp.Cout;
     if (per_sample % 4 == 0 && ly.slices == 1 && j.n_rounds == 1 && (size_t)j.S * (per_sample + 4) * 4 <= (size_t)budget) {
@@ -547,7 +552,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     Layer& pv = P->layers.back();
     const ConvJob& pj = pv.job;
     const int halo_hi_rows = (j.box_l - j.halo_lo - Lin) * j.S;
-    const bool ok = !ls && pj.st_cw != 0 && !pj.st_wave && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
+    const bool ok = !ls && pv.kind == JOB_CONV && pj.st_cw != 0 && !pj.st_wave && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
                     ly.slices == 1 && pj.st_cw == j.Cc && j.src_chunks[0] == pj.st_nq && j.n_ltiles == 1 &&
                     pj.Lout * pj.S == pj.st_rows && j.halo_lo * j.S * j.row_bytes <= kStageGap &&
                     halo_hi_rows * j.row_bytes <= kStageGap;
@@ -572,7 +577,8 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
     if (j.n_w_stages % 2) j.n_w_stages -= 1;
     if (j.n_w_stages < 2) { j.n_w_stages = 1; j.mma_mode = 1; }
   }
-  if (!P->layers.empty()) P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, j);
+  if (!P->layers.empty() && P->layers.back().kind == JOB_CONV)
+    P->layers.back().job.pre_next = prefetchable_w_loads(P->layers.back().job, j);
   P->layers.push_back(ly);
   return DM_OK;
 }
@@ -654,48 +660,76 @@ static bool has_attention_weights(const WeightMap& W, const std::string& key) {
   return W.find(key + ".fn.fn.to_qkv.weight") != W.end();
 }
 
+// One CUDA-core stage of the attention block (attn_stages.cuh): a job of the layer list that reads activation `src` and
+// writes a new activation of outC channels.
+static int add_attn_stage(dm_plan* P, const std::string& name, int kind, int src, int outC, const float* g, const float* b,
+                          int L_if_no_src, int* out_act) {
+  const int L = src >= 0 ? P->acts[src].L : L_if_no_src;
+  int out, rc;
+  if ((rc = new_act(P, outC, L, &out))) return rc;
+  Layer ly;
+  ly.kind = kind;
+  ly.hidden = true;
+  ly.name = name;
+  ly.out_act = out;
+  ly.src_acts[0] = src;
+  memset(&ly.job, 0, sizeof(ly.job));
+  memset(&ly.maps, 0, sizeof(ly.maps));
+  ConvJob& j = ly.job;
+  j.kind = (unsigned char)kind;
+  j.S = 8;
+  j.Lj = j.Lout = j.Lfull_out = j.gn_L = L;
+  j.Cout = outC;
+  j.B = P->B;
+  j.slices = 1;
+  j.n_rounds = 1;
+  j.tb_off = -1;
+  if (src >= 0) { const Act& in = P->acts[src]; j.res = in.p; j.res_C = in.C; j.res_plane_stride = in.plane; }
+  j.out = P->acts[out].p; j.out_C = outC; j.out_plane_stride = P->acts[out].plane;
+  j.gamma = g; j.beta = b;
+  ly.smem = kind == JOB_ATTN_CORE ? kCoreSmemBytes + 1024 : 0;
+  P->layers.push_back(ly);
+  *out_act = out;
+  return DM_OK;
+}
+
+// Residual(PreNorm(dim, LinearAttention(dim))) (helpers.py:75-131; temporal.py:85,94,103) as four jobs: LayerNorm stage,
+// to_qkv 1x1 conv (tensor pipe), softmax/context stage, to_out 1x1 conv with bias and the block's residual (tensor pipe).
+// The last one carries the block's name; the first three are hidden from dm_plan_layer_info.
 static int add_attention(dm_plan* P, const WeightMap& W, const std::string& key, int src, int C, int* out_act) {
   const Act in = P->acts[src];
   if (in.C != C) return fail(DM_ERR_ARG, "internal: attention input %s is channel padded", key.c_str());
-  const int heads = 4, dh = 32, hid = heads * dh;   // LinearAttention defaults (helpers.py:111); temporal.py never overrides them
-  const float *g, *b, *wqkv, *wout, *bout;
+  const float *g, *b;
   int rc;
   if ((rc = find_w(W, key + ".fn.norm.g", {1, C, 1}, &g))) return rc;
   if ((rc = find_w(W, key + ".fn.norm.b", {1, C, 1}, &b))) return rc;
-  if ((rc = find_w(W, key + ".fn.fn.to_qkv.weight", {3 * hid, C, 1}, &wqkv))) return rc;
-  if ((rc = find_w(W, key + ".fn.fn.to_out.weight", {C, hid, 1}, &wout))) return rc;
-  if ((rc = find_w(W, key + ".fn.fn.to_out.bias", {C}, &bout))) return rc;
-  std::vector<float> wq_t((size_t)C * 3 * hid), wo_t((size_t)hid * C);
-  for (int o = 0; o < 3 * hid; ++o)
-    for (int c = 0; c < C; ++c) wq_t[(size_t)c * 3 * hid + o] = wqkv[(size_t)o * C + c];
-  for (int c = 0; c < C; ++c)
-    for (int j = 0; j < hid; ++j) wo_t[(size_t)j * C + c] = wout[(size_t)c * hid + j];
-  float *dg, *db, *dwq, *dwo, *dbo;
+  float *dg, *db;
   if ((rc = upload(P, std::vector<float>(g, g + C), &dg))) return rc;
   if ((rc = upload(P, std::vector<float>(b, b + C), &db))) return rc;
-  if ((rc = upload(P, wq_t, &dwq))) return rc;
-  if ((rc = upload(P, wo_t, &dwo))) return rc;
-  if ((rc = upload(P, std::vector<float>(bout, bout + C), &dbo))) return rc;
-  int out;
-  if ((rc = new_act(P, C, in.L, &out))) return rc;
-  const int ns = attention_pick_ns(C, in.L);
-  if (ns == 0) return fail(DM_ERR_ARG, "attention tile C=%d L=%d does not fit in shared memory (horizon too long)", C, in.L);
-  Layer ly;
-  ly.kind = 1;
-  ly.name = key;
-  ly.out_act = out;
-  memset(&ly.job, 0, sizeof(ly.job));
-  ly.job.Cout = C;
-  ly.job.Lout = in.L;
-  AttnParams& a = ly.attn;
-  a.in = in.p; a.in_plane = in.plane;
-  a.out = P->acts[out].p; a.out_plane = P->acts[out].plane;
-  a.C = C; a.L = in.L; a.NS = ns; a.heads = heads;
-  a.eps = 1e-5f; a.scale = 1.f / sqrtf((float)dh);
-  a.ln_g = dg; a.ln_b = db; a.wqkv_t = dwq; a.wout_t = dwo; a.bout = dbo;
-  P->layers.push_back(ly);
+  int xn, qkv, o, y;
+  if ((rc = add_attn_stage(P, key + ".norm", JOB_ATTN_NORM, src, C, dg, db, -1, &xn))) return rc;
+  ConvSpec cq;
+  cq.name = key + ".to_qkv";
+  cq.wkey = key + ".fn.fn.to_qkv";
+  cq.kind = CONV_K1;
+  cq.src[0] = xn;
+  cq.src_real_c[0] = C;
+  cq.Cout = 3 * kAttnHid;
+  cq.no_bias = true;
+  cq.hidden = true;
+  if ((rc = add_conv(P, W, cq, &qkv))) return rc;
+  if ((rc = add_attn_stage(P, key + ".core", JOB_ATTN_CORE, qkv, kAttnHid, nullptr, nullptr, -1, &o))) return rc;
+  ConvSpec co;
+  co.name = key;
+  co.wkey = key + ".fn.fn.to_out";
+  co.kind = CONV_K1;
+  co.src[0] = o;
+  co.src_real_c[0] = kAttnHid;
+  co.Cout = C;
+  co.res = src;
+  if ((rc = add_conv(P, W, co, &y))) return rc;
   P->has_attention = true;
-  *out_act = out;
+  *out_act = y;
   return DM_OK;
 }
 
@@ -868,7 +902,6 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     int readers = 0;
     for (size_t k = 0; k < P->layers.size(); ++k) {
       const Layer& c = P->layers[k];
-      if (c.kind == 1) { if (c.attn.in == P->acts[ly.out_act].p) ++readers; continue; }
       for (int s = 0; s < 2; ++s) readers += c.src_acts[s] == ly.out_act;
       readers += c.res_act == ly.out_act;
     }
@@ -911,8 +944,8 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
 // Launch every layer.  tb: time-bias rows; tb_stride 0 = one row for all samples (uniform t).
 static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, cudaStream_t s) {
   for (Layer& ly : P->layers) {
-    if (ly.kind == 1) {
-      DM_CUDA(launch_linear_attention(ly.attn, P->G, s));
+    if (ly.kind != JOB_CONV) {
+      DM_CUDA(launch_attention_stage(ly.job, P->G, s));
       P->last_launches++;
       continue;
     }
@@ -921,7 +954,7 @@ static int run_unet(dm_plan* P, const float* tb, int tb_stride, float* out_f32, 
       j.tbias = tb + ly.tb_off;
       j.tbias_stride = tb_stride;
     }
-    if (j.out_f32) j.out_f32 = out_f32;
+    if (j.out_f32 == P->model_out) j.out_f32 = out_f32;
     j.a_res = 0;       // per-layer launches always go through global memory
     j.next_res = 0;
     j.no_store = 0;
@@ -1206,7 +1239,6 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
     unsigned long long sd = seed;
     DM_CUDA(cudaMemcpyAsync(P->seed_dev, &sd, sizeof(sd), cudaMemcpyHostToDevice, s));
   }
-  if (P->has_attention) fused = 0;   // LinearAttention runs as its own launch between the conv layers
   if (!fused) return enqueue_loop(P, x_dev, have_start, noise_stack_dev, seed, timesteps, predict_epsilon, clip_denoised,
                                   cond, chain_dev, s);
   // ---- persistent cluster kernel: the whole loop is ONE launch ----
@@ -1265,7 +1297,7 @@ extern "C" int dm_plan_layer_info(const dm_plan_t* P, int i, char* name, int nam
   if (!P || i < 0 || i >= (int)P->layers.size()) return fail(DM_ERR_ARG, "layer index out of range");
   const Layer& ly = P->layers[i];
   if (name && name_cap > 0) snprintf(name, name_cap, "%s", ly.name.c_str());
-  if (C) *C = ly.out_act >= 0 ? ly.job.Cout : 0;
+  if (C) *C = ly.out_act >= 0 && !ly.hidden ? ly.job.Cout : 0;
   if (L) *L = ly.kind == 0 ? ly.job.Lfull_out : ly.job.Lout;
   return DM_OK;
 }

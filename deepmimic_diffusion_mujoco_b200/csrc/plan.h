@@ -21,8 +21,8 @@ struct Act {
 };
 
 struct Layer {
-  int kind = 0;          // 0: conv launch (job, maps); 1: Residual(PreNorm(LinearAttention)) launch (attn)
-  AttnParams attn{};
+  int kind = 0;          // == job.kind: JOB_CONV (job, maps), or an attention stage (job only; attn_stages.cuh)
+  bool hidden = false;   // intermediate of an attention block: dm_plan_layer_info reports no output for it
   ConvJob job;
   ConvMaps maps;
   int slices = 1;

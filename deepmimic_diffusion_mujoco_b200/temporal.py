@@ -3,8 +3,9 @@
 Same constructor signature, same parameter construction order (so a seeded default init gives the reference's
 weights) and the same state_dict keys/shapes (so reference checkpoints load); forward() runs the hand-written
 sm_100a kernels through libdm_b200.so.  The nn modules below only HOLD parameters -- none of them is ever
-called.  attention=True adds the Residual(PreNorm(LinearAttention)) stages (helpers.py:75-131) as their own CUDA
-launches between the conv layers; a non-CUDA device is a hard error (no fallback).
+called.  attention=True adds the Residual(PreNorm(LinearAttention)) blocks (helpers.py:75-131): LayerNorm and
+softmax/context stages on the CUDA cores, to_qkv / to_out as 1x1 conv layers on the tensor pipe, all inside the same
+fused loop kernel; a non-CUDA device is a hard error (no fallback).
 """
 import ctypes
 

@@ -37,7 +37,7 @@ if "c2" in which: gd("configs[1] B=1024 H=64 box inpaint", 1024, 64, cond=box)
 if "c3" in which: gd("configs[2] per-GPU share of 8: B=512 H=256 arm limit", 512, 256, cond=box)
 if "c4" in which: gd("configs[3] per-GPU share of 8: B=2048 H=128", 2048, 128)
 if "c5" in which: gd("configs[4] per-GPU share of 8: B=8192 H=64", 8192, 64)
-if "attn" in which: gd("attention=True B=1024 H=64 (per-layer launches)", 1024, 64, attention=True, cond=box)
+if "attn" in which: gd("attention=True B=1024 H=64", 1024, 64, attention=True, cond=box)
 if "unfused" in which:
     net = dm.TemporalUnet(64, 35, 35); net.load_state_dict(O.seeded_state_dict(H=64, seed=0))
     diff = dm.GaussianDiffusion(net, 64, 35, n_timesteps=100, predict_epsilon=False).cuda()

@@ -9,8 +9,9 @@ from deepmimic_diffusion_mujoco_b200 import synthetic as O
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 H = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 steps = 6
-net = dm.TemporalUnet(H, 35, 35)
-net.load_state_dict(O.seeded_state_dict(H=H, seed=0))
+ATTN = bool(os.environ.get("TRACE_ATTN"))
+net = dm.TemporalUnet(H, 35, 35, attention=ATTN)
+net.load_state_dict(O.seeded_state_dict(H=H, seed=0, attention=ATTN))
 diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=steps, predict_epsilon=False).cuda()
 plan = net.plan_for(B, H)
 names = plan.layer_names()
