@@ -254,7 +254,10 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
 
   // N split and TMEM budget.  N = 256 for the 64-row layers (M = 128 pair MMA: the widest N reads A least often), else 128.
   const int n_step = j.mrows == 64 ? 64 : 32;                  // mrows 64: each lane half holds Nc / 2 columns (32-column units)
-  int Nc = cout_pad < (j.mrows == 64 ? 256 : 128) ? cout_pad : (j.mrows == 64 ? 256 : 128);
+  // (the attention block's 384-channel to_qkv layer uses N = 192 when it is a single M tile: two units instead of three,
+  // and the output tile still fits the staged epilogue)
+  const int n_cap = (j.mrows == 64 || (sp.hidden && mt_total == 1)) ? 256 : 128;
+  int Nc = cout_pad < n_cap ? cout_pad : n_cap;
   while (cout_pad % Nc || (gn && Nc % cg)) Nc -= n_step;
   const int mt_all = j.n_ltiles * j.Mt;
   auto tile_cols = [&](int n) { return j.mrows == 64 ? n / 2 : n; };
