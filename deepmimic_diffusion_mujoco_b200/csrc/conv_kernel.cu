@@ -103,7 +103,7 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
 // its own shared memory.  The bytes of both CTAs are counted on the LEADER's full barriers (the leader's MMA warps are
 // the only waiters): the leader arms them with arrive.expect_tx for twice its own byte count, the peer only issues its
 // loads.  Stage reuse is gated per CTA by its own empty barriers, which the MMA commits signal in both CTAs.
-template <bool TR>
+template <bool TR, bool LS>
 __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
                                               const CUtensorMap* x_map, int g, int b0, int n0, int rank, uint32_t a_smem,
                                               uint32_t w_smem, ConvShared& sh, RoleState& rs, unsigned long long* tr,
@@ -114,7 +114,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 2);
   for (int lt = 0; lt < job.n_ltiles; ++lt) {
-    const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo + rs.lhalf * job.ls_in;
+    const int lstart = job.l_stride * (lt * job.Lt) - job.halo_lo + (LS ? rs.lhalf * job.ls_in : 0);
     int chunk0 = 0;   // index of the source's first channel chunk inside the concatenated input (weights are chunk-major)
     for (int src = 0; src < job.nsrc; ++src) {
       const int nch = job.src_chunks[src];
@@ -198,7 +198,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
 // take one commit from each warp as well.
 // RD = false: the kernel variant for plans whose every layer fits TMEM at once (all horizons <= 256): the round logic
 // compiles away.  RD = true: layers may pass through TMEM in rounds (job.n_rounds > 1).
-template <bool TR, bool RD>
+template <bool TR, bool RD, bool LS>
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr,
                                          const int which) {
@@ -217,8 +217,9 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const uint32_t a_plane16 = (uint32_t)(job.a_res ? job.a_res_plane : job.a_plane_bytes) >> 4;
   const uint32_t w_plane16 = job.w_plane_bytes >> 4;
   const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
-  const uint32_t peer_w_empty = mapa_u32(smem_u32(&sh.w_empty[0]), (uint32_t)rs.pair_base + 1);   // the peer CTA's copy of the ring's empty barriers
-  const unsigned short cmask = (unsigned short)(3u << rs.pair_base);     // the pair's ranks, for the multicast commits
+  const int pair_base = LS ? rs.pair_base : 0;   // (a compile-time 0 in the common kernels)
+  const uint32_t peer_w_empty = mapa_u32(smem_u32(&sh.w_empty[0]), (uint32_t)pair_base + 1);   // the peer CTA's copy of the ring's empty barriers
+  const unsigned short cmask = (unsigned short)(3u << pair_base);     // the pair's ranks, for the multicast commits
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 21);
   int lt_in = 0;            // l-tile index inside the current TMEM round
@@ -463,6 +464,7 @@ __device__ __forceinline__ void gn_accumulate_unit(const ConvJob& job, const flo
 // L-split: the twin CTA (same samples, other half of the positions) holds the other half of every sum: the 128 combining
 // threads write theirs into the twin's sh.xstat (st.shared::cluster + remote mbarrier arrive), wait for the twin's, and add
 // the two in a fixed order (half 0 first), so both CTAs normalise with bit-identical statistics.
+template <bool LS>
 __device__ __forceinline__ void gn_finalize(const ConvJob& job, ConvShared& sh, int tid, int Nc, int lhalf = 0,
                                             int pair_base = 0, int rank = 0, uint32_t x_parity = 0) {
   constexpr int S = 8;
@@ -475,7 +477,7 @@ __device__ __forceinline__ void gn_finalize(const ConvJob& job, ConvShared& sh, 
       a += pv.x;
       q2 += pv.y;
     }
-    if (job.ls) {
+    if (LS && job.ls) {
       const uint32_t twin = (uint32_t)((pair_base ^ 2) + rank);
       st_remote_f32x2(mapa_u32(smem_u32(&sh.xstat[x_parity][tid][0]), twin), a, q2);
       mbar_arrive_remote(mapa_u32(smem_u32(&sh.xstat_full), twin));          // release.cluster: orders the store before it
@@ -708,7 +710,7 @@ __device__ __forceinline__ void epilogue_rounds(const ConvJob& job, int warp, in
     }
   }
   if (gn) {
-    gn_finalize(job, sh, tid, Nc);          // (starts with a barrier: every warp's partial sums are complete)
+    gn_finalize<false>(job, sh, tid, Nc);   // (starts with a barrier: every warp's partial sums are complete)
     // pass 2: every thread streams back the raw values it parked (same thread, same addresses: no fence needed)
     for (int T = 0; T < MT_all; ++T) {
       const int j = (T * mrows + row) >> 3;
@@ -732,7 +734,7 @@ __device__ __forceinline__ void epilogue_rounds(const ConvJob& job, int warp, in
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
 // RD: the "big tile" kernel variants (see mma_unit) also carry the wave-staged pass 2.
-template <bool TR, bool RD>
+template <bool TR, bool RD, bool LS>
 __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps* maps, int warp, int g, int b0, int n0,
                                               int rank, const float* tbias, int tbias_stride, uint32_t stg, ConvShared& sh,
                                               uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
@@ -751,7 +753,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
   const int b = row & (S - 1);
   const bool gn = job.epi == EPI_GN_MISH;
   const bool tb_uniform = tbias != nullptr && tbias_stride == 0;
-  const int loff = rs.lhalf * job.ls_out;        // L-split: first output position of this pair's half (0 otherwise)
+  const int loff = LS ? rs.lhalf * job.ls_out : 0;   // L-split: first output position of this pair's half (0 otherwise)
 
   for (int i = tid; i < Nc; i += kEpiThreads) {
     sh.par[0][i] = __ldg(job.bias + n0 + i);
@@ -844,8 +846,8 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     if (job.acc2) tmem_st_wait();
     trace_mark<TR>(tr, 40);
     if (job.aux && tid == 0) tma_store_wait_read();   // the auxiliary tile has left the staging buffer
-    gn_finalize(job, sh, tid, Nc, rs.lhalf, rs.pair_base, rank, rs.x_count & 1);
-    if (job.ls) rs.x_count++;
+    gn_finalize<LS>(job, sh, tid, Nc, rs.lhalf, rs.pair_base, rank, rs.x_count & 1);
+    if (LS && job.ls) rs.x_count++;
   }
   trace_mark<TR>(tr, 10);
 
@@ -1038,7 +1040,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     named_bar_sync(1, kEpiThreads);
     if (job.next_res && threadIdx.x == 0) {   // releases the leader's MMA warps waiting in the next layer (one arrival per CTA)
       if (rank == 0) mbar_arrive(&sh.tile_ready);
-      else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)rs.pair_base));
+      else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)(LS ? rs.pair_base : 0)));
     }
     trace_mark<TR>(tr, 15);
     if (tid == 0 && !job.no_store) {
@@ -1059,7 +1061,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
 
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
 // rank = this CTA's rank in its pair: it owns samples b0 = 8 * rank .. of group g.
-template <bool TR, bool RD>
+template <bool TR, bool RD, bool LS>
 __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp, int rank,
                                          int g, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
@@ -1069,14 +1071,14 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
   const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
   const int b0 = rank * 8;
   if (warp == kProducerWarp) {
-    producer_unit<TR>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, rank, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
+    producer_unit<TR, LS>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, rank, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
   } else if (warp == kMmaWarp || warp == kMmaWarpB) {
-    if (rank == 0) mma_unit<TR, RD>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
+    if (rank == 0) mma_unit<TR, RD, LS>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
   } else if (RD && job.n_rounds > 1) {
     epilogue_rounds<TR>(job, warp, g, b0, n0, rank, tbias, tbias_stride, sh, tmem_base, rs.acc_count);
     rs.acc_count += job.n_rounds;
   } else {
-    epilogue_unit<TR, RD>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
+    epilogue_unit<TR, RD, LS>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
 }
 
@@ -1126,7 +1128,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   RoleState rs;
   rs.lhalf = LS ? crank >> 1 : 0;
   rs.pair_base = crank & ~1;
-  run_unit<false, RD>(job, &maps, warp, rank, (int)(blockIdx.x >> (LS ? 2 : 1)), blockIdx.y * job.Nc, job.tbias, job.tbias_stride,
+  run_unit<false, RD, LS>(job, &maps, warp, rank, (int)(blockIdx.x >> (LS ? 2 : 1)), blockIdx.y * job.Nc, job.tbias, job.tbias_stride,
                       smem, sh, tmem_base, rs);
   pair_end(warp, tmem_base, job.tmem_cols);
 }
@@ -1221,7 +1223,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         for (int sl = 0; sl < slices; ++sl) {      // N slices of the layer, one after the other, by the whole pair
           const bool last_unit = sl + 1 >= slices;
           if (TR && threadIdx.x == kMmaWarp * 32 && tr && sl == 0) trace_mark<TR>(tr, 23);
-          run_unit<TR, RD>(job, maps, warp, rank, g, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == 0 ? tr : nullptr,
+          run_unit<TR, RD, LS>(job, maps, warp, rank, g, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == 0 ? tr : nullptr,
                        last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, 0);
           if (sl + 1 < slices) {   // TMEM / staging smem are reused by the next unit (the peer's side of the pair is
             tc_fence_before();     // protected through the full barriers: its loads for the next unit follow its barrier)
