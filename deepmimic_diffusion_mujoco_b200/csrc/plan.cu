@@ -231,8 +231,9 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   j.ls_out = ls ? Lo : 0;
   j.Lfull_out = Lout;
   j.gn_L = Lj_full;
-  if (ls && (Lj % pos_per_mt || j.n_ltiles * Mt * pos_per_mt != Lj))   // a padded tile's rows would land in the other half
-    return fail(DM_ERR_STATE, "%s: half of the positions is not a whole number of MMA tiles", sp.name.c_str());
+  // a half that is not a whole number of MMA tiles (H = 480: 30 positions at the deepest level): the padded rows of its
+  // last tile must not be stored (they would land in the other half), so the store boxes below cover the valid rows only
+  const bool ls_padded = ls && (Lj % pos_per_mt || j.n_ltiles * Mt * pos_per_mt != Lj);
   j.a_plane_bytes = j.box_l * j.S * j.row_bytes;
   j.a_tx_bytes = 2 * j.a_plane_bytes;
   j.a_stage_bytes = round_up(j.a_tx_bytes, 1024);
@@ -426,14 +427,14 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   size_t st_bytes = 0;
   if (sp.want_act_out) {
     const int rows = j.nphase * mt_all * j.mrows;
-    const int lbox = rows / j.S;
+    const int lbox = ls ? Lo : rows / j.S;           // (unsplit: TMA clips a padded box at the end of the activation)
     const int cw = Nc % 64 == 0 ? 64 : 32;
     const int blk_stride = rows * cw * 2 + 2 * kStageGap;
     st_bytes = (size_t)2 * (Nc / cw) * blk_stride;
     if (lbox <= 256 && st_bytes <= (size_t)budget && j.n_rounds == 1) {
       j.st_cw = cw;
       j.st_nq = Nc / cw;
-      j.st_rows = rows;
+      j.st_rows = lbox * j.S;
       j.st_lbox = lbox;
       j.st_blk_stride = blk_stride;
       if (ly.smem < st_bytes + 1024) ly.smem = st_bytes + 1024;
@@ -453,12 +454,11 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
                                  (uint64_t)r.C * 2 * kGroupSamples * r.L, (uint64_t)r.plane * 2};
         if ((rc = encode_map(&ly.maps.r_map, r.p, 5, dims, str, box, st_swz))) return rc;
       }
-    } else if (j.n_rounds == 1 && j.nphase == 1 && j.mrows == 128 && (Nc == 32 || Nc == 64 || Nc == 128)) {
+    } else if (j.n_rounds == 1 && j.nphase == 1 && j.mrows == 128 && (Nc == 32 || Nc == 64 || Nc == 128) &&
+               !(ls && (ls_padded || (mt_all * (Nc / 32)) % 4))) {   // (split: whole waves only, else the direct stores below)
       // big tile: wave-staged epilogue (conv_kernel.cu, pass 2).  One wave = 4 units of 128 rows x 32 channels.
       const int nchunks = Nc / 32;
       const int rows_w = 512 / nchunks;
-      if (ls && (mt_all * nchunks) % 4)   // a partly filled last wave would store rows into the other half
-        return fail(DM_ERR_STATE, "%s: the half does not fill whole staging waves", sp.name.c_str());
       j.st_wave = 1;
       j.st_cw = cw;
       j.st_nq = Nc / cw;
@@ -1023,7 +1023,7 @@ extern "C" int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, 
 #ifdef DM_NO_LSPLIT
   bool try_split = false;
 #else
-  bool try_split = 4 * G <= n_sm && H >= 128 && (H >> (n_mults - 1)) % 16 == 0;
+  bool try_split = 4 * G <= n_sm && H >= 128 && (H >> (n_mults - 1)) % 2 == 0;
 #endif
   dm_plan* P = nullptr;
   for (;;) {

@@ -308,12 +308,15 @@ def test_full_batch_rows_match_oracle(dm):
 
 
 @pytest.mark.parametrize("B,H,ctas,rows", [(592, 128, 4, [0, 3, 4, 9, 14, 300, 591]), (160, 256, 4, [1, 6, 11, 12, 159]),
-                                             (608, 128, 2, [0, 9, 300, 607]), (608, 256, 2, [0, 15, 607])])
+                                             (608, 128, 2, [0, 9, 300, 607]), (608, 256, 2, [0, 15, 607]),
+                                             (20, 160, 4, [0, 7, 13, 19]), (18, 480, 4, [2, 8, 17]), (608, 480, 2, [5, 607])])
 def test_split_and_unsplit_layouts_at_long_horizons(dm, B, H, ctas, rows):
     """Small batches at H >= 128 run with FOUR CTAs per 16-sample group (two pairs, half of the positions each, GroupNorm
     sums exchanged between them); from 4 * groups > SM count on the plan keeps one pair per group.  Both layouts, at the
     largest split batch and the smallest unsplit one: rows from every CTA's share of the step kernel (samples 4r .. 4r+3
-    of a split group) against the oracle run on just those rows, fused and per-layer launches."""
+    of a split group) against the oracle run on just those rows, fused and per-layer launches.  H = 160 and 480 (the training
+    and projection horizons of archive/3_5_long_projection.ipynb) split into halves that are NOT whole MMA tiles (padded last
+    tile, direct stores); unsplit, H = 480 goes through TMEM in rounds."""
     n = 3
     sd = O.seeded_state_dict(H=H, seed=8)
     noise = torch.randn(n + 1, B, H, 35, generator=torch.Generator().manual_seed(B + H))
