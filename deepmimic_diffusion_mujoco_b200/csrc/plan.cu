@@ -88,6 +88,19 @@ int encode_map(CUtensorMap* m, void* base, int rank, const uint64_t* dims, const
   return DM_OK;
 }
 
+typedef CUresult (*ReplaceAddressFn)(CUtensorMap*, void*);
+static ReplaceAddressFn get_replace_address() {
+  static ReplaceAddressFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapReplaceAddress", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<ReplaceAddressFn>(p);
+  }
+  return fn;
+}
+
 // ---- allocation helpers ----
 static int dev_alloc(dm_plan* P, void** p, size_t bytes, bool zero = true) {
   DM_CUDA(cudaMalloc(p, bytes));
@@ -736,6 +749,70 @@ static int add_attention(dm_plan* P, const WeightMap& W, const std::string& key,
   return DM_OK;
 }
 
+// Fused-loop workspace.  Every layer output has an activation of its own (dm_plan_read_layer and the per-layer launches use
+// those), 40 x 8.4 MB at the bench shape: far beyond L2, so every tile written is evicted to DRAM before its buffer comes
+// round again.  Inside the fused loop a buffer is dead after its last reader of the step, so the loop's copies of the
+// descriptors (P->loop_jobs, the device copy of the tensor maps) point activations whose lifetimes do not overlap at the SAME
+// memory: the step's working set becomes a handful of buffers that stay in L2.  Lifetimes are by layer index: a layer's
+// outputs never share with its own inputs, and a buffer is only handed on after the layer that last reads it (any reader
+// from global memory follows a completed store and a barrier, so a later store to the same bytes is ordered behind both).
+static int alias_loop_workspace(dm_plan* P, std::vector<ConvMaps>& maps) {
+  ReplaceAddressFn replace = get_replace_address();
+  if (!replace) return DM_OK;                     // old driver: keep one buffer per activation
+  const int n = (int)P->layers.size(), na = (int)P->acts.size();
+  std::vector<int> last_use(na, -1);
+  for (int i = 0; i < n; ++i) {
+    const Layer& ly = P->layers[i];
+    for (int s = 0; s < 2; ++s) if (ly.src_acts[s] >= 0) last_use[ly.src_acts[s]] = i;
+    if (ly.res_act >= 0) last_use[ly.res_act] = i;
+  }
+  std::vector<__half*> alias(na);
+  for (int a = 0; a < na; ++a) alias[a] = P->acts[a].p;
+  std::map<long long, std::vector<__half*>> free_bufs;   // by plane size
+  size_t distinct = 0, pooled = 0;
+  std::vector<__half*> seen;
+  for (int i = 0; i < n; ++i) {
+    const Layer& ly = P->layers[i];
+    const int defs[2] = {ly.out_act, ly.aux_act};
+    for (int d = 0; d < 2; ++d) {
+      const int a = defs[d];
+      if (a < 0 || a == P->xs_act) continue;
+      std::vector<__half*>& fb = free_bufs[P->acts[a].plane];
+      if (!fb.empty()) { alias[a] = fb.back(); fb.pop_back(); }
+      distinct += (size_t)P->acts[a].plane * 4;
+      if (std::find(seen.begin(), seen.end(), alias[a]) == seen.end()) { seen.push_back(alias[a]); pooled += (size_t)P->acts[a].plane * 4; }
+    }
+    for (int a = 0; a < na; ++a) {
+      if (a == P->xs_act) continue;
+      const bool def_here = a == ly.out_act || a == ly.aux_act;
+      if (last_use[a] == i || (def_here && last_use[a] < i)) free_bufs[P->acts[a].plane].push_back(alias[a]);
+    }
+  }
+  P->loop_workspace_bytes = pooled;
+  P->layer_workspace_bytes = distinct;
+  auto swap = [&](CUtensorMap* m, int a) -> int {
+    if (a < 0 || alias[a] == P->acts[a].p) return DM_OK;
+    const CUresult r = replace(m, alias[a]);
+    return r == CUDA_SUCCESS ? DM_OK : fail(DM_ERR_CUDA, "cuTensorMapReplaceAddress failed (%d)", (int)r);
+  };
+  for (int i = 0; i < n; ++i) {
+    const Layer& ly = P->layers[i];
+    ConvJob& j = P->loop_jobs[i];
+    int rc;
+    if (ly.kind == JOB_CONV) {
+      for (int s = 0; s < j.nsrc; ++s) if ((rc = swap(&maps[i].a_map[s], ly.src_acts[s]))) return rc;
+      if (j.st_cw != 0 && ly.out_act >= 0 && (rc = swap(&maps[i].o_map, ly.out_act))) return rc;
+      if (j.st_cw != 0 && ly.res_act >= 0 && (rc = swap(&maps[i].r_map, ly.res_act))) return rc;
+      if (j.aux && (rc = swap(&maps[i].p_map, ly.aux_act))) return rc;
+      if (ly.res_act >= 0) j.res = alias[ly.res_act];
+    } else if (ly.src_acts[0] >= 0) {
+      j.res = alias[ly.src_acts[0]];
+    }
+    if (ly.out_act >= 0) j.out = alias[ly.out_act];
+  }
+  return DM_OK;
+}
+
 static int build_unet(dm_plan* P, const WeightMap& W) {
   const int nlev = (int)P->mults.size();
   std::vector<int> dims;
@@ -932,10 +1009,13 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if (n > kMaxLoopJobs) return fail(DM_ERR_ARG, "U-Net has %d layer launches; the fused loop supports %d", n, kMaxLoopJobs);
     std::vector<ConvMaps> maps(n);
     P->loop_smem = 0;
+    P->loop_jobs.resize(n);
     for (int i = 0; i < n; ++i) {
       maps[i] = P->layers[i].maps;
+      P->loop_jobs[i] = P->layers[i].job;
       if (P->layers[i].smem > P->loop_smem) P->loop_smem = P->layers[i].smem;
     }
+    if ((rc = alias_loop_workspace(P, maps))) return rc;
     if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->maps_dev), n * sizeof(ConvMaps), false))) return rc;
     DM_CUDA(cudaMemcpy(P->maps_dev, maps.data(), n * sizeof(ConvMaps), cudaMemcpyHostToDevice));
   }
@@ -1269,7 +1349,7 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   P->steps_pending = true;
   static thread_local LoopParams lp;   // ~19 KB: keep it off the stack
   lp.n_jobs = (int)P->layers.size();
-  for (int i = 0; i < lp.n_jobs; ++i) lp.jobs[i] = P->layers[i].job;
+  for (int i = 0; i < lp.n_jobs; ++i) lp.jobs[i] = P->loop_jobs[i];   // (activation pointers of the shared loop workspace)
 #ifdef DM_DEV_DEBUG
   {   // debugging aid (compile with -DDM_DEV_DEBUG): the fused loop's job list
     for (int i = 0; i < lp.n_jobs; ++i) {

@@ -58,6 +58,8 @@ struct dm_plan {
   std::vector<void*> allocs;
   std::vector<dm::Act> acts;
   std::vector<dm::Layer> layers;
+  std::vector<dm::ConvJob> loop_jobs;   // the fused loop's copy of the descriptors: activations alias a small shared workspace
+  size_t loop_workspace_bytes = 0, layer_workspace_bytes = 0;   // activation bytes the fused loop / the per-layer path touch per step
   int xs_act = -1;
   bool lsplit = false;             // L-split (conv_job.h): two CTA pairs per 16-sample group, half of the positions each
   bool has_attention = false;      // attention=True: per-layer launches only (the fused loop kernel has no attention stage)
