@@ -42,6 +42,9 @@ struct ConvMaps {
   CUtensorMap r_map;      // 5-D load map of the residual activation, same box as o_map
   CUtensorMap x_map;      // 5-D weights of the fused auxiliary 1x1 conv (the block's residual_conv), layout and box as w_map
   CUtensorMap p_map;      // 5-D store map of the auxiliary output activation, same box as o_map
+  // weight multicast (ConvJob::mc): boxes of a QUARTER of the tile's N rows, one plane each
+  CUtensorMap wq_map;     // as w_map, box (Cc, Nc / 4, 1, 1, 1)
+  CUtensorMap xq_map;     // as x_map, box (Cc, Nc / 4, 1, 1, 1)
 };
 
 // Plain-data layer descriptor.  It is always read from kernel-parameter (constant-bank) space, so every field
@@ -131,6 +134,7 @@ struct ConvJob {
   const float* aux_bias;  // [CoutPad]
   // one-byte flags, kept together (80 descriptors share the 32 KB kernel-parameter block)
   unsigned char kind;               // JOB_CONV, or one of the attention stages
+  unsigned char mc;                 // fused loop only: clusters of four = TWO groups; the pairs share every weight tile by TMA multicast
   unsigned char ls;                 // 1: L-split job (see ls_in / ls_out above)
   unsigned char cg_pow2;            // cg is a power of two (lets the epilogue fold partial sums by shifts)
   unsigned char a_res;              // this layer's A operand is the previous layer's staged tile

@@ -67,6 +67,7 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full, res_full;
   uint64_t tile_ready;   // resident link (leader CTA's copy is the live one): both CTAs' staged tiles are complete
+  uint64_t mc_done;      // weight multicast: the MMAs of the current unit have completed in BOTH pairs of the cluster
   uint64_t xstat_full;   // L-split: the twin CTA (other half of L, same samples) has delivered its GroupNorm partial sums
   uint32_t tmem_slot;
   alignas(8) float xstat[2][128][2];    // L-split: the twin's (sum, sum of squares) per (sample, group), double-buffered by use
@@ -83,14 +84,17 @@ struct ConvShared {
 // though ring depths change from layer to layer inside the persistent kernel.
 struct RoleState {
   uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0, tile_count = 0, x_count = 0;
+  uint32_t mc_count = 0;
   int pre_w = 0;   // producer: weight loads of the current unit that were already issued during the previous epilogue
   int lhalf = 0;       // L-split: which half of the positions this CTA's pair works on (0 when the job is not split)
   int pair_base = 0;   // rank of the pair's leader inside the cluster (0, or 2 for the second pair of a cluster of four)
 };
 
-__device__ __forceinline__ void init_shared(ConvShared& sh) {
+// mc: weight stages are filled for, and released by, both pairs of the cluster (two MMA warps each)
+__device__ __forceinline__ void init_shared(ConvShared& sh, bool mc = false) {
   for (int i = 0; i < 2; ++i) { mbar_init(&sh.a_full[i], 1); mbar_init(&sh.a_empty[i], 2); }   // both MMA warps release
-  for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], 2); }
+  for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], mc ? 4 : 2); }
+  mbar_init(&sh.mc_done, 4);
   mbar_init(&sh.acc_full, 2);
   mbar_init(&sh.res_full, 1);
   mbar_init(&sh.tile_ready, 2);   // one arrival from each CTA of the pair (the peer's is remote)
@@ -103,11 +107,25 @@ __device__ __forceinline__ void init_shared(ConvShared& sh) {
 // its own shared memory.  The bytes of both CTAs are counted on the LEADER's full barriers (the leader's MMA warps are
 // the only waiters): the leader arms them with arrive.expect_tx for twice its own byte count, the peer only issues its
 // loads.  Stage reuse is gated per CTA by its own empty barriers, which the MMA commits signal in both CTAs.
-template <bool TR, bool LS>
-__device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensorMap* a_maps, const CUtensorMap* w_map,
+// MC (weight multicast, clusters of four = two pairs working on two groups): the same-ranked CTAs of the two pairs need
+// the same half of every weight tile, so each loads a QUARTER (two boxes, one per plane) and multicasts it to both.  A
+// stage is refilled when BOTH pairs have released it (w_empty counts four), and this warp leaves a unit only when both
+// pairs' MMAs have completed (mc_done): the next unit's fills land in the other pair's shared memory too.
+__device__ __forceinline__ void load_w_quarter(const ConvJob& jb, const CUtensorMap* wq, uint32_t stage, uint64_t* bar, int wn0,
+                                               int chunk, int tap, int rank, int pair) {
+  const int rows_q = jb.Nc >> 2;
+  const unsigned short mask = (unsigned short)((1u << rank) | (4u << rank));
+  const uint32_t dst = stage + (uint32_t)(pair * rows_q * jb.row_bytes);
+  tma_load_5d_pair_mc(dst, wq, bar, 0, wn0 + pair * rows_q, chunk, tap, 0, mask);
+  tma_load_5d_pair_mc(dst + (uint32_t)jb.w_plane_bytes, wq, bar, 0, wn0 + pair * rows_q, chunk, tap, 1, mask);
+}
+
+template <bool TR, bool LS, bool MC>
+__device__ __forceinline__ void producer_unit(const ConvJob& job, const ConvMaps* maps, const CUtensorMap* a_maps, const CUtensorMap* w_map,
                                               const CUtensorMap* x_map, int g, int b0, int n0, int rank, uint32_t a_smem,
                                               uint32_t w_smem, ConvShared& sh, RoleState& rs, unsigned long long* tr,
-                                              uint32_t smem_base, const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0) {
+                                              uint32_t smem_base, const ConvJob* nj, const CUtensorMap* n_w_map, int n_n0,
+                                              const CUtensorMap* n_wq_map) {
   const bool leader = elect_one_sync();
   const bool arm = leader && rank == 0;
   const int wn0 = n0 + rank * (job.Nc >> 1);          // this CTA's rows of the weight tile
@@ -132,7 +150,10 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
           } else {
             mbar_wait(&sh.w_empty[ws], ((rs.w_bits >> ws) & 1) ^ 1, 0x200 + ws);
             if (arm) mbar_arrive_expect_tx(&sh.w_full[ws], 2u * job.w_tx_bytes);
-            if (leader) {
+            if (MC && leader) {
+              load_w_quarter(job, t < job.ntaps ? &maps->wq_map : &maps->xq_map, w_smem + ws * job.w_stage_bytes, &sh.w_full[ws],
+                             wn0, chunk0 + ch, t < job.ntaps ? job.taps[t].wtap : 0, rank, rs.pair_base >> 1);
+            } else if (leader) {
               tma_load_5d_pair(w_smem + ws * job.w_stage_bytes, t < job.ntaps ? w_map : x_map, &sh.w_full[ws], 0, wn0,
                                chunk0 + ch, t < job.ntaps ? job.taps[t].wtap : 0, 0);
 #if defined(DM_TRACE_WLOADS) && !defined(DM_TRACE_MMA)
@@ -157,6 +178,10 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
     }
   }
   if (leader) trace_mark<TR>(tr, 4);
+  if (MC) {   // both pairs' MMAs of this unit are complete: every operand stage of the unit is dead in all four CTAs
+    mbar_wait(&sh.mc_done, rs.mc_count & 1, 0x730);
+    rs.mc_count++;
+  }
   // A resident link has no block barrier behind it (the roles run ahead, see sample_loop_kernel): this warp may only
   // touch the next layer's ring once this layer's MMAs have completed, whether or not it prefetches.
   if (job.next_res && !(nj != nullptr && job.pre_next > 0)) mbar_wait(&sh.acc_full, rs.acc_count & 1, 0x710);
@@ -169,7 +194,10 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
     for (int i = 0; i < job.pre_next; ++i) {
       mbar_wait(&sh.w_empty[i], ((rs.w_bits >> i) & 1) ^ 1, 0x780 + i);
       if (arm) mbar_arrive_expect_tx(&sh.w_full[i], 2u * nj->w_tx_bytes);
-      if (leader)
+      if (MC && leader)
+        load_w_quarter(*nj, n_wq_map, nw_smem + i * nj->w_stage_bytes, &sh.w_full[i], n_n0 + rank * (nj->Nc >> 1), 0,
+                       nj->taps[i].wtap, rank, rs.pair_base >> 1);
+      else if (leader)
         tma_load_5d_pair(nw_smem + i * nj->w_stage_bytes, n_w_map, &sh.w_full[i], 0, n_n0 + rank * (nj->Nc >> 1), 0,
                          nj->taps[i].wtap, 0);
       rs.w_bits ^= 1u << i;
@@ -198,7 +226,7 @@ __device__ __forceinline__ void producer_unit(const ConvJob& job, const CUtensor
 // take one commit from each warp as well.
 // RD = false: the kernel variant for plans whose every layer fits TMEM at once (all horizons <= 256): the round logic
 // compiles away.  RD = true: layers may pass through TMEM in rounds (job.n_rounds > 1).
-template <bool TR, bool RD, bool LS>
+template <bool TR, bool RD, bool LS, bool MC>
 __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base, uint32_t a_smem, uint32_t w_smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs, unsigned long long* tr,
                                          const int which) {
@@ -217,9 +245,12 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
   const uint32_t a_plane16 = (uint32_t)(job.a_res ? job.a_res_plane : job.a_plane_bytes) >> 4;
   const uint32_t w_plane16 = job.w_plane_bytes >> 4;
   const uint32_t mt_step16 = (uint32_t)(job.l_stride * pos_per_mt * S * job.row_bytes) >> 4;
-  const int pair_base = LS ? rs.pair_base : 0;   // (a compile-time 0 in the common kernels)
+  const int pair_base = (LS || MC) ? rs.pair_base : 0;   // (a compile-time 0 in the common kernels)
   const uint32_t peer_w_empty = mapa_u32(smem_u32(&sh.w_empty[0]), (uint32_t)pair_base + 1);   // the peer CTA's copy of the ring's empty barriers
   const unsigned short cmask = (unsigned short)(3u << pair_base);     // the pair's ranks, for the multicast commits
+  const unsigned short wmask = MC ? (unsigned short)0xF : cmask;      // weight stages are shared with the other pair
+  const uint32_t twin_w_empty0 = MC ? mapa_u32(smem_u32(&sh.w_empty[0]), (uint32_t)(pair_base ^ 2)) : 0u;
+  const uint32_t twin_w_empty1 = MC ? mapa_u32(smem_u32(&sh.w_empty[0]), (uint32_t)(pair_base ^ 2) + 1) : 0u;
   int as = 0, ws = 0, wi = 0;
   if (leader) trace_mark<TR>(tr, 21);
   int lt_in = 0;            // l-tile index inside the current TMEM round
@@ -274,6 +305,10 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
             if (leader) {
               mbar_arrive(&sh.w_empty[ws]);
               mbar_arrive_remote(peer_w_empty + 8u * (uint32_t)ws);
+              if (MC) {
+                mbar_arrive_remote(twin_w_empty0 + 8u * (uint32_t)ws);
+                mbar_arrive_remote(twin_w_empty1 + 8u * (uint32_t)ws);
+              }
             }
           } else {
             tc_fence_after();
@@ -314,8 +349,8 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
 #endif
             __syncwarp();
             if (leader) {
-              umma_commit_pair(&sh.w_empty[ws], cmask);
-              if (mode == 2) umma_commit_pair(&sh.w_empty[ws], cmask);   // the owner's release counts for both warps
+              umma_commit_pair(&sh.w_empty[ws], wmask);
+              if (mode == 2) umma_commit_pair(&sh.w_empty[ws], wmask);   // the owner's release counts for both warps
             }
           }
           ++wi;
@@ -328,7 +363,10 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
       }
     }
     if (!RD) {
-      if (lt + 1 == job.n_ltiles && leader) umma_commit_pair(&sh.acc_full, cmask);
+      if (lt + 1 == job.n_ltiles && leader) {
+        umma_commit_pair(&sh.acc_full, cmask);
+        if (MC) umma_commit_pair(&sh.mc_done, (unsigned short)0xF);   // (one from each issuer warp of each pair)
+      }
     } else if (++lt_in == job.lt_round || lt + 1 == job.n_ltiles) {   // end of a TMEM round: hand the accumulators to the epilogues
       lt_in = 0;
       if (leader) umma_commit_pair(&sh.acc_full, cmask);
@@ -734,7 +772,7 @@ __device__ __forceinline__ void epilogue_rounds(const ConvJob& job, int warp, in
 // Warp w reads TMEM lanes 32*(w%4).. (hardware rule) and takes the (tile, 32-column chunk) units u with
 // u % 4 == w / 4.  Thread <-> GEMM row (l, b); b = row % S is constant per thread across tiles.
 // RD: the "big tile" kernel variants (see mma_unit) also carry the wave-staged pass 2.
-template <bool TR, bool RD, bool LS>
+template <bool TR, bool RD, bool LS, bool MC>
 __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps* maps, int warp, int g, int b0, int n0,
                                               int rank, const float* tbias, int tbias_stride, uint32_t stg, ConvShared& sh,
                                               uint32_t tmem_base, RoleState& rs, unsigned long long* tr) {
@@ -1040,7 +1078,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     named_bar_sync(1, kEpiThreads);
     if (job.next_res && threadIdx.x == 0) {   // releases the leader's MMA warps waiting in the next layer (one arrival per CTA)
       if (rank == 0) mbar_arrive(&sh.tile_ready);
-      else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)(LS ? rs.pair_base : 0)));
+      else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)((LS || MC) ? rs.pair_base : 0)));
     }
     trace_mark<TR>(tr, 15);
     if (tid == 0 && !job.no_store) {
@@ -1061,31 +1099,33 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
 
 // One work unit = (sample sub-group, N slice) of one layer, executed by all roles of the CTA.
 // rank = this CTA's rank in its pair: it owns samples b0 = 8 * rank .. of group g.
-template <bool TR, bool RD, bool LS>
+template <bool TR, bool RD, bool LS, bool MC = false>
 __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* maps, int warp, int rank,
                                          int g, int n0, const float* tbias, int tbias_stride, uint32_t smem,
                                          ConvShared& sh, uint32_t tmem_base, RoleState& rs,
                                          unsigned long long* tr = nullptr, const ConvJob* nj = nullptr,
-                                         const CUtensorMap* n_w_map = nullptr, int n_n0 = 0) {
+                                         const CUtensorMap* n_w_map = nullptr, int n_n0 = 0,
+                                         const CUtensorMap* n_wq_map = nullptr) {
   const uint32_t a_smem = smem;
   const uint32_t w_smem = smem + (job.a_res ? job.w_off_res : job.n_a_stages * job.a_stage_bytes);
   const int b0 = rank * 8;
   if (warp == kProducerWarp) {
-    producer_unit<TR, LS>(job, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, rank, a_smem, w_smem, sh, rs, tr, smem, nj, n_w_map, n_n0);
+    producer_unit<TR, LS, MC>(job, maps, &maps->a_map[0], &maps->w_map, &maps->x_map, g, b0, n0, rank, a_smem, w_smem, sh, rs, tr, smem, nj,
+                              n_w_map, n_n0, n_wq_map);
   } else if (warp == kMmaWarp || warp == kMmaWarpB) {
-    if (rank == 0) mma_unit<TR, RD, LS>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
+    if (rank == 0) mma_unit<TR, RD, LS, MC>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
   } else if (RD && job.n_rounds > 1) {
     epilogue_rounds<TR>(job, warp, g, b0, n0, rank, tbias, tbias_stride, sh, tmem_base, rs.acc_count);
     rs.acc_count += job.n_rounds;
   } else {
-    epilogue_unit<TR, RD, LS>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
+    epilogue_unit<TR, RD, LS, MC>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
   }
 }
 
 // Pair set-up / tear-down shared by both kernels: barriers of both CTAs exist before any remote arrival or pair TMA can
 // target them, and nobody frees TMEM or leaves while the leader's MMAs may still read the peer's shared memory.
-__device__ __forceinline__ uint32_t pair_begin(ConvShared& sh, int warp, uint32_t tmem_cols) {
-  if (threadIdx.x == 0) init_shared(sh);
+__device__ __forceinline__ uint32_t pair_begin(ConvShared& sh, int warp, uint32_t tmem_cols, bool mc = false) {
+  if (threadIdx.x == 0) init_shared(sh, mc);
   __syncthreads();
   if (warp == kMmaWarp) tmem_alloc_pair(&sh.tmem_slot, tmem_cols);
   tc_fence_before();
@@ -1163,17 +1203,20 @@ __device__ __noinline__ void attn_stage_call(const ConvJob& job, int g, int b0, 
 
 // AT: the layer list carries attention stages (attn_stages.cuh); a variant of its own so that the common kernels keep their
 // register allocation.
-template <bool TR, bool RD, bool LS, bool AT>
-__global__ void __cluster_dims__(LS ? 4 : 2, 1, 1) __launch_bounds__(kConvThreads, 1)
+// MC: clusters of four = two pairs working on two GROUPS (2c, 2c + 1) that share every weight tile by TMA multicast (see
+// producer_unit); layers hand over through the cluster barrier wherever they are not resident links.
+template <bool TR, bool RD, bool LS, bool AT, bool MC = false>
+__global__ void __cluster_dims__((LS || MC) ? 4 : 2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
+  static_assert(!(MC && (RD || LS || AT)), "weight multicast exists for the common kernel shape only");
   const uint32_t smem = aligned_dyn_smem();
   __shared__ ConvShared sh;
   __shared__ StepParams sstep;
   const int warp = warp_idx_sync();
   const int crank = (int)cluster_ctarank();
   const int rank = crank & 1;
-  const int g = (int)cluster_id_x();
-  const uint32_t tmem_base = pair_begin(sh, warp, 512);
+  const int g = MC ? 2 * (int)cluster_id_x() + (crank >> 1) : (int)cluster_id_x();
+  const uint32_t tmem_base = pair_begin(sh, warp, 512, MC);
   RoleState rs;
   rs.lhalf = LS ? crank >> 1 : 0;
   rs.pair_base = crank & ~1;
@@ -1181,7 +1224,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   // K4 works on whole samples: 8 per CTA, or 4 per CTA of an L-split cluster (every CTA of the group takes a share)
   const long long ht4 = ((long long)lp.H * lp.T) >> 2;           // float4 per sample
   const int k4_n = LS ? 4 : 8;
-  const int s_lo = g * kGroupSamples + crank * k4_n;
+  const int s_lo = g * kGroupSamples + (MC ? rank : crank) * k4_n;
   const int s_hi = min(lp.B, s_lo + k4_n);
 
   for (int k = 0; k <= lp.n_steps; ++k) {
@@ -1189,7 +1232,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
       const int t_index = lp.steps[k].t_index;
       for (int ji = 0; ji < lp.n_jobs; ++ji) {
         const ConvJob& job = lp.jobs[ji];   // kernel-parameter (constant) space: warp-uniform
-        unsigned long long* tr = (TR && lp.trace && g == lp.trace_cluster && crank == 0 && k == lp.trace_step)
+        unsigned long long* tr = (TR && lp.trace && g == lp.trace_cluster && (MC ? rank : crank) == 0 && k == lp.trace_step)
                                      ? lp.trace + (size_t)ji * kTraceSlots : nullptr;
         if (TR && threadIdx.x == 0 && tr) { trace_mark<TR>(tr, 0); tr[1] = (unsigned long long)clock64(); }   // slot 1: SM clock (effective MHz)
         if (TR && threadIdx.x == kMmaWarp * 32 && tr) trace_mark<TR>(tr, 22);
@@ -1223,11 +1266,11 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
         for (int sl = 0; sl < slices; ++sl) {      // N slices of the layer, one after the other, by the whole pair
           const bool last_unit = sl + 1 >= slices;
           if (TR && threadIdx.x == kMmaWarp * 32 && tr && sl == 0) trace_mark<TR>(tr, 23);
-          run_unit<TR, RD, LS>(job, maps, warp, rank, g, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == 0 ? tr : nullptr,
-                       last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, 0);
+          run_unit<TR, RD, LS, MC>(job, maps, warp, rank, g, sl * job.Nc, tb, 0, smem, sh, tmem_base, rs, sl == 0 ? tr : nullptr,
+                                   last_unit && has_next ? &njob : nullptr, &lp.maps[nji].w_map, 0, &lp.maps[nji].wq_map);
           if (sl + 1 < slices) {   // TMEM / staging smem are reused by the next unit (the peer's side of the pair is
             tc_fence_before();     // protected through the full barriers: its loads for the next unit follow its barrier)
-            if (LS) cluster_sync_all();   // (L-split: also keeps the twin's next statistics exchange one use behind at most)
+            if (LS || MC) cluster_sync_all();   // (L-split: also keeps the twin's next statistics exchange one use behind at most)
             else __syncthreads();
             tc_fence_after();
           }
@@ -1282,7 +1325,9 @@ static cudaError_t ensure_smem_attr() {
                            (const void*)sample_loop_kernel<false, false, true, false>, (const void*)sample_loop_kernel<false, true, true, false>,
                            (const void*)sample_loop_kernel<true, false, true, false>, (const void*)sample_loop_kernel<true, true, true, false>,
                            (const void*)sample_loop_kernel<false, false, false, true>, (const void*)sample_loop_kernel<true, false, false, true>,
-                           (const void*)sample_loop_kernel<false, true, false, true>, (const void*)sample_loop_kernel<true, true, false, true>};
+                           (const void*)sample_loop_kernel<false, true, false, true>, (const void*)sample_loop_kernel<true, true, false, true>,
+                           (const void*)sample_loop_kernel<false, false, false, false, true>,
+                           (const void*)sample_loop_kernel<true, false, false, false, true>};
   for (const void* k : kernels) {
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) break;
@@ -1323,6 +1368,12 @@ cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStre
                     else sample_loop_kernel<true, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp); }
     else { if (rounds) sample_loop_kernel<false, true, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp);
            else sample_loop_kernel<false, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp); }
+    return cudaGetLastError();
+  }
+  if (lp.n_jobs > 0 && lp.jobs[0].mc) {   // (the plan sets it on every job or on none; it implies !rounds, !ls, !at, G even)
+    if (rounds || ls || (lp.G & 1)) return cudaErrorInvalidValue;
+    if (lp.trace) sample_loop_kernel<true, false, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp);
+    else sample_loop_kernel<false, false, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp);
     return cudaGetLastError();
   }
 #define DM_LOOP(TR_, RD_, LS_) sample_loop_kernel<TR_, RD_, LS_, false><<<grid, kConvThreads, smem_bytes, stream>>>(lp)

@@ -376,6 +376,11 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
                              (uint64_t)wplane * 2};
     const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)(Nc / 2), 1, 1, 2};   // per CTA: half of the tile's N rows
     if ((rc = encode_map(&ly.maps.w_map, wdev, 5, dims, str, box, j.swz))) return rc;
+    if (Nc % 32 == 0) {   // weight multicast: a quarter of the rows (whole swizzle atoms), one plane per box
+      const uint32_t qbox[5] = {(uint32_t)j.Cc, (uint32_t)(Nc / 4), 1, 1, 1};
+      if ((rc = encode_map(&ly.maps.wq_map, wdev, 5, dims, str, qbox, j.swz))) return rc;
+      ly.mc_ok = true;
+    }
   }
   for (int s = 0; s < sp.nsrc; ++s) {
     const Act& a = P->acts[sp.src[s]];
@@ -531,6 +536,10 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
                                (uint64_t)xplane * 2};
       const uint32_t box[5] = {(uint32_t)j.Cc, (uint32_t)(Nc / 2), 1, 1, 2};
       if ((rc = encode_map(&ly.maps.x_map, xdev, 5, dims, str, box, j.swz))) return rc;
+      if (Nc % 32 == 0) {
+        const uint32_t qbox[5] = {(uint32_t)j.Cc, (uint32_t)(Nc / 4), 1, 1, 1};
+        if ((rc = encode_map(&ly.maps.xq_map, xdev, 5, dims, str, qbox, j.swz))) return rc;
+      }
     }
     std::vector<float> hxb(cout_pad, 0.f);
     for (int c = 0; c < sp.Cout; ++c) hxb[c] = xb[c];
@@ -1016,6 +1025,20 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
       if (P->layers[i].smem > P->loop_smem) P->loop_smem = P->layers[i].smem;
     }
     if ((rc = alias_loop_workspace(P, maps))) return rc;
+    // Weight multicast (conv_kernel.cu, producer_unit): clusters of four CTAs = two groups whose pairs share every weight
+    // tile.  Common kernel shape only, an even number of groups, and at least one full cluster's worth of them.
+#ifndef DM_NO_MCAST
+    P->mcast = !P->lsplit && !P->has_attention && P->G % 2 == 0;
+    for (int i = 0; i < n; ++i) {
+      const Layer& ly = P->layers[i];
+      if (ly.kind != JOB_CONV || !ly.mc_ok || ly.job.n_rounds > 1 || ly.job.st_wave) P->mcast = false;
+    }
+#endif
+    if (P->mcast)
+      for (int i = 0; i < n; ++i) {
+        P->loop_jobs[i].mc = 1;
+        P->loop_jobs[i].sync_local = 0;   // the other pair writes into this CTA's weight stages: cluster barrier
+      }
     if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->maps_dev), n * sizeof(ConvMaps), false))) return rc;
     DM_CUDA(cudaMemcpy(P->maps_dev, maps.data(), n * sizeof(ConvMaps), cudaMemcpyHostToDevice));
   }
@@ -1365,7 +1388,7 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   lp.maps = P->maps_dev;
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
-  lp.k4_local = !P->lsplit && P->layers.front().job.S == 8 && P->layers.back().job.S == 8;
+  lp.k4_local = !P->lsplit && !P->mcast && P->layers.front().job.S == 8 && P->layers.back().job.S == 8;
   lp.trace = P->trace_dev; lp.trace_cluster = P->trace_cluster; lp.trace_step = P->trace_step;
   DM_CUDA(launch_sample_loop(lp, P->loop_smem, s));
   P->last_launches = 1;

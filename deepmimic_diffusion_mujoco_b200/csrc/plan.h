@@ -22,6 +22,7 @@ struct Act {
 
 struct Layer {
   int kind = 0;          // == job.kind: JOB_CONV (job, maps), or an attention stage (job only; attn_stages.cuh)
+  bool mc_ok = false;    // quarter-tile weight maps exist (weight multicast)
   bool hidden = false;   // intermediate of an attention block: dm_plan_layer_info reports no output for it
   ConvJob job;
   ConvMaps maps;
@@ -61,6 +62,7 @@ struct dm_plan {
   std::vector<dm::ConvJob> loop_jobs;   // the fused loop's copy of the descriptors: activations alias a small shared workspace
   size_t loop_workspace_bytes = 0, layer_workspace_bytes = 0;   // activation bytes the fused loop / the per-layer path touch per step
   int xs_act = -1;
+  bool mcast = false;              // fused loop: clusters of four = two groups sharing weight tiles by TMA multicast
   bool lsplit = false;             // L-split (conv_job.h): two CTA pairs per 16-sample group, half of the positions each
   bool has_attention = false;      // attention=True: per-layer launches only (the fused loop kernel has no attention stage)
   float* model_out = nullptr;      // fp32 [B,H,T] scratch for the sampling loop

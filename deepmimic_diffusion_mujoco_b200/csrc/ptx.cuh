@@ -140,6 +140,18 @@ __device__ __forceinline__ void tma_load_5d_pair(uint32_t dst, const CUtensorMap
       : "memory");
 }
 
+// The same with multicast: the box lands at the same offset in the shared memory of every CTA in `mask` (cluster ranks), and
+// each destination's bytes are counted on the barrier of ITS pair's leader.
+__device__ __forceinline__ void tma_load_5d_pair_mc(uint32_t dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
+                                                    int c2, int c3, int c4, unsigned short mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1, {%4, %5, %6, %7, %8}], [%2], %3;" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "h"(mask), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
+      "r"(c4)
+      : "memory");
+}
+
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
