@@ -370,6 +370,7 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
     } else if (++lt_in == job.lt_round || lt + 1 == job.n_ltiles) {   // end of a TMEM round: hand the accumulators to the epilogues
       lt_in = 0;
       if (leader) umma_commit_pair(&sh.acc_full, cmask);
+      if (MC && leader && lt + 1 == job.n_ltiles) umma_commit_pair(&sh.mc_done, (unsigned short)0xF);
       if (lt + 1 < job.n_ltiles) {
         // the next round overwrites these columns in BOTH CTAs: wait until both epilogues have drained them
         mbar_wait_cluster(&sh.tile_ready, rs.tile_count & 1, 0x320);
@@ -605,7 +606,7 @@ __device__ __forceinline__ void staged_write(const ConvJob& job, uint32_t stg_da
 template <bool TR>
 __device__ __forceinline__ void epilogue_rounds(const ConvJob& job, int warp, int g, int b0, int n0, int rank,
                                              const float* tbias, int tbias_stride, ConvShared& sh, uint32_t tmem_base,
-                                             uint32_t acc_count0) {
+                                             uint32_t acc_count0, int pair_base = 0) {
   constexpr int S = 8;
   const int lane = threadIdx.x & 31, tid = threadIdx.x;
   const int Nc = job.Nc, mrows = job.mrows, ncols = job.ncols;
@@ -743,7 +744,7 @@ __device__ __forceinline__ void epilogue_rounds(const ConvJob& job, int warp, in
       named_bar_sync(1, kEpiThreads);
       if (tid == 0) {
         if (rank == 0) mbar_arrive(&sh.tile_ready);
-        else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), 0));
+        else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)pair_base));
       }
     }
   }
@@ -1115,7 +1116,7 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
   } else if (warp == kMmaWarp || warp == kMmaWarpB) {
     if (rank == 0) mma_unit<TR, RD, LS, MC>(job, smem, a_smem, w_smem, sh, tmem_base, rs, tr, warp == kMmaWarp ? 0 : 1);   // the leader issues for the pair
   } else if (RD && job.n_rounds > 1) {
-    epilogue_rounds<TR>(job, warp, g, b0, n0, rank, tbias, tbias_stride, sh, tmem_base, rs.acc_count);
+    epilogue_rounds<TR>(job, warp, g, b0, n0, rank, tbias, tbias_stride, sh, tmem_base, rs.acc_count, MC ? rs.pair_base : 0);
     rs.acc_count += job.n_rounds;
   } else {
     epilogue_unit<TR, RD, LS, MC>(job, maps, warp, g, b0, n0, rank, tbias, tbias_stride, smem, sh, tmem_base, rs, tr);
@@ -1208,7 +1209,7 @@ __device__ __noinline__ void attn_stage_call(const ConvJob& job, int g, int b0, 
 template <bool TR, bool RD, bool LS, bool AT, bool MC = false>
 __global__ void __cluster_dims__((LS || MC) ? 4 : 2, 1, 1) __launch_bounds__(kConvThreads, 1)
 sample_loop_kernel(const __grid_constant__ LoopParams lp) {
-  static_assert(!(MC && (RD || LS || AT)), "weight multicast exists for the common kernel shape only");
+  static_assert(!(MC && (AT || LS)), "weight multicast exists for the unsplit kernels without attention stages only");
   const uint32_t smem = aligned_dyn_smem();
   __shared__ ConvShared sh;
   __shared__ StepParams sstep;
@@ -1327,7 +1328,9 @@ static cudaError_t ensure_smem_attr() {
                            (const void*)sample_loop_kernel<false, false, false, true>, (const void*)sample_loop_kernel<true, false, false, true>,
                            (const void*)sample_loop_kernel<false, true, false, true>, (const void*)sample_loop_kernel<true, true, false, true>,
                            (const void*)sample_loop_kernel<false, false, false, false, true>,
-                           (const void*)sample_loop_kernel<true, false, false, false, true>};
+                           (const void*)sample_loop_kernel<true, false, false, false, true>,
+                           (const void*)sample_loop_kernel<false, true, false, false, true>,
+                           (const void*)sample_loop_kernel<true, true, false, false, true>};
   for (const void* k : kernels) {
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) break;
@@ -1370,10 +1373,12 @@ cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStre
            else sample_loop_kernel<false, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp); }
     return cudaGetLastError();
   }
-  if (lp.n_jobs > 0 && lp.jobs[0].mc) {   // (the plan sets it on every job or on none; it implies !rounds, !ls, !at, G even)
-    if (rounds || ls || (lp.G & 1)) return cudaErrorInvalidValue;
-    if (lp.trace) sample_loop_kernel<true, false, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp);
-    else sample_loop_kernel<false, false, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp);
+  if (lp.n_jobs > 0 && lp.jobs[0].mc) {   // (the plan sets it on every conv job or on none; it implies !ls, !at, G even)
+    if (ls || (lp.G & 1)) return cudaErrorInvalidValue;
+#define DM_LOOP_MC(TR_, RD_) sample_loop_kernel<TR_, RD_, false, false, true><<<grid, kConvThreads, smem_bytes, stream>>>(lp)
+    if (lp.trace) { if (rounds) DM_LOOP_MC(true, true); else DM_LOOP_MC(true, false); }
+    else { if (rounds) DM_LOOP_MC(false, true); else DM_LOOP_MC(false, false); }
+#undef DM_LOOP_MC
     return cudaGetLastError();
   }
 #define DM_LOOP(TR_, RD_, LS_) sample_loop_kernel<TR_, RD_, LS_, false><<<grid, kConvThreads, smem_bytes, stream>>>(lp)

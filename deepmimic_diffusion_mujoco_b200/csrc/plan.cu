@@ -1028,15 +1028,18 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     // Weight multicast (conv_kernel.cu, producer_unit): clusters of four CTAs = two groups whose pairs share every weight
     // tile.  Common kernel shape only, an even number of groups, and at least one full cluster's worth of them.
 #ifndef DM_NO_MCAST
-    P->mcast = !P->lsplit && !P->has_attention && P->G % 2 == 0;
+    // Measured (A/B, ms per pass): B = 1024, H = 64: 43.2 -> 40.0; B = 2048, H = 128: 158.2 -> 153.0.  The multicast form costs
+    // four small TMA operations per tile instead of two, and at long horizons the first levels re-stream their 2 KB tiles per
+    // l-tile: B = 256, H = 480 (L-split) 172.9 -> 187.7, and the L-split layouts at H = 128 / 256 gain under 1 %.
+    P->mcast = !P->has_attention && !P->lsplit && P->G % 2 == 0 && P->H <= 128;
     for (int i = 0; i < n; ++i) {
       const Layer& ly = P->layers[i];
-      if (ly.kind != JOB_CONV || !ly.mc_ok || ly.job.n_rounds > 1 || ly.job.st_wave) P->mcast = false;
+      if (ly.kind != JOB_CONV || !ly.mc_ok) P->mcast = false;
     }
 #endif
     if (P->mcast)
       for (int i = 0; i < n; ++i) {
-        P->loop_jobs[i].mc = 1;
+        P->loop_jobs[i].mc = 1;           // (every job or none: the kernel variant is chosen by the first job's flag)
         P->loop_jobs[i].sync_local = 0;   // the other pair writes into this CTA's weight stages: cluster barrier
       }
     if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->maps_dev), n * sizeof(ConvMaps), false))) return rc;
