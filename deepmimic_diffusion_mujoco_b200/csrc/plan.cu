@@ -17,6 +17,7 @@ namespace dm {
 cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes,
                             cudaStream_t stream);
 cudaError_t read_device_error(unsigned int* code);
+cudaError_t max_resident_clusters_of_four(size_t smem_bytes, int* n);
 
 static thread_local char g_err[512] = "";
 int fail(int code, const char* fmt, ...) {
@@ -1037,6 +1038,16 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
       if (ly.kind != JOB_CONV || !ly.mc_ok) P->mcast = false;
     }
 #endif
+    if (P->mcast || P->lsplit) {
+      // both layouts launch clusters of four and assume ONE wave: check what this device can hold (GPC boundaries, disabled SMs)
+      int fit = 0;
+      const int need = P->lsplit ? P->G : P->G / 2;
+      if (max_resident_clusters_of_four(P->loop_smem, &fit) != cudaSuccess) { cudaGetLastError(); fit = 0; }
+      if (fit < need) {
+        if (P->lsplit) return fail(DM_ERR_STATE, "the device holds %d clusters of four, the split plan needs %d", fit, need);
+        P->mcast = false;
+      }
+    }
     if (P->mcast)
       for (int i = 0; i < n; ++i) {
         P->loop_jobs[i].mc = 1;           // (every job or none: the kernel variant is chosen by the first job's flag)

@@ -307,13 +307,14 @@ def test_full_batch_rows_match_oracle(dm):
     assert torch.equal(chain[:, -1][m], ref[:, -1][m])
 
 
-@pytest.mark.parametrize("B,H,ctas,rows", [(592, 128, 4, [0, 3, 4, 9, 14, 300, 591]), (160, 256, 4, [1, 6, 11, 12, 159]),
+@pytest.mark.parametrize("B,H,ctas,rows", [(512, 128, 4, [0, 3, 4, 9, 14, 300, 511]), (160, 256, 4, [1, 6, 11, 12, 159]),
                                              (608, 128, 2, [0, 9, 300, 607]), (608, 256, 2, [0, 15, 607]),
                                              (20, 160, 4, [0, 7, 13, 19]), (18, 480, 4, [2, 8, 17]), (608, 480, 2, [5, 607])])
 def test_split_and_unsplit_layouts_at_long_horizons(dm, B, H, ctas, rows):
     """Small batches at H >= 128 run with FOUR CTAs per 16-sample group (two pairs, half of the positions each, GroupNorm
-    sums exchanged between them); from 4 * groups > SM count on the plan keeps one pair per group.  Both layouts, at the
-    largest split batch and the smallest unsplit one: rows from every CTA's share of the step kernel (samples 4r .. 4r+3
+    sums exchanged between them); when the clusters of four would not all be resident at once (the device reports how many
+    it holds: 33 on a 148-SM B200) the plan keeps one pair per group.  Both layouts, at a large split batch and the smallest
+    batch that is unsplit on every device: rows from every CTA's share of the step kernel (samples 4r .. 4r+3
     of a split group) against the oracle run on just those rows, fused and per-layer launches.  H = 160 and 480 (the training
     and projection horizons of archive/3_5_long_projection.ipynb) split into halves that are NOT whole MMA tiles (padded last
     tile, direct stores); unsplit, H = 480 goes through TMEM in rounds."""
