@@ -1393,21 +1393,22 @@ cudaError_t launch_sample_loop(const LoopParams& lp, size_t smem_bytes, cudaStre
   return cudaGetLastError();
 }
 
-// Clusters of four CTAs of the loop kernel the device can hold at once (GPC boundaries and disabled SMs decide, not just
+// Clusters of two / four CTAs of the loop kernel the device can hold at once (GPC boundaries and disabled SMs decide, not just
 // the SM count): the L-split and multicast layouts are only worth it when every cluster of the plan is resident in ONE wave.
-cudaError_t max_resident_clusters_of_four(size_t smem_bytes, int* n) {
+cudaError_t max_resident_clusters(int cluster_size, size_t smem_bytes, int* n) {
   cudaError_t e = ensure_smem_attr();
   if (e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(4 * 148);
+  cfg.gridDim = dim3(cluster_size * 148);
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem_bytes;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 4; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[0].val.clusterDim.x = cluster_size; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return cudaOccupancyMaxActiveClusters(n, (const void*)sample_loop_kernel<false, false, false, false, true>, &cfg);
+  if (cluster_size == 4) return cudaOccupancyMaxActiveClusters(n, (const void*)sample_loop_kernel<false, false, false, false, true>, &cfg);
+  return cudaOccupancyMaxActiveClusters(n, (const void*)sample_loop_kernel<false, false, false, false, false>, &cfg);
 }
 
 cudaError_t read_device_error(unsigned int* code) {

@@ -17,7 +17,7 @@ namespace dm {
 cudaError_t launch_conv_job(const ConvMaps& maps, const ConvJob& job, int n_groups, int n_slices, size_t smem_bytes,
                             cudaStream_t stream);
 cudaError_t read_device_error(unsigned int* code);
-cudaError_t max_resident_clusters_of_four(size_t smem_bytes, int* n);
+cudaError_t max_resident_clusters(int cluster_size, size_t smem_bytes, int* n);
 
 static thread_local char g_err[512] = "";
 int fail(int code, const char* fmt, ...) {
@@ -1039,14 +1039,15 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     }
 #endif
     if (P->mcast || P->lsplit) {
-      // both layouts launch clusters of four and assume ONE wave: check what this device can hold (GPC boundaries, disabled SMs)
-      int fit = 0;
-      const int need = P->lsplit ? P->G : P->G / 2;
-      if (max_resident_clusters_of_four(P->loop_smem, &fit) != cudaSuccess) { cudaGetLastError(); fit = 0; }
-      if (fit < need) {
-        if (P->lsplit) return fail(DM_ERR_STATE, "the device holds %d clusters of four, the split plan needs %d", fit, need);
-        P->mcast = false;
-      }
+      // Both layouts launch clusters of four; how many of them the device holds at once is decided by GPC boundaries and
+      // disabled SMs (33 on a 148-SM B200, against 74 pairs).  The split must fit in ONE wave (it exists to fill idle SMs);
+      // multicast must not need more waves than the independent pairs would.
+      int fit4 = 0, fit2 = 0;
+      if (max_resident_clusters(4, P->loop_smem, &fit4) != cudaSuccess || fit4 < 1) { cudaGetLastError(); fit4 = 0; }
+      if (max_resident_clusters(2, P->loop_smem, &fit2) != cudaSuccess || fit2 < 1) { cudaGetLastError(); fit2 = 1; }
+      if (P->lsplit && fit4 < P->G)
+        return fail(DM_ERR_STATE, "the device holds %d clusters of four, the split plan needs %d", fit4, P->G);
+      if (P->mcast && (fit4 == 0 || (P->G / 2 + fit4 - 1) / fit4 > (P->G + fit2 - 1) / fit2)) P->mcast = false;
     }
     if (P->mcast)
       for (int i = 0; i < n; ++i) {
