@@ -568,10 +568,13 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
 #ifndef DM_MODE2
 #define DM_MODE2 2
 #endif
+#ifndef DM_MODE2_CYCLES
+#define DM_MODE2_CYCLES 600
+#endif
   if (j.acc2 && j.ntaps >= 2) {
     // pipe time of one tap's MMAs (cycles, MAC floor of the pair MMA) against the issuing warp's per-tap bookkeeping
     const int mma_cycles = j.Mt * j.ksteps * 3 * ((j.mrows * Nc) / 256);
-    if (DM_MODE2 == 1 || (DM_MODE2 == 2 && mma_cycles < 600)) j.mma_mode = 2;
+    if (DM_MODE2 == 1 || (DM_MODE2 == 2 && mma_cycles < DM_MODE2_CYCLES)) j.mma_mode = 2;
   }
   // ---- resident link: read the previous layer's staged tile in place (fused loop only) ----
   if (!P->layers.empty()) {
