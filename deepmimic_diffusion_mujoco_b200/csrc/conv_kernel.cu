@@ -1196,8 +1196,10 @@ __device__ __forceinline__ void local_sync(bool wrote_global, bool issues_tma) {
   if (issues_tma) fence_proxy_async_global();
 }
 
-// Out of line on purpose: the stages keep their own register allocation and the conv roles around the call keep theirs.
-__device__ __noinline__ void attn_stage_call(const ConvJob& job, int g, int b0, float* sm) {
+// The attention stages of the AT kernel variants.  (With one lane per softmax row the core stage needed more registers than
+// the 96 this kernel has and was kept out of line; with its 4 x 8 register block it inlines with 148 bytes of spills, and the
+// pass is 4 % faster than through the call.)
+__device__ __forceinline__ void attn_stage_call(const ConvJob& job, int g, int b0, float* sm) {
   if (job.kind == JOB_ATTN_NORM) attn_norm_stage(job, g, b0, threadIdx.x);
   else attn_core_stage(job, g, b0, threadIdx.x, sm);
 }
