@@ -67,6 +67,7 @@ __device__ __forceinline__ void trace_mark(unsigned long long* tr, int ev) {
 struct ConvShared {
   uint64_t a_full[2], a_empty[2], w_full[8], w_empty[8], acc_full, res_full;
   uint64_t tile_ready;   // resident link (leader CTA's copy is the live one): both CTAs' staged tiles are complete
+  uint64_t halo_free;    // L-split resident links: the TWIN pair's MMAs of the current unit have completed (its halo rows may be overwritten)
   uint64_t mc_done;      // weight multicast: the MMAs of the current unit have completed in BOTH pairs of the cluster
   uint64_t xstat_full;   // L-split: the twin CTA (other half of L, same samples) has delivered its GroupNorm partial sums
   uint32_t tmem_slot;
@@ -84,20 +85,21 @@ struct ConvShared {
 // though ring depths change from layer to layer inside the persistent kernel.
 struct RoleState {
   uint32_t a_bits = 0, w_bits = 0, acc_count = 0, res_count = 0, tile_count = 0, x_count = 0;
-  uint32_t mc_count = 0;
+  uint32_t mc_count = 0, h_count = 0;
   int pre_w = 0;   // producer: weight loads of the current unit that were already issued during the previous epilogue
   int lhalf = 0;       // L-split: which half of the positions this CTA's pair works on (0 when the job is not split)
   int pair_base = 0;   // rank of the pair's leader inside the cluster (0, or 2 for the second pair of a cluster of four)
 };
 
 // mc: weight stages are filled for, and released by, both pairs of the cluster (two MMA warps each)
-__device__ __forceinline__ void init_shared(ConvShared& sh, bool mc = false) {
+__device__ __forceinline__ void init_shared(ConvShared& sh, bool mc = false, bool ls = false) {
   for (int i = 0; i < 2; ++i) { mbar_init(&sh.a_full[i], 1); mbar_init(&sh.a_empty[i], 2); }   // both MMA warps release
   for (int i = 0; i < 8; ++i) { mbar_init(&sh.w_full[i], 1); mbar_init(&sh.w_empty[i], mc ? 4 : 2); }
   mbar_init(&sh.mc_done, 4);
   mbar_init(&sh.acc_full, 2);
   mbar_init(&sh.res_full, 1);
-  mbar_init(&sh.tile_ready, 2);   // one arrival from each CTA of the pair (the peer's is remote)
+  mbar_init(&sh.tile_ready, ls ? 4 : 2);   // one arrival from each CTA of the pair (the peer's is remote); L-split: and of the twin pair
+  mbar_init(&sh.halo_free, 2);             // both issuer warps of the twin pair's leader
   mbar_init(&sh.xstat_full, 128);  // one remote arrival per (sample, group) value pair the twin writes
   fence_barrier_init();
 }
@@ -366,11 +368,13 @@ __device__ __forceinline__ void mma_unit(const ConvJob& job, uint32_t smem_base,
       if (lt + 1 == job.n_ltiles && leader) {
         umma_commit_pair(&sh.acc_full, cmask);
         if (MC) umma_commit_pair(&sh.mc_done, (unsigned short)0xF);   // (one from each issuer warp of each pair)
+        if (LS) umma_commit_pair(&sh.halo_free, (unsigned short)(3u << (pair_base ^ 2)));   // the twin pair may overwrite our halo rows
       }
     } else if (++lt_in == job.lt_round || lt + 1 == job.n_ltiles) {   // end of a TMEM round: hand the accumulators to the epilogues
       lt_in = 0;
       if (leader) umma_commit_pair(&sh.acc_full, cmask);
       if (MC && leader && lt + 1 == job.n_ltiles) umma_commit_pair(&sh.mc_done, (unsigned short)0xF);
+      if (LS && leader && lt + 1 == job.n_ltiles) umma_commit_pair(&sh.halo_free, (unsigned short)(3u << (pair_base ^ 2)));
       if (lt + 1 < job.n_ltiles) {
         // the next round overwrites these columns in BOTH CTAs: wait until both epilogues have drained them
         mbar_wait_cluster(&sh.tile_ready, rs.tile_count & 1, 0x320);
@@ -1070,9 +1074,31 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
       const int per_blk = 2 * kStageGap / 16;
       for (int i = tid; i < 2 * job.st_nq * per_blk; i += kEpiThreads) {
         const int blk = i / per_blk, o = i - blk * per_blk;
-        const uint32_t off = o < kStageGap / 16 ? (uint32_t)o * 16u : kStageGap + blk_bytes + (uint32_t)(o - kStageGap / 16) * 16u;
+        const bool leading = o < kStageGap / 16;
+        // L-split: the gap towards the other half holds ITS edge rows (written by the twin CTA, below): only the outer one is zero
+        if (LS && job.ls && leading == (rs.lhalf != 0)) continue;
+        const uint32_t off = leading ? (uint32_t)o * 16u : kStageGap + blk_bytes + (uint32_t)(o - kStageGap / 16) * 16u;
         sts128(stg + (uint32_t)blk * blk_stride + off, z);
       }
+    }
+    if (LS && job.ls && job.next_res) {
+      // The consumer's conv halo across the split: this CTA's two edge positions (16 rows of every block, raw bytes: the rows
+      // keep their swizzle phase) go into the twin CTA's gap, once the twin's MMAs of THIS layer no longer read the rows that
+      // are there (halo_free).  The twin's arrival on our leader's tile_ready (below) covers its copy into our gaps.
+      fence_proxy_async_smem();
+      if (warp == kPollWarp) mbar_wait_cluster(&sh.halo_free, rs.h_count & 1, 0x540);
+      named_bar_sync(1, kEpiThreads);            // every row of this tile is staged, and the twin's gap may be written
+      const uint32_t rb = (uint32_t)job.st_cw * 2u;                                     // bytes per staged row
+      const uint32_t src0 = rs.lhalf == 0 ? kStageGap + blk_bytes - 16u * rb : kStageGap;          // last / first two positions
+      const uint32_t dst0 = rs.lhalf == 0 ? kStageGap - 16u * rb : kStageGap + blk_bytes;          // twin's leading / trailing gap
+      const uint32_t twin = (uint32_t)((rs.pair_base ^ 2) + rank);
+      const int per_blk16 = (int)(16u * rb / 16u);
+      for (int i = tid; i < 2 * job.st_nq * per_blk16; i += kEpiThreads) {
+        const int blk = i / per_blk16, o = i - blk * per_blk16;
+        const uint4 v = lds128(stg + (uint32_t)blk * blk_stride + src0 + 16u * (uint32_t)o);
+        st_remote_b128(mapa_u32(stg + (uint32_t)blk * blk_stride + dst0 + 16u * (uint32_t)o, twin), v);
+      }
+      fence_proxy_async_all();                   // remote generic-proxy writes -> the twin's tensor-core reads
     }
     fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store engine / next MMAs
     tc_fence_before();                    // this thread's TMEM reads are complete before the hand-over below
@@ -1080,6 +1106,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     if (job.next_res && threadIdx.x == 0) {   // releases the leader's MMA warps waiting in the next layer (one arrival per CTA)
       if (rank == 0) mbar_arrive(&sh.tile_ready);
       else mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)((LS || MC) ? rs.pair_base : 0)));
+      if (LS && job.ls) mbar_arrive_remote(mapa_u32(smem_u32(&sh.tile_ready), (uint32_t)(rs.pair_base ^ 2)));   // ... and the twin pair's
     }
     trace_mark<TR>(tr, 15);
     if (tid == 0 && !job.no_store) {
@@ -1095,6 +1122,7 @@ __device__ __forceinline__ void epilogue_unit(const ConvJob& job, const ConvMaps
     }
     __syncwarp();
   }
+  if (LS && job.ls) rs.h_count++;   // (one halo_free phase per unit, waited for or not)
   trace_mark<TR>(tr, 11);
 }
 
@@ -1125,8 +1153,8 @@ __device__ __forceinline__ void run_unit(const ConvJob& job, const ConvMaps* map
 
 // Pair set-up / tear-down shared by both kernels: barriers of both CTAs exist before any remote arrival or pair TMA can
 // target them, and nobody frees TMEM or leaves while the leader's MMAs may still read the peer's shared memory.
-__device__ __forceinline__ uint32_t pair_begin(ConvShared& sh, int warp, uint32_t tmem_cols, bool mc = false) {
-  if (threadIdx.x == 0) init_shared(sh, mc);
+__device__ __forceinline__ uint32_t pair_begin(ConvShared& sh, int warp, uint32_t tmem_cols, bool mc = false, bool ls = false) {
+  if (threadIdx.x == 0) init_shared(sh, mc, ls);
   __syncthreads();
   if (warp == kMmaWarp) tmem_alloc_pair(&sh.tmem_slot, tmem_cols);
   tc_fence_before();
@@ -1219,7 +1247,7 @@ sample_loop_kernel(const __grid_constant__ LoopParams lp) {
   const int crank = (int)cluster_ctarank();
   const int rank = crank & 1;
   const int g = MC ? 2 * (int)cluster_id_x() + (crank >> 1) : (int)cluster_id_x();
-  const uint32_t tmem_base = pair_begin(sh, warp, 512, MC);
+  const uint32_t tmem_base = pair_begin(sh, warp, 512, MC, LS);
   RoleState rs;
   rs.lhalf = LS ? crank >> 1 : 0;
   rs.pair_base = crank & ~1;

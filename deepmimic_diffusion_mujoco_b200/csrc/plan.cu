@@ -248,6 +248,7 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   // a half that is not a whole number of MMA tiles (H = 480: 30 positions at the deepest level): the padded rows of its
   // last tile must not be stored (they would land in the other half), so the store boxes below cover the valid rows only
   const bool ls_padded = ls && (Lj % pos_per_mt || j.n_ltiles * Mt * pos_per_mt != Lj);
+  ly.ls_padded = ls_padded;
   j.a_plane_bytes = j.box_l * j.S * j.row_bytes;
   j.a_tx_bytes = 2 * j.a_plane_bytes;
   j.a_stage_bytes = round_up(j.a_tx_bytes, 1024);
@@ -580,8 +581,10 @@ static int add_conv(dm_plan* P, const WeightMap& W, const ConvSpec& sp, int* out
   if (!P->layers.empty()) {
     Layer& pv = P->layers.back();
     const ConvJob& pj = pv.job;
-    const int halo_hi_rows = (j.box_l - j.halo_lo - Lin) * j.S;
-    const bool ok = !ls && pv.kind == JOB_CONV && pj.st_cw != 0 && !pj.st_wave && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
+    // (L-split: the tile is one half of the positions; the gap towards the other half receives ITS edge rows from the twin
+    // CTA through distributed shared memory, conv_kernel.cu.  A padded half keeps garbage rows behind its valid ones: no link.)
+    const int halo_hi_rows = (j.box_l - j.halo_lo - (Lin >> ls)) * j.S;
+    const bool ok = !(ls && (pv.ls_padded || ls_padded)) && pv.kind == JOB_CONV && pj.st_cw != 0 && !pj.st_wave && pv.out_act == sp.src[0] && sp.nsrc == 1 && pj.S == 8 && j.S == 8 && pv.slices == 1 &&
                     ly.slices == 1 && pj.st_cw == j.Cc && j.src_chunks[0] == pj.st_nq && j.n_ltiles == 1 &&
                     pj.Lout * pj.S == pj.st_rows && j.halo_lo * j.S * j.row_bytes <= kStageGap &&
                     halo_hi_rows * j.row_bytes <= kStageGap;
@@ -984,7 +987,7 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     const ConvJob& pj = P->layers[i - 1].job;
     if (P->layers[i].kind != 0 || P->layers[i - 1].kind != 0) continue;
 #ifndef DM_NO_GAPS_CLEAN
-    j.gaps_clean = j.next_res && j.a_res && pj.next_res && pj.st_cw == j.st_cw && pj.st_nq == j.st_nq &&
+    j.gaps_clean = !P->lsplit && j.next_res && j.a_res && pj.next_res && pj.st_cw == j.st_cw && pj.st_nq == j.st_nq &&
                    pj.st_blk_stride == j.st_blk_stride && pj.st_rows == j.st_rows && j.f32_stride == 0;
 #endif
   }

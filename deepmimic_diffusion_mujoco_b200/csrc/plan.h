@@ -22,6 +22,7 @@ struct Act {
 
 struct Layer {
   int kind = 0;          // == job.kind: JOB_CONV (job, maps), or an attention stage (job only; attn_stages.cuh)
+  bool ls_padded = false;   // L-split: the half is not a whole number of MMA tiles (no resident link from or to this layer)
   bool mc_ok = false;    // quarter-tile weight maps exist (weight multicast)
   bool hidden = false;   // intermediate of an attention block: dm_plan_layer_info reports no output for it
   ConvJob job;

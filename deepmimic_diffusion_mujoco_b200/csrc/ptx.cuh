@@ -230,6 +230,10 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar, unsigned short m
       "h"(mask)
       : "memory");
 }
+// 16 bytes into another CTA's shared memory (shared::cluster address from mapa)
+__device__ __forceinline__ void st_remote_b128(uint32_t remote, const uint4& v) {
+  asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(remote), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 // fp32 pair into another CTA's shared memory (shared::cluster address from mapa)
 __device__ __forceinline__ void st_remote_f32x2(uint32_t remote, float a, float b) {
   asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(a), "f"(b) : "memory");
