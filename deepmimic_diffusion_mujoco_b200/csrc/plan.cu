@@ -1144,10 +1144,13 @@ extern "C" int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, 
   int n_sm = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+#ifndef DM_LSPLIT_MIN_H
+#define DM_LSPLIT_MIN_H 128
+#endif
 #ifdef DM_NO_LSPLIT
   bool try_split = false;
 #else
-  bool try_split = 4 * G <= n_sm && H >= 128 && (H >> (n_mults - 1)) % 2 == 0;
+  bool try_split = 4 * G <= n_sm && H >= DM_LSPLIT_MIN_H && (H >> (n_mults - 1)) % 2 == 0;
 #endif
   dm_plan* P = nullptr;
   for (;;) {
