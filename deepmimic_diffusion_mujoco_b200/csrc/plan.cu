@@ -1058,7 +1058,9 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if (P->mcast)
       for (int i = 0; i < n; ++i) {
         P->loop_jobs[i].mc = 1;           // (every job or none: the kernel variant is chosen by the first job's flag)
-        P->loop_jobs[i].sync_local = 0;   // the other pair writes into this CTA's weight stages: cluster barrier
+        // The other pair's producer fills THIS CTA's weight stages for the next layer as soon as ITS roles are through the
+        // barrier: a block barrier is enough only where those stages lie beyond this layer's staging (what pre_next says).
+        if (P->loop_jobs[i].pre_next == 0) P->loop_jobs[i].sync_local = 0;
       }
     if ((rc = dev_alloc(P, reinterpret_cast<void**>(&P->maps_dev), n * sizeof(ConvMaps), false))) return rc;
     DM_CUDA(cudaMemcpy(P->maps_dev, maps.data(), n * sizeof(ConvMaps), cudaMemcpyHostToDevice));
@@ -1412,7 +1414,8 @@ extern "C" int dm_sample_loop(dm_plan_t* P, float* x_dev, int have_start, const 
   lp.maps = P->maps_dev;
   lp.steps = P->steps_dev; lp.n_steps = timesteps; lp.tb_table = P->tb_table; lp.TB = P->TB;
   lp.G = P->G; lp.B = P->B; lp.H = P->H; lp.T = P->T;
-  lp.k4_local = !P->lsplit && !P->mcast && P->layers.front().job.S == 8 && P->layers.back().job.S == 8;
+  lp.k4_local = !P->lsplit && (!P->mcast || P->layers.back().job.pre_next > 0) && P->layers.front().job.S == 8 &&
+                P->layers.back().job.S == 8;
   lp.trace = P->trace_dev; lp.trace_cluster = P->trace_cluster; lp.trace_step = P->trace_step;
   DM_CUDA(launch_sample_loop(lp, P->loop_smem, s));
   P->last_launches = 1;
