@@ -2,12 +2,17 @@
 // fed, with the reference block's epilogue fused: bias -> GroupNorm(8) -> Mish -> + time bias -> + residual.
 // Two kernels share the device code below:
 //   conv_gemm_kernel    one launch per layer (dm_unet_forward: arbitrary per-sample timesteps, layer debugging)
-//   sample_loop_kernel  PERSISTENT: a 2-CTA cluster owns one 16-sample group and runs every layer of every
-//                       denoising step plus the fused DDPM update (K4) with only cluster-local barriers --
-//                       samples never interact, so the whole p_sample_loop is one launch.
+//   sample_loop_kernel  PERSISTENT: a CTA pair (tcgen05 cta_group::2) owns one 16-sample group and runs every layer of
+//                       every denoising step plus the fused DDPM update (K4); samples never interact, so the whole
+//                       p_sample_loop is one launch.  Template variants (the common one carries none of the others' code):
+//                         RD  big tiles: TMEM rounds (H > 256) and wave-staged epilogues
+//                         LS  L-split: clusters of four = two pairs per group, half of the positions each (small batches
+//                             at H >= 128); GroupNorm sums and conv halos cross the split through distributed shared memory
+//                         MC  weight multicast: clusters of four = two groups whose pairs share every weight tile
+//                         AT  the attention blocks' CUDA-core stages (attn_stages.cuh) as jobs of the same list
 //
 // Data layout: activations are fp16 planes [plane][G][L][16][C] (plane 0 = hi, 1 = lo,
-// value = hi + lo).  A work unit owns S (8 or 16) samples of one group for ALL L positions, so its GEMM rows
+// value = hi + lo).  A CTA owns S = 8 samples of one group for all L positions (half of them when split), so its GEMM rows
 // are ordered (l, b): row = l * S + b.  A conv tap that reads position l + d is then the SAME shared-memory
 // tile viewed d * S rows further down -- a whole number of 8-row swizzle atoms -- so the five taps of a k=5
 // conv are five UMMA descriptors over one TMA-loaded box (halo rows zero-filled by TMA out-of-bounds handling).
