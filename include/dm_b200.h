@@ -21,7 +21,7 @@ typedef void* dm_stream_t; /* cudaStream_t */
 
 enum dm_status {
   DM_OK = 0,
-  DM_ERR_ARG = -1,     /* bad argument / unsupported shape (e.g. H % 8 != 0, an attention tile beyond shared memory) */
+  DM_ERR_ARG = -1,     /* bad argument / unsupported shape (e.g. H % 8 != 0) */
   DM_ERR_DEVICE = -2,  /* no CUDA device, or device is not sm_100 */
   DM_ERR_CUDA = -3,    /* a CUDA runtime / driver call failed */
   DM_ERR_WEIGHT = -4,  /* a state_dict tensor is missing or has the wrong shape */
@@ -71,8 +71,10 @@ const char* dm_last_error(void);
 
 /* TemporalUnet.__init__ + load_state_dict (diffuser/models/temporal.py:51-113).  Packs the weights into fp16
  * hi/lo UMMA operand tiles, builds TMA descriptors and the per-layer launch list for batch B, horizon H,
- * transition_dim T.  attention=True state dicts (helpers.py:75-131) add one launch per attention stage and switch
- * dm_sample_loop to per-layer launches. */
+ * transition_dim T.  attention=True state dicts (helpers.py:75-131) add four jobs per attention block (LayerNorm stage,
+ * to_qkv conv, softmax / context stage, to_out conv) to the same list; dm_sample_loop stays one launch.  The layout is
+ * chosen here: one CTA pair per 16-sample group, two pairs per group for small batches at H >= 128 (dm_plan_ctas_per_group),
+ * clusters of two groups sharing weight tiles by TMA multicast at H <= 128 when all of them are resident at once. */
 int dm_plan_create(const dm_tensor_t* weights, int n_weights, int B, int H, int T, int dim, const int* dim_mults,
                    int n_mults, dm_plan_t** plan);
 void dm_plan_free(dm_plan_t* plan);
