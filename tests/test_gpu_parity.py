@@ -376,6 +376,32 @@ def test_horizons_beyond_256_layers_and_chain(dm, B, H, n):
         assert tuple(out.trajectories.shape) == (B, H, 35)
 
 
+def test_plan_lifecycle_returns_device_memory(dm):
+    """Plans of every layout (one pair per group, multicast clusters, L-split with its fallback build, attention blocks,
+    TMEM rounds) are created, used for a pass and freed, twice over: the second round must not need more device memory
+    than the first (dm_plan_free returns the packed weights, the per-layer activations, the schedule tables, the workspace
+    the split layout's abandoned first build allocated, ...)."""
+    import gc
+    shapes = [(3, 64, False), (32, 64, False), (5, 128, False), (2, 480, False), (608, 480, False), (4, 64, True)]
+
+    def one_round():
+        for B, H, attn in shapes:
+            net = dm.TemporalUnet(H, 35, 35, attention=attn)
+            net.load_state_dict(O.seeded_state_dict(H=H, seed=1, attention=attn))
+            diff = dm.GaussianDiffusion(net, H, 35, n_timesteps=2, predict_epsilon=False).cuda()
+            out = diff.p_sample_loop((B, H, 35), {}, verbose=False, seed=3)
+            assert torch.isfinite(out.trajectories).all()
+            del out, diff, net
+        gc.collect()
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        return torch.cuda.mem_get_info()[0]
+
+    free1 = one_round()
+    free2 = one_round()
+    assert free1 - free2 < 8 << 20, (free1, free2)     # (allocator granularity, not a plan's worth: the smallest plan is > 100 MB)
+
+
 def test_ddpm_step_kernel_matches_oracle(dm):
     """K4 alone through dm_ddpm_step, both parameterisations, with clamp and a per-sample mask."""
     import ctypes
