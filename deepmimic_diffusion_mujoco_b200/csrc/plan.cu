@@ -1034,11 +1034,14 @@ static int build_unet(dm_plan* P, const WeightMap& W) {
     if ((rc = alias_loop_workspace(P, maps))) return rc;
     // Weight multicast (conv_kernel.cu, producer_unit): clusters of four CTAs = two groups whose pairs share every weight
     // tile.  Common kernel shape only, an even number of groups, and at least one full cluster's worth of them.
+#ifndef DM_MCAST_MAX_H
+#define DM_MCAST_MAX_H 128
+#endif
 #ifndef DM_NO_MCAST
     // Measured (A/B, ms per pass): B = 1024, H = 64: 43.2 -> 40.0; B = 2048, H = 128: 158.2 -> 153.0.  The multicast form costs
     // four small TMA operations per tile instead of two, and at long horizons the first levels re-stream their 2 KB tiles per
     // l-tile: B = 256, H = 480 (L-split) 172.9 -> 187.7, and the L-split layouts at H = 128 / 256 gain under 1 %.
-    P->mcast = !P->has_attention && !P->lsplit && P->G % 2 == 0 && P->H <= 128;
+    P->mcast = !P->has_attention && !P->lsplit && P->G % 2 == 0 && P->H <= DM_MCAST_MAX_H;
     for (int i = 0; i < n; ++i) {
       const Layer& ly = P->layers[i];
       if (ly.kind != JOB_CONV || !ly.mc_ok) P->mcast = false;
